@@ -1,0 +1,197 @@
+/* pmhot.h — C ABI of libpmhot, the B200-native photon-mapping hot path.
+ *
+ * This is the drop-in boundary for the three device stages of
+ * nico-mayora/photon-mapping (citations are paths inside the reference tree):
+ *
+ *   stage 1  photon emission + multi-bounce tracing
+ *            replaces owlRayGenLaunch2D(pointLightRayGen)      photon-mapping/src/hostCode.cu:72-90
+ *            and the device programs                           photon-mapping/cuda/deviceCode.cu:10-136
+ *   stage 2  photon-map (left-balanced kd-tree) construction
+ *            replaces cukd::buildTree<Photon,Photon_traits>    ray-tracer/src/hostCode.cu:94-95
+ *   stage 3  per-pixel kNN radiance gather / render
+ *            replaces owlRayGenLaunch2D(simpleRayGen)          ray-tracer/src/hostCode.cu:231-237
+ *            and cukd::stackBased::knn + gatherPhotons         ray-tracer/cuda/shading.h:11-18,93-121
+ *   scene    replaces loadGeometry (OptiX BLAS/TLAS)           common/src/world.cpp:3-58
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative PM_ERR_* code; pm_last_error()
+ *     returns a thread-local message for the last failure. No exceptions cross the ABI.
+ *   - plain pointers and sizes only. Pointers named *_host must be host memory, *_dev device
+ *     memory; pointers without a suffix may be either (the library asks the CUDA runtime which
+ *     it is and stages host buffers through device memory itself).
+ *   - a pm_ctx is bound to one CUDA device and owns one stream. Calls are synchronous on
+ *     return unless documented otherwise. A context is not thread-safe; use one per thread.
+ *   - there is no CPU fallback: without a usable CUDA device pm_ctx_create fails with
+ *     PM_ERR_CUDA and nothing else can be called.
+ */
+#ifndef PMHOT_H
+#define PMHOT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PM_OK              0
+#define PM_ERR_INVALID    -1   /* bad argument */
+#define PM_ERR_CUDA       -2   /* CUDA runtime error (message in pm_last_error) */
+#define PM_ERR_NOMEM      -3
+#define PM_ERR_IO         -4
+#define PM_ERR_CAPACITY   -5   /* output buffer too small; *count holds the required size */
+#define PM_ERR_UNSUPPORTED -6
+
+/* ---- record layouts (byte-for-byte the reference structs) ---------------------------- */
+
+/* pass-1 photon, photon-mapping/include/photon.h:5-11 — 40 bytes */
+typedef struct pm_photon40 {
+  float   pos[3];
+  float   dir[3];      /* OUTGOING scattered direction (deviceCode.cu:15) */
+  int32_t power;       /* never written by the reference; we write 0 */
+  float   color[3];    /* colour carried BEFORE the albedo of this hit */
+} pm_photon40;
+
+/* pass-2 photon = kd-tree node, ray-tracer/include/photon.h:11-22 — 44 bytes */
+typedef struct pm_photon44 {
+  float   pos[3];
+  float   dir[3];
+  float   color[3];
+  float   power;
+  uint8_t quantized_normal[3];   /* unused by the reference */
+  uint8_t split_dim;             /* filled by pm_map_build */
+} pm_photon44;
+
+/* common/src/mesh.h:6-12 — 28 bytes */
+typedef struct pm_material {
+  float albedo[3];
+  float diffuse;
+  float specular;
+  float transmission;
+  float refraction_idx;
+} pm_material;
+
+/* point light: the fields of LightSource (common/src/world.h:13-24) the device code reads */
+typedef struct pm_light {
+  float  pos[3];
+  float  rgb[3];
+  double power;
+} pm_light;
+
+/* ray-tracer/include/deviceCode.h:29-34 (already set up as in hostCode.cu:100-108) */
+typedef struct pm_camera {
+  float pos[3];
+  float dir_00[3];
+  float dir_du[3];
+  float dir_dv[3];
+} pm_camera;
+
+typedef struct pm_ray {
+  float org[3];
+  float tmin;
+  float dir[3];
+  float tmax;
+} pm_ray;
+
+typedef struct pm_hit {
+  int32_t prim;     /* global triangle id, -1 on miss */
+  float   t;        /* hit distance (ray parameter) */
+} pm_hit;
+
+/* RNG modes for pm_emit_photons / pm_render */
+#define PM_RNG_LCG_PARITY 0   /* owl::LCG<4> seeded exactly like the reference */
+#define PM_RNG_COUNTER    1   /* counter-based hash RNG keyed by (seed, id, draw) */
+
+typedef struct pm_ctx   pm_ctx;
+typedef struct pm_scene pm_scene;
+typedef struct pm_map   pm_map;
+
+/* ---- context ------------------------------------------------------------------------- */
+const char* pm_last_error(void);
+int  pm_version(void);
+int  pm_ctx_create(int device, pm_ctx** out);
+void pm_ctx_destroy(pm_ctx* ctx);
+/* cudaStream_t of the context, as an opaque pointer (for event timing by the caller) */
+void* pm_ctx_stream(pm_ctx* ctx);
+int  pm_ctx_sync(pm_ctx* ctx);
+/* counters: number of kernels launched by this context since creation / last reset */
+int64_t pm_ctx_launch_count(pm_ctx* ctx);
+void pm_ctx_reset_launch_count(pm_ctx* ctx);
+/* device time in ms of the most recent call's dominant kernel(s) (CUDA events on ctx stream) */
+float pm_ctx_last_kernel_ms(pm_ctx* ctx);
+
+/* ---- scene: LBVH build + traversal  (≙ loadGeometry, common/src/world.cpp:3-58) ------- */
+/* verts: 3*nv floats; tris: 3*nt vertex indices; tri_mesh: nt mesh ids; mats: n_mesh records */
+int  pm_scene_create(pm_ctx* ctx, const float* verts_host, int nv,
+                     const int32_t* tris_host, int nt, const int32_t* tri_mesh_host,
+                     const pm_material* mats_host, int n_mesh, pm_scene** out);
+void pm_scene_destroy(pm_scene* scene);
+/* test hook: closest hit for n rays (≙ optixTrace with closest-hit, both face orientations) */
+int  pm_trace_closest(pm_ctx* ctx, const pm_scene* scene, const pm_ray* rays, int64_t n, pm_hit* hits);
+/* test hook: occlusion (≙ the TERMINATE_ON_FIRST_HIT shadow ray, ray-tracer/cuda/deviceCode.cu:70-85) */
+int  pm_trace_occluded(pm_ctx* ctx, const pm_scene* scene, const pm_ray* rays, int64_t n, uint8_t* occluded);
+
+/* ---- stage 1 (≙ runNormal/runCaustics → runPointLightRayGen loop) -------------------- */
+/* Emits for every light int(power * int(casted / sum(power))) photon paths
+ * (photon-mapping/src/hostCode.cu:86,102-110), walks them for at most max_depth segments and
+ * appends stored photons to `out` (host or device, capacity records). This rank traces launch
+ * indices first_photon, first_photon+photon_stride, ... of every light.
+ * *count receives the number stored; *n_paths and *n_segments (may be NULL) the work done. */
+int  pm_emit_photons(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host, int n_lights,
+                     int64_t casted, int max_depth, int caustics_mode,
+                     uint64_t seed, int rng_mode, int64_t first_photon, int64_t photon_stride,
+                     pm_photon40* out, int64_t capacity, int64_t* count,
+                     int64_t* n_paths, int64_t* n_segments);
+
+/* pass-1 → pass-2 record conversion done by ray-tracer/src/hostCode.cu:65-83:
+ * global map = non-caustic (power 1.0) followed by caustic (power 0.5); caustic map = caustic (0.5).
+ * `out_global` needs n_global + n_caustic records, `out_caustic` n_caustic. Device or host pointers. */
+int  pm_photons_to_maps(pm_ctx* ctx, const pm_photon40* global_in, int64_t n_global,
+                        const pm_photon40* caustic_in, int64_t n_caustic,
+                        pm_photon44* out_global, pm_photon44* out_caustic);
+
+/* ---- stage 2 (≙ cukd::buildTree<Photon,Photon_traits>) ------------------------------- */
+/* Reorders photons[0..n) IN PLACE into left-balanced kd-tree order (array index = node id),
+ * fills split_dim, writes the AABB to bounds[6] = {lo.xyz, hi.xyz} (may be NULL), and returns a
+ * map handle that owns the query-side acceleration copy. n < 1 → *out = NULL, returns PM_OK
+ * (builder_thrust.h:441). photons may be host or device memory. The map keeps a pointer to
+ * `photons` only if it is device memory; otherwise it owns a device copy. */
+int  pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n, float* bounds_host, pm_map** out);
+/* Wrap an array that is ALREADY in tree order (e.g. built by the reference builder). */
+int  pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map** out);
+void pm_map_destroy(pm_map* map);
+int64_t pm_map_size(const pm_map* map);
+
+/* ---- stage 3 ------------------------------------------------------------------------- */
+/* kNN (≙ cukd::stackBased::knn<HeapCandidateList<k>> with cutoff radius):
+ * for each query the k smallest (dist² bits, node id) among nodes with dist² < cutoff².
+ * out_ids: nq*k int32, slots not filled are -1; out_dist2 (nq*k, may be NULL) holds the matching
+ * squared distances (cutoff² in unfilled slots); out_r2 (nq, may be NULL) is the return value of
+ * knn(): the largest dist² if k were found, else cutoff². Slots are sorted ascending.
+ * k must be one of 8, 16, 32, 50, 64. All pointers host or device. */
+int  pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int k,
+            float cutoff_radius, int32_t* out_ids, float* out_dist2, float* out_r2);
+
+/* fused kNN + radiance estimate (≙ gatherPhotons, ray-tracer/cuda/shading.h:93-121).
+ * hit: 3*nq, brdf: nq, out_rgb: 3*nq. */
+int  pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, int64_t nq,
+               int k, float cutoff_radius, float* out_rgb);
+
+/* render (≙ simpleRayGen launch): fb is W*H RGBA8, rows as the reference writes them
+ * (row H - py; row 0 stays 0, the reference's out-of-bounds row H is not written).
+ * maps may be NULL (empty). Pixels [pixel_begin, pixel_end) of the launch grid (index = px + W*py)
+ * are rendered by this call (tile sharding); pass 0, W*H for everything. */
+int  pm_render(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host, int n_lights,
+               const pm_map* global_map, const pm_map* caustic_map, const pm_camera* camera,
+               int width, int height, int spp, int depth, const float sky[3],
+               int64_t pixel_begin, int64_t pixel_end, uint32_t* fb_rgba8);
+
+/* ---- photon wire format (≙ writeAlivePhotons / readPhotonsFromFile) ------------------ */
+/* text: 9 floats "pos dir color", std::fixed, 6 decimals (photon-mapping/src/hostCode.cu:31-49) */
+int  pm_photons_write_text(const char* path, const pm_photon40* photons_host, int64_t n);
+/* reads at most capacity records; *count = number of records in the file */
+int  pm_photons_read_text(const char* path, pm_photon40* photons_host, int64_t capacity, int64_t* count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PMHOT_H */
