@@ -1,0 +1,365 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200-native photon-mapping hot path.
+
+Workload (BASELINE.json configs[1], "C2"): synthetic uniform photon cloud of 10 M photons (per-axis seeded
+permutations scaled by 2^-18 → unique coordinates → unique kd-tree), 1 M kNN queries, k = 64, cutoff radius 100.
+A *step* is one pass of the kNN gather over the 1 M-query batch on a photon map that is resident in HBM.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+N > 1 is launched by torchrun (one rank per GPU). The photon map is replicated, every rank answers its own
+1 M queries (weak scaling, no data-path collective — SURVEY §8e: pixels/queries shard with no communication).
+Rank 0 prints ONE JSON line.
+
+`--impl reference` times the CPU arm: the reference has no CPU implementation of the gather (it is
+GPU-only through OptiX/cukd device code), so the arm is the oracle port of cukd's stackBased::knn
+(oracle/orc_kdtree.cpp, kind "port") on all host threads over a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_PHOTONS = 10_000_000
+N_QUERIES = 1_000_000
+K = 64
+CUTOFF = 100.0
+SCALE = 2.0**-18
+QUERY_EXTENT = 38.15
+BYTES_PER_QUERY = 12 + 20 * K  # query 12 B + k*(12 B position read + 8 B id/dist² written)
+METRIC = "knn_gather_queries_per_s_k64"
+UNIT = "queries/s"
+
+PHOTON44 = np.dtype(
+    [("pos", "<f4", 3), ("dir", "<f4", 3), ("color", "<f4", 3), ("power", "<f4"), ("qn", "u1", 3), ("split_dim", "u1")]
+)
+
+
+def make_cloud(n: int) -> np.ndarray:
+    import torch
+
+    a = np.zeros(n, PHOTON44)
+    for ax in range(3):
+        g = torch.Generator().manual_seed(1234 + ax)
+        a["pos"][:, ax] = (torch.randperm(n, generator=g).to(torch.float32) * SCALE).numpy()
+    a["dir"][:, 2] = 1.0
+    a["color"] = 1.0
+    a["power"] = 1.0
+    return a
+
+
+def make_queries(nq: int, rank: int) -> np.ndarray:
+    import torch
+
+    g = torch.Generator().manual_seed(4321 + rank)
+    return (torch.rand((nq, 3), generator=g) * QUERY_EXTENT).numpy().astype(np.float32)
+
+
+def load_oracle():
+    path = os.path.join(ROOT, "oracle", "libpm_oracle.so")
+    L = ctypes.CDLL(path)
+    L.orc_knn_batch.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int,
+                                ctypes.c_float, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    L.orc_kd_build.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+    L.orc_omp_threads.restype = ctypes.c_int
+    return L
+
+
+def cpu_knn_rate(orc, tree: np.ndarray, queries: np.ndarray, budget_s: float = 12.0):
+    """queries/s of the oracle port on all host threads over a bounded sample (first `m` queries)."""
+    threads = orc.orc_omp_threads()
+    m = min(len(queries), 4096 * max(1, threads // 4))
+    ids = np.empty((len(queries), K), np.int32)
+    r2 = np.empty(len(queries), np.float32)
+
+    def run(count):
+        t0 = time.perf_counter()
+        orc.orc_knn_batch(tree.ctypes.data, len(tree), queries.ctypes.data, count, K, CUTOFF, ids.ctypes.data, None,
+                          r2.ctypes.data, 0)
+        return time.perf_counter() - t0
+
+    dt = run(m)  # calibration (also warms the caches)
+    rate = m / dt
+    m2 = int(min(len(queries), max(m, rate * budget_s)))
+    dt2 = run(m2)
+    return m2 / dt2, threads, m2, dt2
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for nme, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def traffic_per_launch():
+    """dram bytes per launch of the kNN kernel from the committed ncu capture, or None."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get("k_knn_64_dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+def run_reference(args, rank: int):
+    """CPU arm: oracle port of the reference's kNN (no GPU work at all)."""
+    if rank != 0:
+        return
+    orc = load_oracle()
+    cloud = make_cloud(N_PHOTONS)
+    t0 = time.perf_counter()
+    orc.orc_kd_build(cloud.ctypes.data, len(cloud), None)
+    build_s = time.perf_counter() - t0
+    threads = orc.orc_omp_threads()
+    queries = make_queries(N_QUERIES, 0)
+    ids = np.empty((N_QUERIES, K), np.int32)
+    # size one step to ~6 s of host work
+    probe = 4096 * max(1, threads // 4)
+    t0 = time.perf_counter()
+    orc.orc_knn_batch(cloud.ctypes.data, len(cloud), queries.ctypes.data, probe, K, CUTOFF, ids.ctypes.data, None, None, 0)
+    rate = probe / (time.perf_counter() - t0)
+    sample = int(min(N_QUERIES, max(probe, rate * 6.0)))
+    for _ in range(args.warmup):
+        orc.orc_knn_batch(cloud.ctypes.data, len(cloud), queries.ctypes.data, min(sample, probe), K, CUTOFF, ids.ctypes.data, None, None, 0)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        orc.orc_knn_batch(cloud.ctypes.data, len(cloud), queries.ctypes.data, sample, K, CUTOFF, ids.ctypes.data, None, None, 0)
+    dt = time.perf_counter() - t0
+    value = sample * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C2: 10M-photon uniform cloud, kNN k=64, cutoff 100 (CPU arm: bounded sample per step)",
+                   "photons": N_PHOTONS, "queries_per_step": sample, "k": K},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{sample} of {N_QUERIES} queries per step on the 10M-photon tree; oracle port of "
+                                   "cukd stackBased::knn<HeapCandidateList<64>> (the reference has no CPU path); "
+                                   f"tree built by the oracle in {build_s:.1f} s (untimed)"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank: int, local_rank: int, world: int):
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as graft
+
+    pkg = graft.load_package()
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = pkg.Context(local_rank)
+    ext_stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local_rank))
+
+    # ---- setup (untimed): synthetic cloud → device → photon map (stage 2) -----------------------
+    cloud = make_cloud(N_PHOTONS)
+    d_tree = torch.from_numpy(cloud.view(np.uint8)).cuda()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    pmap = pkg.PhotonMap.build(ctx, d_tree)
+    build_ms = 1e3 * (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    pmap.close()
+    d_tree.copy_(torch.from_numpy(cloud.view(np.uint8)))
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    pmap = pkg.PhotonMap.build(ctx, d_tree)  # second build: scratch already allocated
+    build_ms_warm = 1e3 * (time.perf_counter() - t0)
+
+    queries = make_queries(N_QUERIES, rank)
+    d_q = torch.from_numpy(queries).cuda()
+    d_ids = torch.empty((N_QUERIES, K), dtype=torch.int32, device="cuda")
+    d_d2 = torch.empty((N_QUERIES, K), dtype=torch.float32, device="cuda")
+    d_r2 = torch.empty(N_QUERIES, dtype=torch.float32, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def step_device():
+        pmap.knn(d_q, K, CUTOFF, out_ids=d_ids, out_dist2=d_d2, out_r2=d_r2)
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ctx.reset_launch_count()
+    step_ms, kern_ms = [], []
+    wall0 = time.perf_counter()
+    with torch.cuda.stream(ext_stream):
+        for _ in range(args.steps):
+            flush.zero_()  # L2 flush, outside the timed events
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(ext_stream)
+            step_device()
+            e1.record(ext_stream)
+            e1.synchronize()
+            step_ms.append(e0.elapsed_time(e1))
+            kern_ms.append(ctx.last_kernel_ms)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    wall_ms = 1e3 * (time.perf_counter() - wall0)
+    launches = ctx.launch_count
+    total_ms = float(sum(step_ms))
+    clocks = sampler.stop() if sampler else None
+
+    # ---- e2e: same call with HOST (pinned) buffers; H2D + D2H inside the timed region -------------
+    h_q = torch.from_numpy(queries).pin_memory()
+    h_ids = torch.empty((N_QUERIES, K), dtype=torch.int32).pin_memory()
+    h_r2 = torch.empty(N_QUERIES, dtype=torch.float32).pin_memory()
+
+    def step_host():
+        pkg._check(pkg.lib().pm_knn(ctx.handle, pmap.handle, h_q.data_ptr(), N_QUERIES, K, CUTOFF, h_ids.data_ptr(), None,
+                                    h_r2.data_ptr()))
+
+    for _ in range(2):
+        step_host()
+    e2e_steps = max(3, min(args.steps, 10))
+    e2e_ms = []
+    with torch.cuda.stream(ext_stream):
+        for _ in range(e2e_steps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(ext_stream)
+            step_host()
+            e1.record(ext_stream)
+            e1.synchronize()
+            e2e_ms.append(e0.elapsed_time(e1))
+    e2e_total = float(sum(e2e_ms))
+    assert int(h_ids[0, 0]) >= 0
+
+    t = torch.tensor([total_ms, e2e_total], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms_max, e2e_total_max = float(t[0]), float(t[1])
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        value = world * N_QUERIES * args.steps / (total_ms_max * 1e-3)
+        e2e_value = world * N_QUERIES * e2e_steps / (e2e_total_max * 1e-3)
+        k_ms = float(np.mean(kern_ms))
+        achieved = BYTES_PER_QUERY * N_QUERIES / (k_ms * 1e-3) / 1e9
+        # CPU baseline on this box's host cores (bounded sample), rank 0 at N = 1 only
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            orc = load_oracle()
+            tree_h = d_tree.cpu().numpy().view(PHOTON44).reshape(-1)
+            rate, threads, m, dt = cpu_knn_rate(orc, tree_h, queries)
+            cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
+                   "sample": f"first {m} of the {N_QUERIES} queries on the same 10M-photon tree ({dt:.1f} s); oracle port of cukd "
+                             "stackBased::knn<HeapCandidateList<64>>, OpenMP over queries (the reference has no CPU path)"}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": total_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C2: 10M-photon uniform cloud (unique coords), 1M kNN queries per GPU, k=64, cutoff 100",
+                       "photons": N_PHOTONS, "queries_per_gpu": N_QUERIES, "k": K,
+                       "parallelism": f"replicated map, queries sharded x{world}",
+                       "l2": "256 MiB flush write between steps (untimed); per-step working set 684 MB > 126 MB L2",
+                       "outputs": "ids + dist2 + r2 per query (device resident)"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(N_QUERIES * 12),
+                    "d2h_bytes_per_step": int(N_QUERIES * K * 4 + N_QUERIES * 4), "steps": e2e_steps,
+                    "api": "pm_knn with pinned host buffers (queries in, ids + r2 out)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic_per_launch(), "kernel": "k_knn<64>", "kernel_ms": k_ms,
+                         "algorithmic_bytes_per_launch": BYTES_PER_QUERY * N_QUERIES, "peak_source": peak_src},
+            "cpu_baseline": cpu,
+            "clocks": clocks,
+            "stage2_build": {"photons": N_PHOTONS, "ms_first": build_ms, "ms": build_ms_warm,
+                             "photons_per_s": N_PHOTONS / (build_ms_warm * 1e-3)},
+            "wall_ms_timed_region": wall_ms,
+        }
+        print(json.dumps(line), flush=True)
+    pmap.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world == 1 and args.gpus > 1:
+        # convenience: relaunch under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29531", os.path.abspath(__file__), "--gpus", str(args.gpus),
+               "--steps", str(args.steps), "--warmup", str(args.warmup)]
+        sys.exit(subprocess.call(cmd))
+    run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,132 @@
+/* pm_ctx.cu — context, error reporting, scratch memory and host/device staging. */
+#include <cstdarg>
+#include "pm_internal.h"
+
+namespace pm {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+bool is_device_ptr(const void* p) {
+  if (!p) return false;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+int stage_in(pm_ctx* ctx, int slot, const void* p, size_t bytes, const void** dev) {
+  if (!p || bytes == 0 || is_device_ptr(p)) { *dev = p; return PM_OK; }
+  void* d = nullptr;
+  PM_CHECK(ctx->get_scratch(slot, bytes, &d));
+  PM_CUDA(cudaMemcpyAsync(d, p, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  *dev = d;
+  return PM_OK;
+}
+
+int stage_out(pm_ctx* ctx, int slot, void* p, size_t bytes, OutStage* st) {
+  st->host = nullptr; st->dev = p; st->bytes = bytes;
+  if (!p || bytes == 0 || is_device_ptr(p)) return PM_OK;
+  void* d = nullptr;
+  PM_CHECK(ctx->get_scratch(slot, bytes, &d));
+  st->host = p; st->dev = d;
+  return PM_OK;
+}
+
+int stage_out_finish(pm_ctx* ctx, const OutStage& st) {
+  if (!st.host) return PM_OK;
+  PM_CUDA(cudaMemcpyAsync(st.host, st.dev, st.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  return PM_OK;
+}
+
+}  // namespace pm
+
+int pm_ctx::get_scratch(int slot, size_t bytes, void** out) {
+  pm::Scratch& s = scratch[slot];
+  if (bytes > s.cap) {
+    if (s.ptr) {
+      PM_CUDA(cudaStreamSynchronize(stream));
+      PM_CUDA(cudaFree(s.ptr));
+      s.ptr = nullptr; s.cap = 0;
+    }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&s.ptr, want);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      want = bytes;
+      e = cudaMalloc(&s.ptr, want);
+    }
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      pm::set_error("out of device memory allocating %zu bytes (scratch slot %d)", bytes, slot);
+      return PM_ERR_NOMEM;
+    }
+    s.cap = want;
+  }
+  *out = s.ptr;
+  return PM_OK;
+}
+
+extern "C" {
+
+const char* pm_last_error(void) { return pm::g_err; }
+int pm_version(void) { return 100; }
+
+int pm_ctx_create(int device, pm_ctx** out) {
+  if (!out) { pm::set_error("pm_ctx_create: out is NULL"); return PM_ERR_INVALID; }
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    pm::set_error("pm_ctx_create: no usable CUDA device (%s); libpmhot has no CPU fallback",
+                  e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    return PM_ERR_CUDA;
+  }
+  if (device < 0 || device >= ndev) { pm::set_error("pm_ctx_create: device %d out of range [0,%d)", device, ndev); return PM_ERR_INVALID; }
+  PM_CUDA(cudaSetDevice(device));
+  pm_ctx* c = new pm_ctx();
+  c->device = device;
+  cudaDeviceProp prop;
+  PM_CUDA(cudaGetDeviceProperties(&prop, device));
+  c->sm_count = prop.multiProcessorCount;
+  PM_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  PM_CUDA(cudaEventCreate(&c->ev0));
+  PM_CUDA(cudaEventCreate(&c->ev1));
+  *out = c;
+  return PM_OK;
+}
+
+void pm_ctx_destroy(pm_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (auto& s : ctx->scratch)
+    if (s.ptr) cudaFree(s.ptr);
+  cudaEventDestroy(ctx->ev0);
+  cudaEventDestroy(ctx->ev1);
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+void* pm_ctx_stream(pm_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int pm_ctx_sync(pm_ctx* ctx) {
+  if (!ctx) return PM_ERR_INVALID;
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PM_OK;
+}
+
+int64_t pm_ctx_launch_count(pm_ctx* ctx) { return ctx ? ctx->launches : 0; }
+void pm_ctx_reset_launch_count(pm_ctx* ctx) { if (ctx) ctx->launches = 0; }
+float pm_ctx_last_kernel_ms(pm_ctx* ctx) { return ctx ? ctx->last_kernel_ms : 0.f; }
+
+}  // extern "C"

@@ -1,0 +1,105 @@
+/* pm_internal.h — shared internals of libpmhot (not part of the ABI). */
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../include/pmhot.h"
+
+namespace pm {
+
+void set_error(const char* fmt, ...);
+
+#define PM_CUDA(call)                                                                       \
+  do {                                                                                      \
+    cudaError_t e__ = (call);                                                               \
+    if (e__ != cudaSuccess) {                                                               \
+      pm::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+      return PM_ERR_CUDA;                                                                   \
+    }                                                                                       \
+  } while (0)
+
+#define PM_CHECK(call)            \
+  do {                            \
+    int r__ = (call);             \
+    if (r__ != PM_OK) return r__; \
+  } while (0)
+
+#define PM_REQUIRE(cond, msg)                       \
+  do {                                              \
+    if (!(cond)) {                                  \
+      pm::set_error("%s: %s", __func__, msg);       \
+      return PM_ERR_INVALID;                        \
+    }                                               \
+  } while (0)
+
+inline int64_t div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+/* growable device scratch buffers owned by the context, reused across calls so the hot calls do
+ * not cudaMalloc/cudaFree (both synchronise the device) */
+struct Scratch {
+  void* ptr = nullptr;
+  size_t cap = 0;
+};
+
+enum ScratchSlot {
+  S_STAGE_IN0 = 0, S_STAGE_IN1, S_STAGE_IN2, S_STAGE_OUT0, S_STAGE_OUT1, S_STAGE_OUT2,
+  S_KEYS0, S_KEYS1, S_VALS0, S_VALS1, S_CUB, S_PERM, S_MISC0, S_MISC1, S_MISC2, S_MISC3,
+  S_BUILD0, S_BUILD1, S_BUILD2, S_BUILD3, S_BUILD4, S_BUILD5, S_BUILD6, S_BUILD7, S_BUILD8,
+  S_BUILD9, S_BUILD10, S_BUILD11, S_BUILD12, S_BUILD13, S_BUILD14, S_BUILD15,
+  S_RENDER0, S_RENDER1, S_RENDER2, S_RENDER3, S_RENDER4, S_RENDER5, S_RENDER6, S_RENDER7,
+  S_RENDER8, S_RENDER9, S_RENDER10, S_RENDER11,
+  S_COUNT
+};
+
+}  // namespace pm
+
+struct pm_ctx {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int64_t launches = 0;
+  float last_kernel_ms = 0.f;
+  pm::Scratch scratch[pm::S_COUNT];
+
+  /* returns a device buffer of at least `bytes` in slot `slot` (contents undefined) */
+  int get_scratch(int slot, size_t bytes, void** out);
+  template <class T> int get_scratch(int slot, size_t count, T** out) {
+    void* p = nullptr;
+    int r = get_scratch(slot, count * sizeof(T), &p);
+    *out = (T*)p;
+    return r;
+  }
+};
+
+namespace pm {
+
+/* true if `p` is device-accessible global memory (device or managed allocation) */
+bool is_device_ptr(const void* p);
+
+/* Input staging: if `p` is a host pointer copy `bytes` to scratch slot and return the device
+ * alias, else return p unchanged. */
+int stage_in(pm_ctx* ctx, int slot, const void* p, size_t bytes, const void** dev);
+/* Output staging: if `p` is host memory return a scratch device buffer to write to and remember to
+ * copy back with stage_out_finish. */
+struct OutStage { void* host = nullptr; void* dev = nullptr; size_t bytes = 0; };
+int stage_out(pm_ctx* ctx, int slot, void* p, size_t bytes, OutStage* st);
+int stage_out_finish(pm_ctx* ctx, const OutStage& st);
+
+}  // namespace pm
+
+/* the photon map: tree-ordered AoS records (what the reference hands to its kernels) plus the
+ * query-side SoA copies this library traverses */
+struct pm_map {
+  pm_ctx* ctx = nullptr;
+  int64_t n = 0;
+  const pm_photon44* photons_dev = nullptr;  /* tree order; may alias caller memory */
+  pm_photon44* owned_photons = nullptr;      /* set if the map owns the AoS copy */
+  float4* nodes4 = nullptr;                  /* (x, y, z, bits(split_dim)) per node, tree order */
+  float4* color4 = nullptr;                  /* (r, g, b, power) per node */
+  float bounds[6] = {0, 0, 0, 0, 0, 0};
+};

@@ -1,0 +1,377 @@
+/* pm_kdbuild.cu — stage 2: photon-map construction.
+ *
+ * Produces exactly the array cukd::buildTree<Photon,Photon_traits> produces
+ * (reference: externals/cudaKDTree/cukd/builder_thrust.h:414-512, called from
+ * ray-tracer/src/hostCode.cu:94-95): a left-balanced kd-tree stored in level order (children of
+ * node i are 2i+1 / 2i+2), each node's split dimension = widest axis of the node's DOMAIN box
+ * (world AABB clipped by its ancestors' planes; ties → highest axis, cukd/box.h:112-125), pivot =
+ * element of rank |left subtree| among the node's elements ordered by (coord[dim], input index).
+ *
+ * The reference re-sorts all N 48-byte (tag, photon) tuples with a comparison sort once per level.
+ * This builder never moves photons until the end:
+ *   1. three radix sorts (one per axis) of 4-byte element indices by order-preserving float keys;
+ *   2. per level, for every live subtree: pick the pivot from the list sorted along the subtree's
+ *      split axis (its position is known in closed form), mark every element left/right, and
+ *      stable-partition the three index lists inside each subtree's range (prefix sums);
+ *   3. one gather writes the 44-byte records (and the 16-byte query-side copies) in node order.
+ * All three lists share the same segment geometry: positions are IN-ORDER ranks, so a subtree's
+ * range is [begin, begin+size) and its pivot sits at begin + |left subtree|; the slot a pivot
+ * leaves behind simply stays dead.
+ */
+#include <cub/cub.cuh>
+#include "pm_internal.h"
+
+namespace {
+
+constexpr int kDead = -1;
+
+__host__ __device__ inline int64_t subtree_size(int64_t root, int64_t n) {
+  int64_t total = 0, first = root, width = 1;
+  while (first < n) {
+    const int64_t last = (first + width < n) ? first + width : n;
+    total += last - first;
+    first = 2 * first + 1;
+    width *= 2;
+  }
+  return total;
+}
+
+__device__ inline uint32_t ordered_key(float f) {
+  f = f + 0.0f;  /* -0.0f -> +0.0f so that both zeros tie and fall back to index order */
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+/* AoS -> keys for the three axis sorts, and iota values */
+__global__ void k_extract(const pm_photon44* __restrict__ ph, int n, float* __restrict__ cx, float* __restrict__ cy,
+                          float* __restrict__ cz, uint32_t* __restrict__ kx, uint32_t* __restrict__ ky,
+                          uint32_t* __restrict__ kz, int* __restrict__ iota) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* p = reinterpret_cast<const float*>(ph) + (size_t)i * 11;
+  const float x = p[0], y = p[1], z = p[2];
+  cx[i] = x; cy[i] = y; cz[i] = z;
+  kx[i] = ordered_key(x); ky[i] = ordered_key(y); kz[i] = ordered_key(z);
+  iota[i] = i;
+}
+
+/* bounds from the sorted lists: min = first element, max = last element of each axis list */
+__global__ void k_root(const int* __restrict__ ox, const int* __restrict__ oy, const int* __restrict__ oz,
+                       const float* __restrict__ cx, const float* __restrict__ cy, const float* __restrict__ cz, int n,
+                       float* __restrict__ seg_box, int* __restrict__ seg_begin, float* __restrict__ bounds_out) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const float lo[3] = {cx[ox[0]], cy[oy[0]], cz[oz[0]]};
+  const float hi[3] = {cx[ox[n - 1]], cy[oy[n - 1]], cz[oz[n - 1]]};
+  for (int d = 0; d < 3; d++) { seg_box[d] = lo[d]; seg_box[3 + d] = hi[d]; bounds_out[d] = lo[d]; bounds_out[3 + d] = hi[d]; }
+  seg_begin[0] = 0;
+}
+
+__device__ inline int widest_dim(const float* b) {
+  int best = 0; float wbest = 0.f;
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    const float w = b[3 + d] - b[d];
+    if (w < wbest) continue;
+    wbest = w; best = d;
+  }
+  return best;
+}
+
+/* one thread per subtree of the current level: choose dim + pivot, emit the node, derive children */
+__global__ void k_split(int level_first, int level_count, int n, const int* __restrict__ ord0,
+                        const int* __restrict__ ord1, const int* __restrict__ ord2, const float* __restrict__ c0,
+                        const float* __restrict__ c1, const float* __restrict__ c2,
+                        const float* __restrict__ box_cur, const int* __restrict__ begin_cur,
+                        float* __restrict__ box_next, int* __restrict__ begin_next, int* __restrict__ seg_pivot,
+                        uint8_t* __restrict__ seg_dim, int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= level_count) return;
+  const int s = level_first + j;
+  float box[6];
+#pragma unroll
+  for (int d = 0; d < 6; d++) box[d] = box_cur[(size_t)j * 6 + d];
+  const int dim = widest_dim(box);
+  const int begin = begin_cur[j];
+  const int lchild = 2 * s + 1;
+  const int left = (lchild < n) ? (int)subtree_size(lchild, n) : 0;
+  const int pivot = begin + left;
+  const int* ord = dim == 0 ? ord0 : (dim == 1 ? ord1 : ord2);
+  const float* c = dim == 0 ? c0 : (dim == 1 ? c1 : c2);
+  const int e = ord[pivot];
+  const float split = c[e];
+  elem_of_node[s] = e;
+  dim_of_node[s] = (uint8_t)dim;
+  seg_pivot[j] = pivot;
+  seg_dim[j] = (uint8_t)dim;
+  /* children (index in the next level's arrays = 2j, 2j+1) */
+  const int next_first = 2 * level_first + 1;
+  if (lchild < n) {
+    const size_t o = (size_t)(lchild - next_first) * 6;
+#pragma unroll
+    for (int d = 0; d < 6; d++) box_next[o + d] = box[d];
+    box_next[o + 3 + dim] = fminf(split, box[3 + dim]);
+    begin_next[lchild - next_first] = begin;
+  }
+  if (lchild + 1 < n) {
+    const size_t o = (size_t)(lchild + 1 - next_first) * 6;
+#pragma unroll
+    for (int d = 0; d < 6; d++) box_next[o + d] = box[d];
+    box_next[o + dim] = fmaxf(split, box[dim]);
+    begin_next[lchild + 1 - next_first] = pivot + 1;
+  }
+}
+
+/* one thread per in-order position: classify the element found there in the split-axis list */
+__global__ void k_mark(int n, int level_first, const int* __restrict__ seg_of_pos, const int* __restrict__ seg_pivot,
+                       const uint8_t* __restrict__ seg_dim, const int* __restrict__ ord0, const int* __restrict__ ord1,
+                       const int* __restrict__ ord2, uint8_t* __restrict__ side, int* __restrict__ seg_next) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int s = seg_of_pos[i];
+  if (s == kDead) { seg_next[i] = kDead; return; }
+  const int j = s - level_first;
+  const int pivot = seg_pivot[j];
+  const int dim = seg_dim[j];
+  const int* ord = dim == 0 ? ord0 : (dim == 1 ? ord1 : ord2);
+  const int e = ord[i];
+  if (i < pivot) { side[e] = 0; seg_next[i] = 2 * s + 1; }
+  else if (i > pivot) { side[e] = 1; seg_next[i] = 2 * s + 2; }
+  else { side[e] = 2; seg_next[i] = kDead; }
+}
+
+/* packed (lefts | rights << 32) indicator of the element at position i of one list */
+struct SideFlagOp {
+  const int* ord; const uint8_t* side; const int* seg;
+  __device__ unsigned long long operator()(int i) const {
+    if (seg[i] == kDead) return 0ull;
+    const uint8_t sd = side[ord[i]];
+    return sd == 0 ? 1ull : (sd == 1 ? (1ull << 32) : 0ull);
+  }
+};
+
+/* stable partition of one list inside every subtree range, using the exclusive scan of the flags */
+__global__ void k_partition(int n, int level_first, const int* __restrict__ seg_of_pos,
+                            const int* __restrict__ seg_pivot, const int* __restrict__ begin_cur,
+                            const int* __restrict__ ord_in, const uint8_t* __restrict__ side,
+                            const unsigned long long* __restrict__ scan, int* __restrict__ ord_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int s = seg_of_pos[i];
+  if (s == kDead) return;
+  const int j = s - level_first;
+  const int begin = begin_cur[j];
+  const int pivot = seg_pivot[j];
+  const int e = ord_in[i];
+  const uint8_t sd = side[e];
+  const unsigned long long here = scan[i], base = scan[begin];
+  int dst;
+  if (sd == 0) dst = begin + (int)((uint32_t)here - (uint32_t)base);
+  else if (sd == 1) dst = pivot + 1 + (int)((uint32_t)(here >> 32) - (uint32_t)(base >> 32));
+  else dst = pivot;
+  ord_out[dst] = e;
+}
+
+/* final gather: node j <- element elem_of_node[j]; 11 threads per record so that both the random
+ * 44-byte read and the streaming write are full-width */
+__global__ void k_emit_nodes(int n, const int* __restrict__ elem_of_node, const uint8_t* __restrict__ dim_of_node,
+                             const uint32_t* __restrict__ src_words, uint32_t* __restrict__ dst_words) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t total = (int64_t)n * 11;
+  if (t >= total) return;
+  const int node = (int)(t / 11);
+  const int w = (int)(t - (int64_t)node * 11);
+  const int e = elem_of_node[node];
+  uint32_t v = src_words[(size_t)e * 11 + w];
+  if (w == 10) v = (v & 0x00FFFFFFu) | ((uint32_t)dim_of_node[node] << 24);  /* split_dim is byte 43 */
+  dst_words[t] = v;
+}
+
+/* query-side copies from a tree-ordered AoS array */
+__global__ void k_make_soa(int n, const pm_photon44* __restrict__ ph, float4* __restrict__ nodes4,
+                           float4* __restrict__ color4) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* p = reinterpret_cast<const float*>(ph) + (size_t)i * 11;
+  const uint32_t last = reinterpret_cast<const uint32_t*>(p)[10];
+  nodes4[i] = make_float4(p[0], p[1], p[2], __int_as_float((int)(last >> 24)));
+  color4[i] = make_float4(p[6], p[7], p[8], p[9]);
+}
+
+int make_soa(pm_ctx* ctx, pm_map* m) {
+  const int n = (int)m->n;
+  PM_CUDA(cudaMalloc(&m->nodes4, sizeof(float4) * (size_t)n));
+  PM_CUDA(cudaMalloc(&m->color4, sizeof(float4) * (size_t)n));
+  k_make_soa<<<(unsigned)pm::div_up(n, 256), 256, 0, ctx->stream>>>(n, m->photons_dev, m->nodes4, m->color4);
+  ctx->launches++;
+  PM_CUDA(cudaGetLastError());
+  return PM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_host, pm_map** out) {
+  PM_REQUIRE(ctx && out, "ctx/out is NULL");
+  *out = nullptr;
+  if (n64 < 1) return PM_OK; /* builder_thrust.h:441: "return gracefully" */
+  PM_REQUIRE(photons, "photons is NULL");
+  PM_REQUIRE(n64 < (int64_t)1 << 30, "at most 2^30 photons per map");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  const int n = (int)n64;
+  cudaStream_t st = ctx->stream;
+  const bool dev_in = pm::is_device_ptr(photons);
+
+  pm_map* m = new pm_map();
+  m->ctx = ctx; m->n = n;
+  pm_photon44* tree = nullptr;  /* destination, tree order */
+  if (dev_in) {
+    tree = photons;
+  } else {
+    if (cudaMalloc(&m->owned_photons, sizeof(pm_photon44) * (size_t)n) != cudaSuccess) {
+      cudaGetLastError(); delete m; pm::set_error("pm_map_build: out of device memory"); return PM_ERR_NOMEM;
+    }
+    tree = m->owned_photons;
+  }
+  m->photons_dev = tree;
+
+#define PM_B(call) do { int r__ = (call); if (r__ != PM_OK) { pm_map_destroy(m); return r__; } } while (0)
+#define PM_BC(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { pm::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); pm_map_destroy(m); return PM_ERR_CUDA; } } while (0)
+
+  /* unsorted copy of the input records (the gather source) */
+  pm_photon44* src = nullptr;
+  PM_B(ctx->get_scratch(pm::S_BUILD0, (size_t)n, &src));
+  PM_BC(cudaMemcpyAsync(src, photons, sizeof(pm_photon44) * (size_t)n, dev_in ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+
+  float *cx, *cy, *cz; uint32_t *keys_in, *keys_out; int *iota;
+  int* ord[2][3];
+  PM_B(ctx->get_scratch(pm::S_BUILD1, (size_t)n, &cx));
+  PM_B(ctx->get_scratch(pm::S_BUILD2, (size_t)n, &cy));
+  PM_B(ctx->get_scratch(pm::S_BUILD3, (size_t)n, &cz));
+  PM_B(ctx->get_scratch(pm::S_KEYS0, (size_t)n * 3, &keys_in));
+  PM_B(ctx->get_scratch(pm::S_KEYS1, (size_t)n, &keys_out));
+  PM_B(ctx->get_scratch(pm::S_VALS0, (size_t)n, &iota));
+  PM_B(ctx->get_scratch(pm::S_BUILD4, (size_t)n * 3, &ord[0][0]));
+  PM_B(ctx->get_scratch(pm::S_BUILD5, (size_t)n * 3, &ord[1][0]));
+  for (int b = 0; b < 2; b++) { ord[b][1] = ord[b][0] + n; ord[b][2] = ord[b][0] + 2 * (size_t)n; }
+
+  const unsigned nb256 = (unsigned)pm::div_up(n, 256);
+  k_extract<<<nb256, 256, 0, st>>>(src, n, cx, cy, cz, keys_in, keys_in + n, keys_in + 2 * (size_t)n, iota);
+  ctx->launches++;
+
+  /* three stable LSD radix sorts: ties keep ascending element index */
+  size_t cub_bytes = 0, scan_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys_in, keys_out, iota, ord[0][0], n, 0, 32, st);
+  {
+    SideFlagOp op{nullptr, nullptr, nullptr};
+    cub::TransformInputIterator<unsigned long long, SideFlagOp, cub::CountingInputIterator<int>> it(cub::CountingInputIterator<int>(0), op);
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, it, (unsigned long long*)nullptr, n, st);
+  }
+  void* cub_tmp = nullptr;
+  PM_B(ctx->get_scratch(pm::S_CUB, cub_bytes > scan_bytes ? cub_bytes : scan_bytes, &cub_tmp));
+  size_t cub_cap = cub_bytes > scan_bytes ? cub_bytes : scan_bytes;
+  for (int d = 0; d < 3; d++) {
+    size_t tb = cub_cap;
+    PM_BC(cub::DeviceRadixSort::SortPairs(cub_tmp, tb, keys_in + (size_t)d * n, keys_out, iota, ord[0][d], n, 0, 32, st));
+    ctx->launches += 5;
+  }
+
+  /* per-level state */
+  const int num_levels = 32 - __builtin_clz((unsigned)n);  /* floor(log2 n) + 1 */
+  const int max_width = (n + 1) / 2 + 1;
+  float* box[2]; int* begin[2]; int *seg_pivot, *seg[2], *elem_of_node; uint8_t *seg_dim, *side, *dim_of_node;
+  unsigned long long* scan;
+  PM_B(ctx->get_scratch(pm::S_BUILD6, (size_t)max_width * 6, &box[0]));
+  PM_B(ctx->get_scratch(pm::S_BUILD7, (size_t)max_width * 6, &box[1]));
+  PM_B(ctx->get_scratch(pm::S_BUILD8, (size_t)max_width, &begin[0]));
+  PM_B(ctx->get_scratch(pm::S_BUILD9, (size_t)max_width, &begin[1]));
+  PM_B(ctx->get_scratch(pm::S_BUILD10, (size_t)max_width, &seg_pivot));
+  PM_B(ctx->get_scratch(pm::S_BUILD11, (size_t)n * 2, &seg[0]));
+  seg[1] = seg[0] + n;
+  PM_B(ctx->get_scratch(pm::S_BUILD12, (size_t)n, &elem_of_node));
+  PM_B(ctx->get_scratch(pm::S_BUILD13, (size_t)max_width + 2 * (size_t)n, &seg_dim));
+  side = seg_dim + max_width; dim_of_node = side + n;
+  PM_B(ctx->get_scratch(pm::S_BUILD14, (size_t)n, &scan));
+  float* bounds_dev = nullptr;
+  PM_B(ctx->get_scratch(pm::S_BUILD15, (size_t)8, &bounds_dev));
+
+  k_root<<<1, 32, 0, st>>>(ord[0][0], ord[0][1], ord[0][2], cx, cy, cz, n, box[0], begin[0], bounds_dev);
+  ctx->launches++;
+  PM_BC(cudaMemsetAsync(seg[0], 0, sizeof(int) * (size_t)n, st)); /* everything starts in subtree 0 */
+
+  int cur = 0;
+  for (int L = 0; L < num_levels; L++) {
+    const int level_first = (1 << L) - 1;
+    const int level_count = (n - level_first < (1 << L)) ? n - level_first : (1 << L);
+    k_split<<<(unsigned)pm::div_up(level_count, 128), 128, 0, st>>>(
+        level_first, level_count, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
+        box[(L + 1) & 1], begin[(L + 1) & 1], seg_pivot, seg_dim, elem_of_node, dim_of_node);
+    ctx->launches++;
+    if (L == num_levels - 1) break;
+    k_mark<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, seg_dim, ord[cur][0], ord[cur][1], ord[cur][2],
+                                  side, seg[(L + 1) & 1]);
+    ctx->launches++;
+    for (int d = 0; d < 3; d++) {
+      SideFlagOp op{ord[cur][d], side, seg[L & 1]};
+      cub::TransformInputIterator<unsigned long long, SideFlagOp, cub::CountingInputIterator<int>> it(cub::CountingInputIterator<int>(0), op);
+      size_t tb = cub_cap;
+      PM_BC(cub::DeviceScan::ExclusiveSum(cub_tmp, tb, it, scan, n, st));
+      k_partition<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, begin[L & 1], ord[cur][d], side, scan,
+                                         ord[cur ^ 1][d]);
+      ctx->launches += 3;
+    }
+    cur ^= 1;
+  }
+
+  k_emit_nodes<<<(unsigned)pm::div_up((int64_t)n * 11, 256), 256, 0, st>>>(
+      n, elem_of_node, dim_of_node, reinterpret_cast<const uint32_t*>(src), reinterpret_cast<uint32_t*>(tree));
+  ctx->launches++;
+  PM_BC(cudaGetLastError());
+  PM_B(make_soa(ctx, m));
+  PM_BC(cudaMemcpyAsync(m->bounds, bounds_dev, sizeof(float) * 6, cudaMemcpyDeviceToHost, st));
+  if (!dev_in) PM_BC(cudaMemcpyAsync(photons, tree, sizeof(pm_photon44) * (size_t)n, cudaMemcpyDeviceToHost, st));
+  PM_BC(cudaStreamSynchronize(st));
+  if (bounds_host) memcpy(bounds_host, m->bounds, sizeof(float) * 6);
+#undef PM_B
+#undef PM_BC
+  *out = m;
+  return PM_OK;
+}
+
+int pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map** out) {
+  PM_REQUIRE(ctx && out, "ctx/out is NULL");
+  *out = nullptr;
+  if (n < 1) return PM_OK;
+  PM_REQUIRE(photons, "photons is NULL");
+  PM_REQUIRE(n < (int64_t)1 << 30, "at most 2^30 photons per map");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  pm_map* m = new pm_map();
+  m->ctx = ctx; m->n = n;
+  if (pm::is_device_ptr(photons)) {
+    m->photons_dev = photons;
+  } else {
+    if (cudaMalloc(&m->owned_photons, sizeof(pm_photon44) * (size_t)n) != cudaSuccess) {
+      cudaGetLastError(); delete m; pm::set_error("pm_map_from_tree: out of device memory"); return PM_ERR_NOMEM;
+    }
+    cudaMemcpyAsync(m->owned_photons, photons, sizeof(pm_photon44) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
+    m->photons_dev = m->owned_photons;
+  }
+  int r = make_soa(ctx, m);
+  if (r == PM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) { pm::set_error("pm_map_from_tree: sync failed"); r = PM_ERR_CUDA; }
+  if (r != PM_OK) { pm_map_destroy(m); return r; }
+  *out = m;
+  return PM_OK;
+}
+
+void pm_map_destroy(pm_map* m) {
+  if (!m) return;
+  if (m->ctx) { cudaSetDevice(m->ctx->device); cudaStreamSynchronize(m->ctx->stream); }
+  if (m->owned_photons) cudaFree(m->owned_photons);
+  if (m->nodes4) cudaFree(m->nodes4);
+  if (m->color4) cudaFree(m->color4);
+  delete m;
+}
+
+int64_t pm_map_size(const pm_map* m) { return m ? m->n : 0; }
+
+}  // extern "C"

@@ -1,0 +1,351 @@
+/* pm_knn.cu — stage 3: k-nearest-photon search and the fused radiance estimate.
+ *
+ * Replaces cukd::stackBased::knn<HeapCandidateList<k>> (externals/cudaKDTree/cukd/knn.h:298-364,
+ * 536-549; traverse-default-stack-based.h:24-90) as instantiated by
+ * ray-tracer/cuda/shading.h:11-18, and gatherPhotons (shading.h:93-121).
+ *
+ * Result contract: per query, the k smallest (floatBits(dist²), node id) pairs among
+ * nodes with dist² < cutoff²; dist² = fma(dz,dz, fma(dy,dy, dx*dx)), d = node - query.
+ *
+ * B200 design (v1):
+ *   - queries are Morton-sorted (30-bit code inside the map's AABB, radix sort of 4-byte ids) so the
+ *     32 lanes of a warp walk nearly the same root-to-leaf paths: node fetches coalesce into a few
+ *     sectors and the traversal stays convergent;
+ *   - the tree is traversed through a 16-byte (x, y, z, split_dim) copy — one LDG.128 per node
+ *     instead of a 44-byte-stride AoS access;
+ *   - the candidate heap lives in shared memory, laid out [slot][thread] so that every heap access
+ *     of a warp hits 32 distinct banks no matter which slot each lane touches (the reference's
+ *     per-thread uint64[k] array is dynamically indexed and therefore spills to local memory);
+ *     the heap root is mirrored in a register so the common "reject" case costs one compare.
+ */
+#include <cub/cub.cuh>
+#include <cfloat>
+#include "pm_internal.h"
+
+namespace {
+
+constexpr int kBlock = 128;
+
+__device__ __forceinline__ uint64_t encode(float d2, int id) {
+  return ((uint64_t)__float_as_uint(d2) << 32) | (uint32_t)id;
+}
+
+/* expands 10 bits into every third bit */
+__device__ __forceinline__ uint32_t part1by2(uint32_t v) {
+  v &= 0x3FFu;
+  v = (v | (v << 16)) & 0x030000FFu;
+  v = (v | (v << 8)) & 0x0300F00Fu;
+  v = (v | (v << 4)) & 0x030C30C3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+
+struct Box6 { float lo[3]; float inv[3]; };
+
+__global__ void k_morton(const float* __restrict__ q, int nq, Box6 box, uint32_t* __restrict__ keys, int* __restrict__ ids) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  uint32_t code = 0;
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    float t = (q[(size_t)i * 3 + d] - box.lo[d]) * box.inv[d];
+    t = fminf(fmaxf(t, 0.f), 1023.f);
+    code |= part1by2((uint32_t)t) << d;
+  }
+  keys[i] = code;
+  ids[i] = i;
+}
+
+/* Shared-memory max-heap of uint64 entries, one column per thread. */
+template <int K>
+struct SmemHeap {
+  uint64_t* col;  /* &heap[0][threadIdx.x]; slot s is col[s * kBlock] */
+  uint64_t top;   /* register mirror of slot 0 */
+
+  __device__ __forceinline__ void init(uint64_t* base, float cutoff2) {
+    col = base + threadIdx.x;
+    top = encode(cutoff2, -1);
+#pragma unroll 8
+    for (int s = 0; s < K; s++) col[s * kBlock] = top;
+  }
+  __device__ __forceinline__ float max_dist2() const { return __uint_as_float((uint32_t)(top >> 32)); }
+  /* cukd HeapCandidateList::push (knn.h:327-359): replace the root, sift down */
+  __device__ __forceinline__ void push(float d2, int id) {
+    const uint64_t e = encode(d2, id);
+    if (e >= top) return;
+    int pos = 0;
+    uint64_t new_top = e;
+    while (true) {
+      const int c0 = 2 * pos + 1;
+      if (c0 >= K) break;
+      uint64_t v = col[c0 * kBlock];
+      int c = c0;
+      if (c0 + 1 < K) {
+        const uint64_t v1 = col[(c0 + 1) * kBlock];
+        if (v1 > v) { v = v1; c = c0 + 1; }
+      }
+      if (v < e) break;
+      col[pos * kBlock] = v;
+      if (pos == 0) new_top = v;
+      pos = c;
+    }
+    col[pos * kBlock] = e;
+    top = new_top;
+  }
+};
+
+/* stack-based traversal, literal in its visiting order (traverse-default-stack-based.h:49-88) */
+template <int K>
+__device__ __forceinline__ void traverse(const float4* __restrict__ nodes, int n, float qx, float qy, float qz,
+                                         SmemHeap<K>& heap) {
+  struct Entry { int node; float d2; };
+  Entry stack[32];
+  int sp = 0;
+  int curr = 0;
+  float cull = heap.max_dist2();
+  while (true) {
+    while (curr < n) {
+      const float4 nd = __ldg(nodes + curr);
+      const int dim = __float_as_int(nd.w);
+      const float dx = nd.x - qx, dy = nd.y - qy, dz = nd.z - qz;
+      const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+      heap.push(d2, curr);
+      cull = heap.max_dist2();
+      const float dp = dim == 0 ? -dx : (dim == 1 ? -dy : -dz); /* query - node along the split axis */
+      const bool left_close = dp < 0.f;
+      const int l = 2 * curr + 1;
+      const int close_child = left_close ? l : l + 1;
+      const int far_child = left_close ? l + 1 : l;
+      const float plane2 = __fmul_rn(dp, dp);
+      if (plane2 < cull && far_child < n) { stack[sp].node = far_child; stack[sp].d2 = plane2; sp++; }
+      curr = close_child;
+    }
+    bool found = false;
+    while (sp > 0) {
+      --sp;
+      if (stack[sp].d2 >= cull) continue;
+      curr = stack[sp].node;
+      found = true;
+      break;
+    }
+    if (!found) return;
+  }
+}
+
+template <int K>
+__global__ void __launch_bounds__(kBlock)
+k_knn(const float4* __restrict__ nodes, int n, const float* __restrict__ queries, const int* __restrict__ perm, int nq,
+      float cutoff2, int32_t* __restrict__ out_ids, float* __restrict__ out_d2, float* __restrict__ out_r2) {
+  extern __shared__ uint64_t smem_heap[];
+  const int t = blockIdx.x * kBlock + threadIdx.x;
+  SmemHeap<K> heap;
+  heap.init(smem_heap, cutoff2);
+  if (t >= nq) return;
+  const int qi = perm ? perm[t] : t;
+  const float qx = queries[(size_t)qi * 3 + 0], qy = queries[(size_t)qi * 3 + 1], qz = queries[(size_t)qi * 3 + 2];
+  traverse<K>(nodes, n, qx, qy, qz, heap);
+  if (out_r2) out_r2[qi] = heap.max_dist2();
+  /* each thread streams its own row; K is even so rows are 8-byte aligned */
+  int2* ids2 = reinterpret_cast<int2*>(out_ids + (size_t)qi * K);
+  float2* d22 = out_d2 ? reinterpret_cast<float2*>(out_d2 + (size_t)qi * K) : nullptr;
+#pragma unroll 4
+  for (int s = 0; s < K; s += 2) {
+    const uint64_t a = heap.col[s * kBlock], b = heap.col[(s + 1) * kBlock];
+    ids2[s >> 1] = make_int2((int)(uint32_t)a, (int)(uint32_t)b);
+    if (d22) d22[s >> 1] = make_float2(__uint_as_float((uint32_t)(a >> 32)), __uint_as_float((uint32_t)(b >> 32)));
+  }
+}
+
+/* fused kNN + gatherPhotons (shading.h:93-121); arithmetic as written there, one rounding per op */
+template <int K>
+__global__ void __launch_bounds__(kBlock)
+k_gather(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n, const float* __restrict__ hit,
+         const float* __restrict__ brdf, const int* __restrict__ perm, int nq, float cutoff2, float* __restrict__ out_rgb) {
+  extern __shared__ uint64_t smem_heap[];
+  const int t = blockIdx.x * kBlock + threadIdx.x;
+  SmemHeap<K> heap;
+  heap.init(smem_heap, cutoff2);
+  if (t >= nq) return;
+  const int qi = perm ? perm[t] : t;
+  const float qx = hit[(size_t)qi * 3 + 0], qy = hit[(size_t)qi * 3 + 1], qz = hit[(size_t)qi * 3 + 2];
+  traverse<K>(nodes, n, qx, qy, qz, heap);
+  const float r2 = heap.max_dist2();
+  const float rad = __fsqrt_rn(r2);
+  const float f = brdf[qi];
+  float fr = 0.f, fg = 0.f, fb = 0.f;
+  for (int s = 0; s < K; s++) {
+    const int id = (int)(uint32_t)heap.col[s * kBlock];
+    if (id < 0 || id > n) continue; /* sic, shading.h:105 */
+    const float4 p = __ldg(nodes + id);
+    const float4 c = __ldg(color4 + id);
+    const float dx = p.x - qx, dy = p.y - qy, dz = p.z - qz;
+    const float dist = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+    const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
+    const float sc = __fmul_rn(__fmul_rn(f, c.w), w);
+    fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
+    fg = __fadd_rn(fg, __fmul_rn(sc, c.y));
+    fb = __fadd_rn(fb, __fmul_rn(sc, c.z));
+  }
+  const float k1 = (1 - (2.f / 3.f) * (1.f / 1.1f));
+  const float denom = __fmul_rn(__fmul_rn(__fmul_rn(k1, 2.f), 3.14159274101257324f), r2);
+  out_rgb[(size_t)qi * 3 + 0] = __fdiv_rn(fr, denom);
+  out_rgb[(size_t)qi * 3 + 1] = __fdiv_rn(fg, denom);
+  out_rgb[(size_t)qi * 3 + 2] = __fdiv_rn(fb, denom);
+}
+
+/* Morton order of the queries inside the map's box → permutation in scratch slot S_PERM */
+int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, int nq, int** perm_out) {
+  uint32_t *keys_in, *keys_out; int *ids_in, *perm;
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)nq, &keys_in));
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)nq, &keys_out));
+  PM_CHECK(ctx->get_scratch(pm::S_VALS0, (size_t)nq, &ids_in));
+  PM_CHECK(ctx->get_scratch(pm::S_PERM, (size_t)nq, &perm));
+  Box6 box;
+  for (int d = 0; d < 3; d++) {
+    box.lo[d] = map->bounds[d];
+    const float w = map->bounds[3 + d] - map->bounds[d];
+    box.inv[d] = w > 0.f ? 1024.f / w : 0.f;
+  }
+  k_morton<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(q_dev, nq, box, keys_in, ids_in);
+  size_t tb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_in, keys_out, ids_in, perm, nq, 0, 30, ctx->stream);
+  void* tmp = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_CUB, tb, &tmp));
+  PM_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, keys_in, keys_out, ids_in, perm, nq, 0, 30, ctx->stream));
+  ctx->launches += 5;
+  *perm_out = perm;
+  return PM_OK;
+}
+
+template <int K>
+int launch_knn(pm_ctx* ctx, const pm_map* map, const float* q, const int* perm, int nq, float cutoff2, int32_t* ids,
+               float* d2, float* r2) {
+  const size_t smem = sizeof(uint64_t) * K * kBlock;
+  PM_CUDA(cudaFuncSetAttribute(k_knn<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_knn<K><<<(unsigned)pm::div_up(nq, kBlock), kBlock, smem, ctx->stream>>>(map->nodes4, (int)map->n, q, perm, nq, cutoff2,
+                                                                          ids, d2, r2);
+  ctx->launches++;
+  PM_CUDA(cudaGetLastError());
+  return PM_OK;
+}
+
+template <int K>
+int launch_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, const int* perm, int nq,
+                  float cutoff2, float* rgb) {
+  const size_t smem = sizeof(uint64_t) * K * kBlock;
+  PM_CUDA(cudaFuncSetAttribute(k_gather<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_gather<K><<<(unsigned)pm::div_up(nq, kBlock), kBlock, smem, ctx->stream>>>(map->nodes4, map->color4, (int)map->n, hit,
+                                                                             brdf, perm, nq, cutoff2, rgb);
+  ctx->launches++;
+  PM_CUDA(cudaGetLastError());
+  return PM_OK;
+}
+
+__global__ void k_fill_empty(int64_t total, int32_t* ids, float* d2, float cutoff2) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  if (ids) ids[i] = -1;
+  if (d2) d2[i] = cutoff2;
+}
+__global__ void k_fill_f(int64_t total, float* p, float v) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < total) p[i] = v;
+}
+
+}  // namespace
+
+namespace pm {
+
+/* device-pointer entry used by pm_gather and by the render pipeline */
+int gather_device(pm_ctx* ctx, const pm_map* map, const float* hit_dev, const float* brdf_dev, int64_t nq, int k,
+                  float cutoff, float* rgb_dev, bool time_it) {
+  if (nq <= 0) return PM_OK;
+  if (!map || map->n < 1) {
+    k_fill_f<<<(unsigned)div_up(nq * 3, 256), 256, 0, ctx->stream>>>(nq * 3, rgb_dev, 0.f);
+    ctx->launches++;
+    return PM_OK;
+  }
+  const float cutoff2 = cutoff * cutoff;
+  int* perm = nullptr;
+  PM_CHECK(sort_queries(ctx, map, hit_dev, (int)nq, &perm));
+  if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+  int r;
+  switch (k) {
+    case 8: r = launch_gather<8>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
+    case 16: r = launch_gather<16>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
+    case 32: r = launch_gather<32>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
+    case 50: r = launch_gather<50>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
+    case 64: r = launch_gather<64>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
+    default: set_error("k must be one of 8, 16, 32, 50, 64 (got %d)", k); return PM_ERR_UNSUPPORTED;
+  }
+  if (time_it) PM_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  return r;
+}
+
+}  // namespace pm
+
+extern "C" {
+
+int pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int k, float cutoff_radius,
+           int32_t* out_ids, float* out_dist2, float* out_r2) {
+  PM_REQUIRE(ctx, "ctx is NULL");
+  PM_REQUIRE(nq >= 0 && nq < ((int64_t)1 << 31), "nq out of range");
+  PM_REQUIRE(k == 8 || k == 16 || k == 32 || k == 50 || k == 64, "k must be one of 8, 16, 32, 50, 64");
+  if (nq == 0) return PM_OK;
+  PM_REQUIRE(queries && out_ids, "queries/out_ids is NULL");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  const float cutoff2 = cutoff_radius * cutoff_radius;
+  const void* q_dev = nullptr;
+  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN0, queries, sizeof(float) * 3 * (size_t)nq, &q_dev));
+  pm::OutStage o_ids, o_d2, o_r2;
+  PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT0, out_ids, sizeof(int32_t) * (size_t)k * nq, &o_ids));
+  PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT1, out_dist2, sizeof(float) * (size_t)k * nq, &o_d2));
+  PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT2, out_r2, sizeof(float) * (size_t)nq, &o_r2));
+  if (!map || map->n < 1) {
+    k_fill_empty<<<(unsigned)pm::div_up(nq * k, 256), 256, 0, ctx->stream>>>(nq * k, (int32_t*)o_ids.dev, (float*)o_d2.dev, cutoff2);
+    if (o_r2.dev) k_fill_f<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(nq, (float*)o_r2.dev, cutoff2);
+    ctx->launches += 2;
+  } else {
+    int* perm = nullptr;
+    PM_CHECK(sort_queries(ctx, map, (const float*)q_dev, (int)nq, &perm));
+    PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+    int r;
+    switch (k) {
+      case 8: r = launch_knn<8>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
+      case 16: r = launch_knn<16>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
+      case 32: r = launch_knn<32>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
+      case 50: r = launch_knn<50>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
+      default: r = launch_knn<64>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
+    }
+    PM_CHECK(r);
+    PM_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  }
+  PM_CHECK(pm::stage_out_finish(ctx, o_ids));
+  PM_CHECK(pm::stage_out_finish(ctx, o_d2));
+  PM_CHECK(pm::stage_out_finish(ctx, o_r2));
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (map && map->n >= 1) PM_CUDA(cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev0, ctx->ev1));
+  return PM_OK;
+}
+
+int pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, int64_t nq, int k,
+              float cutoff_radius, float* out_rgb) {
+  PM_REQUIRE(ctx, "ctx is NULL");
+  PM_REQUIRE(nq >= 0 && nq < ((int64_t)1 << 31), "nq out of range");
+  PM_REQUIRE(k == 8 || k == 16 || k == 32 || k == 50 || k == 64, "k must be one of 8, 16, 32, 50, 64");
+  if (nq == 0) return PM_OK;
+  PM_REQUIRE(hit && brdf && out_rgb, "hit/brdf/out_rgb is NULL");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  const void *h_dev = nullptr, *b_dev = nullptr;
+  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN0, hit, sizeof(float) * 3 * (size_t)nq, &h_dev));
+  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN1, brdf, sizeof(float) * (size_t)nq, &b_dev));
+  pm::OutStage o;
+  PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT0, out_rgb, sizeof(float) * 3 * (size_t)nq, &o));
+  PM_CHECK(pm::gather_device(ctx, map, (const float*)h_dev, (const float*)b_dev, nq, k, cutoff_radius, (float*)o.dev, true));
+  PM_CHECK(pm::stage_out_finish(ctx, o));
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (map && map->n >= 1) PM_CUDA(cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev0, ctx->ev1));
+  return PM_OK;
+}
+
+}  // extern "C"
