@@ -9,7 +9,7 @@
  *
  * Canonical arithmetic (see DESIGN.md "Arithmetic contract"): IEEE-754 binary32, one rounding
  * per written operation, NO implicit contraction (compiled with -ffp-contract=off), except
- *   - kNN squared distance = fmaf(dz,dz, fmaf(dy,dy, dx*dx)) with d = node - query, which is what
+ *   - kNN squared distance = fmaf(dz,dz, fmaf(dx,dx, dy*dy)) with d = node - query, which is what
  *     nvcc emits for cukd's dot(d,d) (cukd/math.h:208-211, 250-251) under its default -fmad=true;
  *   - the sphere-sampling trigonometry (sinf/cosf/acosf in common/cuda/helpers.h:27-34) uses the
  *     polynomial kernels below instead of a libm, so that host and device agree to the bit.

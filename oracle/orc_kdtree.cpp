@@ -105,10 +105,12 @@ struct Heap {
   }
 };
 
-/* canonical squared distance, d = node - query (cukd/math.h:208-211) */
+/* canonical squared distance, d = node - query (cukd/math.h:208-211). The contraction order is
+ * the one nvcc 12.9 emits for cukd's dot(d,d) = (dx*dx + dy*dy) + dz*dz in the reference kernel
+ * (SASS of oracle/_ref: FMUL t,dy,dy ; FFMA t,dx,dx,t ; FFMA d2,dz,dz,t). */
 inline float sqr_dist(const float* p, const float* q) {
   const float dx = p[0] - q[0], dy = p[1] - q[1], dz = p[2] - q[2];
-  return fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+  return fmaf(dz, dz, fmaf(dx, dx, dy * dy));
 }
 
 /* traverse_default (cukd/traverse-default-stack-based.h:24-90) with explicit split dims */

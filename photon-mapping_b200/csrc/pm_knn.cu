@@ -5,7 +5,8 @@
  * ray-tracer/cuda/shading.h:11-18, and gatherPhotons (shading.h:93-121).
  *
  * Result contract: per query, the k smallest (floatBits(dist²), node id) pairs among
- * nodes with dist² < cutoff²; dist² = fma(dz,dz, fma(dy,dy, dx*dx)), d = node - query.
+ * nodes with dist² < cutoff²; dist² = fma(dz,dz, fma(dx,dx, dy*dy)), d = node - query
+ * (the contraction nvcc emits for cukd's dot(d,d) in the reference kernel).
  *
  * B200 design (v1):
  *   - queries are Morton-sorted (30-bit code inside the map's AABB, radix sort of 4-byte ids) so the
@@ -108,7 +109,7 @@ __device__ __forceinline__ void traverse(const float4* __restrict__ nodes, int n
       const float4 nd = __ldg(nodes + curr);
       const int dim = __float_as_int(nd.w);
       const float dx = nd.x - qx, dy = nd.y - qy, dz = nd.z - qz;
-      const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+      const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
       heap.push(d2, curr);
       cull = heap.max_dist2();
       const float dp = dim == 0 ? -dx : (dim == 1 ? -dy : -dz); /* query - node along the split axis */
