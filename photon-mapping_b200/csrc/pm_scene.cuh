@@ -1,0 +1,143 @@
+/* pm_scene.cuh — device-side scene view and BVH traversal (software replacement for optixTrace:
+ * photon-mapping/cuda/deviceCode.cu:27,40; ray-tracer/cuda/deviceCode.cu:29-41,70-85,129-141).
+ *
+ * Layout in HBM (all 16-byte records, read with LDG.128):
+ *   node  = 4 x float4  {c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y}
+ *                       {c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y}
+ *                       {c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z}
+ *                       {bits(child0), bits(child1), -, -}   child >= 0: inner node, < 0: leaf ~child
+ *   tri   = 3 x float4  {A.xyz, bits(global triangle id)} {B-A, bits(mesh id)} {C-A, -}
+ * Triangle slots are in BVH (Morton) order; the ids they carry are the caller's triangle ids.
+ *
+ * The ray/triangle test is the canonical one of oracle/orc_scene.cpp (Moeller-Trumbore, one rounding
+ * per operation, both orientations, tmin < t < tmax, closest t wins, ties -> lowest triangle id).
+ * Node boxes are padded (pm_scene.cu) and the slab test is NaN-safe, so the BVH only ever culls
+ * triangles the canonical test would reject as well.
+ */
+#pragma once
+#include "pm_internal.h"
+#include "pm_devmath.cuh"
+
+namespace pmd {
+
+constexpr int kNoChild = 0x7fffffff;
+constexpr int kStackDepth = 64;
+
+struct SceneView {
+  const float4* nodes;
+  const float4* tris;
+  const pm_material* mats;
+  int nt;
+};
+
+struct Hit { int prim; float t; int slot; };
+
+/* canonical triangle test; returns true and t on accept */
+__device__ __forceinline__ bool tri_test(const float4 a4, const float4 e14, const float4 e24, vec3 org, vec3 dir,
+                                         float tmin, float tmax, float* t_out) {
+  const vec3 A = v3(a4.x, a4.y, a4.z), e1 = v3(e14.x, e14.y, e14.z), e2 = v3(e24.x, e24.y, e24.z);
+  const vec3 p = cross(dir, e2);
+  const float det = dot(e1, p);
+  if (!(det != 0.f)) return false;
+  const float inv = __fdiv_rn(1.f, det);
+  const vec3 s = org - A;
+  const float u = dot(s, p) * inv;
+  if (!(u >= 0.f && u <= 1.f)) return false;
+  const vec3 q = cross(s, e1);
+  const float v = dot(dir, q) * inv;
+  if (!(v >= 0.f && u + v <= 1.f)) return false;
+  const float t = dot(e2, q) * inv;
+  if (!(t > tmin && t < tmax)) return false;
+  *t_out = t;
+  return true;
+}
+
+/* closest hit (ANY = false) or occlusion (ANY = true: returns at the first accepted triangle) */
+template <bool ANY>
+__device__ __forceinline__ Hit trace(const SceneView& sc, vec3 org, vec3 dir, float tmin, float tmax) {
+  Hit best{-1, tmax, -1};
+  if (sc.nt <= 0) return best;
+  const float ix = __fdiv_rn(1.f, dir.x), iy = __fdiv_rn(1.f, dir.y), iz = __fdiv_rn(1.f, dir.z);
+  int stack[kStackDepth];
+  int sp = 0;
+  int node = 0;
+  while (true) {
+    const float4 q0 = __ldg(sc.nodes + 4 * (size_t)node + 0);
+    const float4 q1 = __ldg(sc.nodes + 4 * (size_t)node + 1);
+    const float4 q2 = __ldg(sc.nodes + 4 * (size_t)node + 2);
+    const float4 q3 = __ldg(sc.nodes + 4 * (size_t)node + 3);
+    const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+    /* slabs; fminf/fmaxf drop the NaN of 0 * inf */
+    const float a0x = (q0.x - org.x) * ix, b0x = (q0.y - org.x) * ix;
+    const float a0y = (q0.z - org.y) * iy, b0y = (q0.w - org.y) * iy;
+    const float a0z = (q2.x - org.z) * iz, b0z = (q2.y - org.z) * iz;
+    const float a1x = (q1.x - org.x) * ix, b1x = (q1.y - org.x) * ix;
+    const float a1y = (q1.z - org.y) * iy, b1y = (q1.w - org.y) * iy;
+    const float a1z = (q2.z - org.z) * iz, b1z = (q2.w - org.z) * iz;
+    const float n0 = fmaxf(fmaxf(fminf(a0x, b0x), fminf(a0y, b0y)), fmaxf(fminf(a0z, b0z), tmin));
+    const float f0 = fminf(fminf(fmaxf(a0x, b0x), fmaxf(a0y, b0y)), fminf(fmaxf(a0z, b0z), best.t));
+    const float n1 = fmaxf(fmaxf(fminf(a1x, b1x), fminf(a1y, b1y)), fmaxf(fminf(a1z, b1z), tmin));
+    const float f1 = fminf(fminf(fmaxf(a1x, b1x), fmaxf(a1y, b1y)), fminf(fmaxf(a1z, b1z), best.t));
+    /* conservative: a couple of ulps of slack on the far side */
+    bool h0 = n0 <= f0 * 1.0000004f;
+    bool h1 = (n1 <= f1 * 1.0000004f) && c1 != kNoChild;
+    if (h0 && c0 < 0) {
+      const int slot = ~c0;
+      const float4 a4 = __ldg(sc.tris + 3 * (size_t)slot), e14 = __ldg(sc.tris + 3 * (size_t)slot + 1),
+                   e24 = __ldg(sc.tris + 3 * (size_t)slot + 2);
+      float t;
+      if (tri_test(a4, e14, e24, org, dir, tmin, tmax, &t)) {
+        const int id = __float_as_int(a4.w);
+        if (best.prim < 0 || t < best.t || (t == best.t && id < best.prim)) { best.prim = id; best.t = t; best.slot = slot; }
+        if (ANY) return best;
+      }
+      h0 = false;
+    }
+    if (h1 && c1 < 0) {
+      const int slot = ~c1;
+      const float4 a4 = __ldg(sc.tris + 3 * (size_t)slot), e14 = __ldg(sc.tris + 3 * (size_t)slot + 1),
+                   e24 = __ldg(sc.tris + 3 * (size_t)slot + 2);
+      float t;
+      if (tri_test(a4, e14, e24, org, dir, tmin, tmax, &t)) {
+        const int id = __float_as_int(a4.w);
+        if (best.prim < 0 || t < best.t || (t == best.t && id < best.prim)) { best.prim = id; best.t = t; best.slot = slot; }
+        if (ANY) return best;
+      }
+      h1 = false;
+    }
+    if (h0 && h1) {
+      const bool first0 = n0 <= n1;
+      if (sp < kStackDepth) stack[sp++] = first0 ? c1 : c0;
+      node = first0 ? c0 : c1;
+    } else if (h0) {
+      node = c0;
+    } else if (h1) {
+      node = c1;
+    } else {
+      if (sp == 0) break;
+      node = stack[--sp];
+    }
+  }
+  return best;
+}
+
+/* getPrimitiveNormal (common/cuda/helpers.h:76-85): normalize(cross(B-A, C-A)), never flipped */
+__device__ __forceinline__ vec3 slot_normal(const SceneView& sc, int slot) {
+  const float4 e14 = __ldg(sc.tris + 3 * (size_t)slot + 1), e24 = __ldg(sc.tris + 3 * (size_t)slot + 2);
+  return normalize(cross(v3(e14.x, e14.y, e14.z), v3(e24.x, e24.y, e24.z)));
+}
+__device__ __forceinline__ int slot_mesh(const SceneView& sc, int slot) {
+  return __float_as_int(__ldg(sc.tris + 3 * (size_t)slot + 1).w);
+}
+
+}  // namespace pmd
+
+/* host-side handle */
+struct pm_scene {
+  pm_ctx* ctx = nullptr;
+  int nt = 0, nv = 0, n_mesh = 0;
+  float4* nodes = nullptr;
+  float4* tris = nullptr;
+  pm_material* mats = nullptr;
+  pmd::SceneView view() const { return pmd::SceneView{nodes, tris, mats, nt}; }
+};

@@ -31,6 +31,7 @@ def load_oracle():
     L.orc_knn_brute.argtypes = [c_void_p, c_int, c_void_p, c_int, c_float, c_void_p, POINTER(c_int)]
     L.orc_knn_batch.argtypes = [c_void_p, c_int, c_void_p, c_int64, c_int, c_float, c_void_p, c_void_p, c_void_p, c_int]
     L.orc_gather_batch.argtypes = [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p, c_int]
+    declare_scene_oracle(L)
     return L
 
 
@@ -93,3 +94,93 @@ def entries(ids, d2):
     """(dist² bits << 32 | id) entries sorted per row — the canonical comparison form."""
     e = (d2.view(np.uint32).astype(np.uint64) << np.uint64(32)) | ids.view(np.uint32).astype(np.uint64)
     return np.sort(e, axis=1)
+
+
+# ---- scenes (stage 1 / 3) ---------------------------------------------------------------------
+MATERIAL = np.dtype(
+    [("albedo", "<f4", 3), ("diffuse", "<f4"), ("specular", "<f4"), ("transmission", "<f4"), ("refraction_idx", "<f4")]
+)
+LIGHT = np.dtype([("pos", "<f4", 3), ("rgb", "<f4", 3), ("power", "<f8")])
+RAY = np.dtype([("org", "<f4", 3), ("tmin", "<f4"), ("dir", "<f4", 3), ("tmax", "<f4")])
+HIT = np.dtype([("prim", "<i4"), ("t", "<f4")])
+
+
+def load_scene(name):
+    """Committed fixture extracted from the reference's assets by tests/golden/make_scenes.py."""
+    z = np.load(os.path.join(GOLDEN, f"scene_{name}.npz"))
+    return dict(verts=np.ascontiguousarray(z["verts"]), tris=np.ascontiguousarray(z["tris"]),
+                tri_mesh=np.ascontiguousarray(z["tri_mesh"]), mats=z["mats"].view(MATERIAL).reshape(-1).copy(),
+                lights=z["lights"].view(LIGHT).reshape(-1).copy(), names=list(z["names"]))
+
+
+def soup_scene(nt, seed, extent=10.0, size=1.5):
+    """Random triangle soup with 4 materials (diffuse / mirror / glass / mixed)."""
+    rng = np.random.default_rng(seed)
+    c = rng.random((nt, 1, 3), dtype=np.float32) * np.float32(extent)
+    verts = (c + (rng.random((nt, 3, 3), dtype=np.float32) - np.float32(0.5)) * np.float32(size)).reshape(-1, 3)
+    tris = np.arange(3 * nt, dtype=np.int32).reshape(nt, 3)
+    tri_mesh = rng.integers(0, 4, nt).astype(np.int32)
+    mats = np.zeros(4, MATERIAL)
+    mats[0] = ((0.7, 0.6, 0.5), 0.9, 0.0, 0.0, 1.0)
+    mats[1] = ((1.0, 1.0, 1.0), 0.0, 1.0, 0.0, 1.0)
+    mats[2] = ((0.8, 0.8, 1.0), 0.0, 0.2, 0.8, 1.5)
+    mats[3] = ((0.9, 0.9, 0.9), 0.5, 0.2, 0.2, 1.3)
+    lights = np.zeros(2, LIGHT)
+    lights[0] = ((extent * 0.5, extent * 0.5, extent * 0.5), (1, 1, 1), 10.0)
+    lights[1] = ((extent * 0.25, extent * 0.75, extent * 0.3), (1.0, 0.9, 0.8), 5.0)
+    return dict(verts=np.ascontiguousarray(verts, np.float32), tris=tris, tri_mesh=tri_mesh, mats=mats, lights=lights)
+
+
+def random_rays(n, seed, lo, hi, tmin=1e-3, tmax=1e30):
+    rng = np.random.default_rng(seed)
+    r = np.zeros(n, RAY)
+    lo, hi = np.asarray(lo, np.float32), np.asarray(hi, np.float32)
+    r["org"] = lo + rng.random((n, 3), dtype=np.float32) * (hi - lo)
+    d = rng.standard_normal((n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True).astype(np.float32)
+    # a share of axis-parallel directions (zero components: 0 * inf in the slab test)
+    ax = rng.integers(0, 8, n)
+    for k in range(3):
+        sel = ax == k
+        d[sel] = 0
+        d[sel, k] = np.where(rng.random(sel.sum()) < 0.5, -1, 1)
+    r["dir"] = d
+    r["tmin"], r["tmax"] = tmin, tmax
+    return r
+
+
+def declare_scene_oracle(L):
+    L.orc_trace_closest.argtypes = [c_void_p, c_int, c_void_p, c_int, c_void_p, c_int64, c_void_p]
+    L.orc_trace_occluded.argtypes = [c_void_p, c_int, c_void_p, c_int, c_void_p, c_int64, c_void_p]
+    L.orc_light_paths.restype = c_int64
+    L.orc_light_paths.argtypes = [c_void_p, c_int, c_int64, c_int]
+    L.orc_emit_photons.restype = c_int64
+    L.orc_emit_photons.argtypes = [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int64,
+                                   c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p, c_int64, POINTER(c_int64),
+                                   POINTER(c_int64)]
+    L.orc_photons_to_maps.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]
+    return L
+
+
+def oracle_trace(orc, sc, rays):
+    hits = np.empty(len(rays), HIT)
+    orc.orc_trace_closest(vp(sc["verts"]), len(sc["verts"]), vp(sc["tris"]), len(sc["tris"]), vp(rays), len(rays), vp(hits))
+    return hits
+
+
+def oracle_occluded(orc, sc, rays):
+    occ = np.empty(len(rays), np.uint8)
+    orc.orc_trace_occluded(vp(sc["verts"]), len(sc["verts"]), vp(sc["tris"]), len(sc["tris"]), vp(rays), len(rays), vp(occ))
+    return occ
+
+
+def oracle_emit(orc, sc, casted, max_depth, caustics, seed=0, rng_mode=0, first=0, stride=1, lights=None):
+    lights = sc["lights"] if lights is None else lights
+    cap = max(1, int(casted) * max(1, max_depth))
+    out = np.zeros(cap, PHOTON40)
+    npaths, nseg = c_int64(0), c_int64(0)
+    n = orc.orc_emit_photons(vp(sc["verts"]), len(sc["verts"]), vp(sc["tris"]), len(sc["tris"]), vp(sc["tri_mesh"]),
+                             vp(sc["mats"]), len(sc["mats"]), vp(lights), len(lights), casted, max_depth,
+                             1 if caustics else 0, seed, rng_mode, first, stride, vp(out), cap, ctypes.byref(npaths),
+                             ctypes.byref(nseg))
+    return out[:n].copy(), npaths.value, nseg.value

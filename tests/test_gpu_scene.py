@@ -1,0 +1,141 @@
+"""GPU parity tests for the scene BVH (hit ids bit-exact vs the brute-force oracle) and stage 1
+(photon emission + walk, byte-exact vs the oracle restatement of photon-mapping/cuda/deviceCode.cu)."""
+import numpy as np
+import pytest
+
+from helpers import (PHOTON40, PHOTON44, load_scene, oracle_emit, oracle_occluded, oracle_trace, random_rays,
+                     soup_scene, vp)
+
+pytestmark = pytest.mark.gpu
+
+
+def make_scene(pkg, ctx, sc):
+    return pkg.Scene(ctx, sc["verts"], sc["tris"], sc["tri_mesh"], sc["mats"])
+
+
+def scene_box(sc):
+    v = sc["verts"][sc["tris"].reshape(-1)]
+    return v.min(0), v.max(0)
+
+
+@pytest.mark.parametrize("name,nrays", [("cornell_box", 200000), ("sphere", 20000)])
+def test_trace_closest_matches_bruteforce_on_reference_assets(pkg, ctx, orc, name, nrays):
+    sc = load_scene(name)
+    s = make_scene(pkg, ctx, sc)
+    lo, hi = scene_box(sc)
+    rays = random_rays(nrays, 11, lo - 1, hi + 1)
+    # a block of rays leaving the light positions (what stage 1 actually shoots)
+    rays["org"][: nrays // 4] = sc["lights"]["pos"][0]
+    got = s.trace_closest(rays)
+    want = oracle_trace(orc, sc, rays)
+    assert (want["prim"] >= 0).mean() > 0.5
+    assert np.array_equal(got["prim"], want["prim"])            # hit ids bit-exact
+    assert got["t"].tobytes() == want["t"].tobytes()            # and so is t
+    occ = s.trace_occluded(rays)
+    assert np.array_equal(occ, oracle_occluded(orc, sc, rays))
+
+
+@pytest.mark.parametrize("nt", [1, 2, 3, 17, 1000, 20000])
+def test_trace_closest_soup(pkg, ctx, orc, nt):
+    sc = soup_scene(nt, nt)
+    s = make_scene(pkg, ctx, sc)
+    rays = random_rays(20000 if nt <= 1000 else 4000, nt + 1, [-1, -1, -1], [11, 11, 11])
+    rays["tmax"][::3] = 6.0   # finite tmax
+    got = s.trace_closest(rays)
+    want = oracle_trace(orc, sc, rays)
+    assert np.array_equal(got["prim"], want["prim"])
+    assert got["t"].tobytes() == want["t"].tobytes()
+    assert np.array_equal(s.trace_occluded(rays), oracle_occluded(orc, sc, rays))
+
+
+def test_trace_duplicate_triangles_tie_to_lowest_id(pkg, ctx, orc):
+    sc = soup_scene(50, 5)
+    # every triangle twice: identical t, the lower id must win
+    sc["verts"] = np.concatenate([sc["verts"], sc["verts"]])
+    sc["tris"] = np.concatenate([sc["tris"] + 150, sc["tris"]]).astype(np.int32)
+    sc["tri_mesh"] = np.concatenate([sc["tri_mesh"], sc["tri_mesh"]])
+    s = make_scene(pkg, ctx, sc)
+    rays = random_rays(20000, 6, [-1, -1, -1], [11, 11, 11])
+    got, want = s.trace_closest(rays), oracle_trace(orc, sc, rays)
+    assert (want["prim"] >= 0).sum() > 100 and (want["prim"][want["prim"] >= 0] < 50).all()
+    assert np.array_equal(got["prim"], want["prim"]) and got["t"].tobytes() == want["t"].tobytes()
+
+
+def test_empty_scene(pkg, ctx):
+    sc = soup_scene(1, 1)
+    s = pkg.Scene(ctx, np.zeros((0, 3), np.float32), np.zeros((0, 3), np.int32), np.zeros(0, np.int32), sc["mats"])
+    rays = random_rays(100, 1, [0, 0, 0], [1, 1, 1])
+    h = s.trace_closest(rays)
+    assert (h["prim"] == -1).all() and np.array_equal(h["t"], rays["tmax"])
+    ph, cnt, npaths, nseg = s.emit_photons(sc["lights"], 1000, 5, False)
+    assert cnt == 0 and npaths == 990 and nseg == 990   # int(1000/15)=66 per watt -> 660 + 330 paths, all miss
+
+
+@pytest.mark.parametrize("caustics", [False, True])
+@pytest.mark.parametrize("scene_name", ["cornell_box", "sphere", "soup"])
+def test_emit_matches_oracle_lcg(pkg, ctx, orc, scene_name, caustics):
+    sc = soup_scene(3000, 9, extent=6.0, size=2.5) if scene_name == "soup" else load_scene(scene_name)
+    casted, depth = (20000, 10) if scene_name != "sphere" else (3000, 6)
+    s = make_scene(pkg, ctx, sc)
+    got, cnt, npaths, nseg = s.emit_photons(sc["lights"], casted, depth, caustics)
+    want, o_paths, o_seg = oracle_emit(orc, sc, casted, depth, caustics)
+    assert (npaths, nseg) == (o_paths, o_seg)
+    assert cnt == len(want)
+    if scene_name == "cornell_box" and not caustics:
+        assert cnt > casted // 4          # the walk really stores photons
+    assert got.tobytes() == want.tobytes()    # same photons, same order, every byte
+
+
+def test_emit_counter_rng_and_sharding(pkg, ctx, orc):
+    sc = load_scene("cornell_box")
+    s = make_scene(pkg, ctx, sc)
+    full, cnt, npaths, nseg = s.emit_photons(sc["lights"], 10000, 8, False, seed=77, rng_mode=pkg.RNG_COUNTER)
+    want, o_paths, o_seg = oracle_emit(orc, sc, 10000, 8, False, seed=77, rng_mode=1)
+    assert full.tobytes() == want.tobytes() and (npaths, nseg) == (o_paths, o_seg)
+    other, _, _, _ = s.emit_photons(sc["lights"], 10000, 8, False, seed=78, rng_mode=pkg.RNG_COUNTER)
+    assert other.tobytes() != full.tobytes()
+    # shard by launch index over 3 ranks: the union is the full set, each shard matches the oracle
+    parts, paths = [], 0
+    for r in range(3):
+        p, c, npth, _ = s.emit_photons(sc["lights"], 10000, 8, False, seed=77, rng_mode=pkg.RNG_COUNTER,
+                                      first_photon=r, photon_stride=3)
+        w, _, _ = oracle_emit(orc, sc, 10000, 8, False, seed=77, rng_mode=1, first=r, stride=3)
+        assert p.tobytes() == w.tobytes()
+        parts.append(p.copy())
+        paths += npth
+    assert paths == npaths
+    allp = np.concatenate(parts)
+    assert sorted(allp.tobytes()[i:i + 40] for i in range(0, allp.nbytes, 40)) == \
+        sorted(full.tobytes()[i:i + 40] for i in range(0, full.nbytes, 40))
+
+
+def test_emit_capacity_and_device_output(pkg, ctx, orc):
+    import torch
+
+    sc = load_scene("cornell_box")
+    s = make_scene(pkg, ctx, sc)
+    want, _, _ = oracle_emit(orc, sc, 5000, 10, False)
+    with pytest.raises(pkg.PmError) as e:
+        s.emit_photons(sc["lights"], 5000, 10, False, capacity=100)
+    assert e.value.code == -5
+    d_out = torch.zeros(5000 * 10 * 40, dtype=torch.uint8, device="cuda")
+    _, cnt, _, _ = s.emit_photons(sc["lights"], 5000, 10, False, out=d_out, capacity=5000 * 10)
+    assert cnt == len(want)
+    assert d_out[: cnt * 40].cpu().numpy().tobytes() == want.tobytes()
+    # depth 1 stores nothing (i > 0 rule), depth 0 traces nothing
+    _, c1, _, s1 = s.emit_photons(sc["lights"], 5000, 1, False)
+    assert c1 == 0 and s1 == 5000
+    _, c0, _, s0 = s.emit_photons(sc["lights"], 5000, 0, False)
+    assert c0 == 0 and s0 == 0
+
+
+def test_photons_to_maps(pkg, ctx, orc):
+    sc = load_scene("cornell_box")
+    s = make_scene(pkg, ctx, sc)
+    g, _, _, _ = s.emit_photons(sc["lights"], 4000, 10, False)
+    c, _, _, _ = s.emit_photons(sc["lights"], 4000, 10, True)
+    og, oc = pkg.photons_to_maps(ctx, g, c)
+    wg, wc = np.zeros(len(g) + len(c), PHOTON44), np.zeros(len(c), PHOTON44)
+    orc.orc_photons_to_maps(vp(np.ascontiguousarray(g)), len(g), vp(np.ascontiguousarray(c)), len(c), vp(wg), vp(wc))
+    assert og.tobytes() == wg.tobytes() and oc.tobytes() == wc.tobytes()
+    assert (og["power"][: len(g)] == 1.0).all() and (og["power"][len(g):] == 0.5).all()
