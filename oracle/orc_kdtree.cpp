@@ -154,7 +154,11 @@ float knn_traverse(const pm_photon44* nodes, int n, const float q[3], int k, flo
   return heap.maxRadius2();
 }
 
-/* gatherPhotons (ray-tracer/cuda/shading.h:93-121), slots visited in heap-array order */
+}  // namespace
+
+namespace orc {
+/* gatherPhotons (ray-tracer/cuda/shading.h:93-121), slots visited in heap-array order.
+ * Also used by orc_render.cpp. */
 void gather_one(const pm_photon44* nodes, int n, const float hit[3], float brdf, int k, float cutoff,
                 uint64_t* heap_mem, float out[3]) {
   const float r2 = knn_traverse(nodes, n, hit, k, cutoff, heap_mem, nullptr);
@@ -173,8 +177,7 @@ void gather_one(const pm_photon44* nodes, int n, const float hit[3], float brdf,
   const vec3 res = flux / denom;
   out[0] = res.x; out[1] = res.y; out[2] = res.z;
 }
-
-}  // namespace
+}  // namespace orc
 
 extern "C" {
 

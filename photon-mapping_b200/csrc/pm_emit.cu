@@ -226,12 +226,11 @@ int pm_emit_photons(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, 
   if (batch > (int64_t)1 << 30) batch = (int64_t)1 << 30;
   if (batch < 1) batch = 1;
 
-  pm_photon40* slots; int* counts; int64_t* offsets; unsigned long long* ctrs; int64_t* totals_dev;
+  pm_photon40* slots; int* counts; int64_t* offsets; unsigned long long* ctrs;
   PM_CHECK(ctx->get_scratch(pm::S_BUILD0, (size_t)batch * P.slots_per_path, &slots));
   PM_CHECK(ctx->get_scratch(pm::S_BUILD1, (size_t)batch + 1, &counts));
   PM_CHECK(ctx->get_scratch(pm::S_BUILD2, (size_t)batch + 1, &offsets));
   PM_CHECK(ctx->get_scratch(pm::S_MISC0, (size_t)4, &ctrs));
-  totals_dev = reinterpret_cast<int64_t*>(ctrs + 2);
   size_t scan_bytes = 0;
   {
     CountToI64 op{counts};

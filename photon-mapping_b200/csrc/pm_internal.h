@@ -95,7 +95,8 @@ int stage_out_finish(pm_ctx* ctx, const OutStage& st);
 /* the photon map: tree-ordered AoS records (what the reference hands to its kernels) plus the
  * query-side SoA copies this library traverses */
 struct pm_map {
-  pm_ctx* ctx = nullptr;
+  pm_ctx* ctx = nullptr;   /* creator; never dereferenced on destroy (it may be gone already) */
+  int device = 0;
   int64_t n = 0;
   const pm_photon44* photons_dev = nullptr;  /* tree order; may alias caller memory */
   pm_photon44* owned_photons = nullptr;      /* set if the map owns the AoS copy */
@@ -103,3 +104,10 @@ struct pm_map {
   float4* color4 = nullptr;                  /* (r, g, b, power) per node */
   float bounds[6] = {0, 0, 0, 0, 0, 0};
 };
+
+namespace pm {
+/* pm_knn.cu: fused kNN + radiance estimate on device pointers (used by pm_gather and pm_render).
+ * Queries whose brdf is not > 0 are not evaluated and yield (0,0,0). */
+int gather_device(pm_ctx* ctx, const pm_map* map, const float* hit_dev, const float* brdf_dev, int64_t nq, int k,
+                  float cutoff, float* rgb_dev, bool time_it);
+}  // namespace pm

@@ -223,7 +223,7 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   const bool dev_in = pm::is_device_ptr(photons);
 
   pm_map* m = new pm_map();
-  m->ctx = ctx; m->n = n;
+  m->ctx = ctx; m->device = ctx->device; m->n = n;
   pm_photon44* tree = nullptr;  /* destination, tree order */
   if (dev_in) {
     tree = photons;
@@ -346,7 +346,7 @@ int pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map*
   PM_REQUIRE(n < (int64_t)1 << 30, "at most 2^30 photons per map");
   PM_CUDA(cudaSetDevice(ctx->device));
   pm_map* m = new pm_map();
-  m->ctx = ctx; m->n = n;
+  m->ctx = ctx; m->device = ctx->device; m->n = n;
   if (pm::is_device_ptr(photons)) {
     m->photons_dev = photons;
   } else {
@@ -365,7 +365,8 @@ int pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map*
 
 void pm_map_destroy(pm_map* m) {
   if (!m) return;
-  if (m->ctx) { cudaSetDevice(m->ctx->device); cudaStreamSynchronize(m->ctx->stream); }
+  cudaSetDevice(m->device);
+  cudaDeviceSynchronize();
   if (m->owned_photons) cudaFree(m->owned_photons);
   if (m->nodes4) cudaFree(m->nodes4);
   if (m->color4) cudaFree(m->color4);

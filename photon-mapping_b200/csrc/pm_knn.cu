@@ -43,9 +43,13 @@ __device__ __forceinline__ uint32_t part1by2(uint32_t v) {
 
 struct Box6 { float lo[3]; float inv[3]; };
 
-__global__ void k_morton(const float* __restrict__ q, int nq, Box6 box, uint32_t* __restrict__ keys, int* __restrict__ ids) {
+__global__ void k_morton(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int nq, Box6 box,
+                         uint32_t* __restrict__ keys, int* __restrict__ ids) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nq) return;
+  ids[i] = i;
+  /* queries that will not be evaluated (brdf <= 0) sort to the end so that whole warps retire at once */
+  if (skip_if_not_positive && !(skip_if_not_positive[i] > 0.f)) { keys[i] = 0x3FFFFFFFu; return; }
   uint32_t code = 0;
 #pragma unroll
   for (int d = 0; d < 3; d++) {
@@ -54,7 +58,6 @@ __global__ void k_morton(const float* __restrict__ q, int nq, Box6 box, uint32_t
     code |= part1by2((uint32_t)t) << d;
   }
   keys[i] = code;
-  ids[i] = i;
 }
 
 /* Shared-memory max-heap of uint64 entries, one column per thread. */
@@ -168,11 +171,15 @@ k_gather(const float4* __restrict__ nodes, const float4* __restrict__ color4, in
   heap.init(smem_heap, cutoff2);
   if (t >= nq) return;
   const int qi = perm ? perm[t] : t;
+  const float f = brdf[qi];
+  if (!(f > 0.f)) { /* flux = brdf * ... is +0 for brdf == 0; negative marks "no query" (render pipeline) */
+    out_rgb[(size_t)qi * 3 + 0] = 0.f; out_rgb[(size_t)qi * 3 + 1] = 0.f; out_rgb[(size_t)qi * 3 + 2] = 0.f;
+    return;
+  }
   const float qx = hit[(size_t)qi * 3 + 0], qy = hit[(size_t)qi * 3 + 1], qz = hit[(size_t)qi * 3 + 2];
   traverse<K>(nodes, n, qx, qy, qz, heap);
   const float r2 = heap.max_dist2();
   const float rad = __fsqrt_rn(r2);
-  const float f = brdf[qi];
   float fr = 0.f, fg = 0.f, fb = 0.f;
   for (int s = 0; s < K; s++) {
     const int id = (int)(uint32_t)heap.col[s * kBlock];
@@ -195,7 +202,7 @@ k_gather(const float4* __restrict__ nodes, const float4* __restrict__ color4, in
 }
 
 /* Morton order of the queries inside the map's box → permutation in scratch slot S_PERM */
-int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, int nq, int** perm_out) {
+int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float* brdf_dev, int nq, int** perm_out) {
   uint32_t *keys_in, *keys_out; int *ids_in, *perm;
   PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)nq, &keys_in));
   PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)nq, &keys_out));
@@ -207,7 +214,7 @@ int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, int nq, int
     const float w = map->bounds[3 + d] - map->bounds[d];
     box.inv[d] = w > 0.f ? 1024.f / w : 0.f;
   }
-  k_morton<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(q_dev, nq, box, keys_in, ids_in);
+  k_morton<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, keys_in, ids_in);
   size_t tb = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_in, keys_out, ids_in, perm, nq, 0, 30, ctx->stream);
   void* tmp = nullptr;
@@ -268,7 +275,7 @@ int gather_device(pm_ctx* ctx, const pm_map* map, const float* hit_dev, const fl
   }
   const float cutoff2 = cutoff * cutoff;
   int* perm = nullptr;
-  PM_CHECK(sort_queries(ctx, map, hit_dev, (int)nq, &perm));
+  PM_CHECK(sort_queries(ctx, map, hit_dev, brdf_dev, (int)nq, &perm));
   if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   int r;
   switch (k) {
@@ -308,7 +315,7 @@ int pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int
     ctx->launches += 2;
   } else {
     int* perm = nullptr;
-    PM_CHECK(sort_queries(ctx, map, (const float*)q_dev, (int)nq, &perm));
+    PM_CHECK(sort_queries(ctx, map, (const float*)q_dev, nullptr, (int)nq, &perm));
     PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
     int r;
     switch (k) {

@@ -178,7 +178,7 @@ int pm_scene_create(pm_ctx* ctx, const float* verts_host, int nv, const int32_t*
   PM_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
   pm_scene* s = new pm_scene();
-  s->ctx = ctx; s->nt = nt; s->nv = nv; s->n_mesh = n_mesh;
+  s->ctx = ctx; s->device = ctx->device; s->nt = nt; s->nv = nv; s->n_mesh = n_mesh;
 #define PM_S(call) do { int r__ = (call); if (r__ != PM_OK) { pm_scene_destroy(s); return r__; } } while (0)
 #define PM_SC(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { pm::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); pm_scene_destroy(s); return PM_ERR_CUDA; } } while (0)
   if (n_mesh > 0 && mats_host) {
@@ -253,7 +253,8 @@ int pm_scene_create(pm_ctx* ctx, const float* verts_host, int nv, const int32_t*
 
 void pm_scene_destroy(pm_scene* s) {
   if (!s) return;
-  if (s->ctx) { cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream); }
+  cudaSetDevice(s->device);
+  cudaDeviceSynchronize();
   if (s->nodes) cudaFree(s->nodes);
   if (s->tris) cudaFree(s->tris);
   if (s->mats) cudaFree(s->mats);

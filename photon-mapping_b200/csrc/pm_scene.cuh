@@ -134,7 +134,8 @@ __device__ __forceinline__ int slot_mesh(const SceneView& sc, int slot) {
 
 /* host-side handle */
 struct pm_scene {
-  pm_ctx* ctx = nullptr;
+  pm_ctx* ctx = nullptr;   /* creator; never dereferenced on destroy (it may be gone already) */
+  int device = 0;
   int nt = 0, nv = 0, n_mesh = 0;
   float4* nodes = nullptr;
   float4* tris = nullptr;

@@ -184,3 +184,32 @@ def oracle_emit(orc, sc, casted, max_depth, caustics, seed=0, rng_mode=0, first=
                              1 if caustics else 0, seed, rng_mode, first, stride, vp(out), cap, ctypes.byref(npaths),
                              ctypes.byref(nseg))
     return out[:n].copy(), npaths.value, nseg.value
+
+
+# ---- stage 3 (camera pass) --------------------------------------------------------------------
+CAMERA = np.dtype([("pos", "<f4", 3), ("dir_00", "<f4", 3), ("dir_du", "<f4", 3), ("dir_dv", "<f4", 3)])
+
+
+def declare_render_oracle(L):
+    L.orc_make_rgba.restype = c_uint32
+    L.orc_make_rgba.argtypes = [c_float, c_float, c_float]
+    L.orc_render.argtypes = [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int,
+                             c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_int64, c_void_p,
+                             c_void_p]
+    return L
+
+
+def oracle_render(orc, sc, gmap, cmap, cam, W, H, spp, depth, sky=(1, 1, 1), begin=0, end=None, fb=None):
+    """gmap / cmap: tree-ordered PHOTON44 arrays (or None)."""
+    declare_render_oracle(orc)
+    end = W * H if end is None else end
+    fb = np.zeros((H, W), np.uint32) if fb is None else fb
+    rgb = np.zeros((W * H, 3), np.float32)
+    sky = np.asarray(sky, np.float32)
+    cam = np.ascontiguousarray(cam, CAMERA)
+    orc.orc_render(vp(sc["verts"]), len(sc["verts"]), vp(sc["tris"]), len(sc["tris"]), vp(sc["tri_mesh"]), vp(sc["mats"]),
+                   len(sc["mats"]), vp(sc["lights"]), len(sc["lights"]),
+                   vp(gmap) if gmap is not None and len(gmap) else None, 0 if gmap is None else len(gmap),
+                   vp(cmap) if cmap is not None and len(cmap) else None, 0 if cmap is None else len(cmap),
+                   vp(cam), W, H, spp, depth, vp(sky), begin, end, vp(fb), vp(rgb))
+    return fb, rgb
