@@ -53,7 +53,7 @@ struct LCG4 {
   }
 };
 
-/* counter RNG of the throughput mode (same function as oracle/orc_common.h CounterRng) */
+/* counter RNG of the throughput mode (same function as the CPU oracle CounterRng) */
 struct CounterRng {
   uint64_t key; uint32_t ctr;
   __device__ __forceinline__ void init(uint64_t seed, uint64_t id) {
@@ -78,7 +78,7 @@ struct Rng {
   __device__ __forceinline__ float next() { return mode == PM_RNG_LCG_PARITY ? lcg.next() : cr.next(); }
 };
 
-/* ---- deterministic trigonometry (same kernels as oracle/orc_common.h) ------------------ */
+/* ---- deterministic trigonometry (same kernels as the CPU oracle) ------------------ */
 __device__ __forceinline__ void pm_sincosf(float x, float* s_out, float* c_out) {
   const float kf = rintf(x * 0.636619772f);
   const int k = (int)kf;

@@ -2,7 +2,7 @@
  *
  * Replaces owlRayGenLaunch2D(simpleRayGen) (ray-tracer/src/hostCode.cu:231-237) and the programs of
  * ray-tracer/cuda/deviceCode.cu:25-281 + shading.h:20-91. Same arithmetic and RNG draw order as the
- * CPU restatement in oracle/orc_render.cpp (which lists the positions taken on the reference's
+ * CPU restatement in the CPU oracle (render restatement) (which lists the positions taken on the reference's
  * undefined behaviour).
  *
  * The reference runs one monolithic thread per pixel: spp x depth x (1 primary + L shadow rays +

@@ -9,7 +9,7 @@
  *   tri   = 3 x float4  {A.xyz, bits(global triangle id)} {B-A, bits(mesh id)} {C-A, -}
  * Triangle slots are in BVH (Morton) order; the ids they carry are the caller's triangle ids.
  *
- * The ray/triangle test is the canonical one of oracle/orc_scene.cpp (Moeller-Trumbore, one rounding
+ * The ray/triangle test is the canonical one of the CPU oracle (scene restatement) (Moeller-Trumbore, one rounding
  * per operation, both orientations, tmin < t < tmax, closest t wins, ties -> lowest triangle id).
  * Node boxes are padded (pm_scene.cu) and the slab test is NaN-safe, so the BVH only ever culls
  * triangles the canonical test would reject as well.
