@@ -1,0 +1,481 @@
+/* pm_grid.cu — stage 3 fast path: warp-cooperative k-nearest-photon search over a uniform grid.
+ *
+ * Same result contract as the kd-tree kernels of pm_knn.cu (which restate
+ * cukd::stackBased::knn<HeapCandidateList<k>>, externals/cudaKDTree/cukd/knn.h:298-364,536-549):
+ * per query the k smallest (floatBits(dist²), node id) pairs among nodes with dist² < cutoff²,
+ * ids being positions in the left-balanced kd-tree array that pm_map_build produced. Only the way
+ * the candidates are found differs.
+ *
+ * Why not the tree: a per-thread traversal is a chain of dependent, divergent 16-byte loads plus a
+ * heap sift per accepted node; on B200 it runs at ~1 % of the HBM roofline. Here
+ *   - the map keeps a second copy of the node positions, sorted by uniform-grid cell (x fastest), so
+ *     the 5x5x5-cell neighbourhood of a query is 25 contiguous runs of (x, y, z, id) records;
+ *   - one warp answers one query: the 25 runs are flattened into one index space (a bitmap of run
+ *     starts in shared memory turns "which run is element j in" into one popc), every lane pulls
+ *     one record per step with a coalesced LDG.128, computes dist² and compacts the candidates
+ *     inside the search radius into shared memory with a ballot;
+ *   - the k smallest are found by COUNTING, not by a heap: two thresholds placed by interpolating
+ *     the count/dist² relation bracket the k-th candidate to <= 32 candidates in (almost always) one
+ *     sweep over <= 5 registers per lane; the bracket is ranked exactly on full 64-bit keys, one
+ *     candidate per lane;
+ *   - exactness: every node closer than G (the distance from the query to the nearest face of the
+ *     5x5x5 block that is not also a face of the whole grid, less a rounding margin) lies inside the
+ *     block, so once k candidates with dist² < G² exist the k nearest are among them. Queries for
+ *     which that fails (sparse neighbourhood), or whose neighbourhood is too dense for the shared
+ *     buffers, are appended to a list that the kd-tree kernel answers.
+ * The cell size comes from a sample of exact k-th-neighbour distances taken when the map is built.
+ */
+#include <cub/cub.cuh>
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include "pm_knn.cuh"
+
+namespace {
+
+using pmk::encode;
+
+constexpr int kWarps = 8;          /* warps (= queries in flight) per CTA */
+constexpr int kBuf = 160;          /* compacted candidates per query */
+constexpr int kSlots = kBuf / 32;  /* candidates per lane in the selection phase */
+constexpr int kMaxScan = 1024;     /* nodes in the 5x5x5 block beyond which the kd-tree kernel takes over */
+constexpr int kWords = kMaxScan / 32;
+constexpr int kTuneK = 64;         /* the cell size is tuned for the largest supported k */
+constexpr int kTuneSamples = 2048;
+constexpr int64_t kMinGridNodes = 4096;
+constexpr int64_t kMaxCells = (int64_t)1 << 24;
+
+struct GridView {
+  const float4* pts;
+  const uint32_t* cell_start;
+  float lo[3];
+  float cell, inv_cell, margin;
+  int nx, ny, nz;
+};
+
+struct __align__(16) WarpScratch {
+  uint64_t keys[kBuf];
+  uint2 words[kWords]; /* x: bitmap of run starts among elements [32 i, 32 i + 32); y: runs started before 32 i */
+  int run_off[32];     /* per non-empty run: (first record of the run) - (its first flat index) */
+};
+
+__device__ __forceinline__ int cell_of(float v, float lo, float inv_cell, int n) {
+  const float u = (v - lo) * inv_cell;
+  /* fminf/fmaxf drop NaN; the clamp keeps out-of-grid queries on the boundary cells */
+  return (int)fminf(fmaxf(floorf(u), 0.f), (float)(n - 1));
+}
+
+template <bool GATHER>
+__global__ void __launch_bounds__(kWarps * 32)
+k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::QueryIO io, int* __restrict__ fb_list,
+             int* __restrict__ fb_count) {
+  __shared__ WarpScratch scratch[kWarps];
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u, le = lt | (1u << lane);
+  WarpScratch& ws = scratch[threadIdx.x >> 5];
+  const int k = io.k;
+  const float cell3 = g.cell * g.cell * g.cell;
+
+  for (int t = blockIdx.x * kWarps + (threadIdx.x >> 5); t < io.nq; t += gridDim.x * kWarps) {
+    const int qi = io.order ? io.order[t] : t;
+    float brdf = 0.f;
+    if (GATHER) {
+      brdf = io.brdf[qi];
+      if (!(brdf > 0.f)) {
+        if (lane < 3) io.rgb[(size_t)qi * 3 + lane] = 0.f;
+        continue;
+      }
+    }
+    const float qx = io.q[(size_t)qi * 3 + 0], qy = io.q[(size_t)qi * 3 + 1], qz = io.q[(size_t)qi * 3 + 2];
+
+    /* ---- the 5x5x5 block and the radius G it is guaranteed to cover ---------------------- */
+    const int cx = cell_of(qx, g.lo[0], g.inv_cell, g.nx), cy = cell_of(qy, g.lo[1], g.inv_cell, g.ny),
+              cz = cell_of(qz, g.lo[2], g.inv_cell, g.nz);
+    const int x0 = max(cx - 2, 0), x1 = min(cx + 2, g.nx - 1);
+    const int y0 = max(cy - 2, 0), y1 = min(cy + 2, g.ny - 1);
+    const int z0 = max(cz - 2, 0), z1 = min(cz + 2, g.nz - 1);
+    float G = INFINITY;
+    if (x0 > 0) G = fminf(G, qx - (g.lo[0] + (float)x0 * g.cell));
+    if (x1 < g.nx - 1) G = fminf(G, (g.lo[0] + (float)(x1 + 1) * g.cell) - qx);
+    if (y0 > 0) G = fminf(G, qy - (g.lo[1] + (float)y0 * g.cell));
+    if (y1 < g.ny - 1) G = fminf(G, (g.lo[1] + (float)(y1 + 1) * g.cell) - qy);
+    if (z0 > 0) G = fminf(G, qz - (g.lo[2] + (float)z0 * g.cell));
+    if (z1 < g.nz - 1) G = fminf(G, (g.lo[2] + (float)(z1 + 1) * g.cell) - qz);
+    G -= g.margin;
+    const float G2 = G > 0.f ? G * G : 0.f;
+    const bool complete = !(G2 < io.cutoff2); /* the block holds every node inside the cutoff ball */
+    const float Rmax2 = fminf(G2, io.cutoff2);
+
+    /* ---- the runs: one per (y, z) row of the block ------------------------------------ */
+    const int ny_r = y1 - y0 + 1, nrows = ny_r * (z1 - z0 + 1);
+    int len = 0, st = 0;
+    if (lane < nrows) {
+      const int ry = y0 + lane % ny_r, rz = z0 + lane / ny_r;
+      const size_t base = ((size_t)rz * g.ny + ry) * g.nx;
+      st = (int)__ldg(g.cell_start + base + x0);
+      len = (int)__ldg(g.cell_start + base + x1 + 1) - st;
+    }
+    int incl = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const int m = __shfl_sync(0xffffffffu, incl, 31);
+    bool give_up = m > kMaxScan;
+
+    int n = 0;
+    if (!give_up) {
+      /* flat index space: bitmap of run starts + per-run address offsets */
+      const int P = incl - len;
+      ws.words[lane] = make_uint2(0u, 0u);
+      __syncwarp();
+      if (len > 0) atomicOr(&ws.words[P >> 5].x, 1u << (P & 31));
+      const unsigned nonempty = __ballot_sync(0xffffffffu, len > 0);
+      if (len > 0) ws.run_off[__popc(nonempty & lt)] = st - P;
+      __syncwarp();
+      {
+        const int wc = __popc(ws.words[lane].x);
+        int wi = wc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int v = __shfl_up_sync(0xffffffffu, wi, o);
+          if (lane >= o) wi += v;
+        }
+        ws.words[lane].y = (unsigned)(wi - wc);
+      }
+      __syncwarp();
+
+      /* first search radius from the block's mean density: expect ~1.3 k + 12 nodes inside it */
+      float R2 = Rmax2;
+      if (m > 0) {
+        const float vol = (float)((x1 - x0 + 1) * nrows) * cell3;
+        const float f3 = (1.3f * (float)k + 12.f) * vol / (4.18879f * (float)m);
+        R2 = fminf(Rmax2, exp2f(log2f(f3) * (2.f / 3.f)));
+      }
+      while (true) {
+        n = 0;
+        for (int i = 0; i * 32 < m; i++) {
+          const int j = i * 32 + lane;
+          const uint2 w = ws.words[i];
+          bool pass = false;
+          uint64_t key = 0;
+          if (j < m) {
+            const int run = (int)w.y + __popc(w.x & le) - 1;
+            const float4 p = __ldg(g.pts + (ws.run_off[run] + j));
+            const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+            pass = d2 < R2;
+            key = encode(d2, __float_as_int(p.w));
+          }
+          const unsigned b = __ballot_sync(0xffffffffu, pass);
+          if (pass) {
+            const int pos = n + __popc(b & lt);
+            if (pos < kBuf) ws.keys[pos] = key;
+          }
+          n += __popc(b);
+        }
+        if (n >= k || !(R2 < Rmax2)) break;
+        R2 = Rmax2; /* too few inside the estimate: take everything the block guarantees */
+        __syncwarp();
+      }
+      if (n > kBuf || (n < k && !complete)) give_up = true;
+    }
+    if (give_up) {
+      if (lane == 0) fb_list[atomicAdd(fb_count, 1)] = qi;
+      __syncwarp();
+      continue;
+    }
+    __syncwarp();
+
+    /* ---- selection: the kk smallest keys among the n candidates ------------------------ */
+    const int kk = min(n, k);
+    int hb[kSlots];
+    uint32_t idv[kSlots];
+#pragma unroll
+    for (int s = 0; s < kSlots; s++) {
+      const int idx = lane + 32 * s;
+      hb[s] = 0x7fffffff; idv[s] = 0xffffffffu;
+      if (idx < n) { const uint64_t e = ws.keys[idx]; hb[s] = (int)(e >> 32); idv[s] = (uint32_t)e; }
+    }
+    __syncwarp();
+    int tlo = 0x7ffffffe, clo = n; /* n <= k: everything is accepted */
+    int nb = 0, rank = 0;
+    uint64_t mine = ~0ull;
+    if (n > k) {
+      int mx = 0;
+#pragma unroll
+      for (int s = 0; s < kSlots; s++) if (hb[s] != 0x7fffffff) mx = max(mx, hb[s]);
+      int thi = __reduce_max_sync(0xffffffffu, mx), chi = n;
+      tlo = -1; clo = 0;
+      float flo = 0.f, fhi = __int_as_float(thi);
+      bool first = true;
+      int it = 0;
+      while (chi - clo > 32) {
+        if (thi - tlo <= 2) { give_up = true; break; } /* > 32 candidates at one distance: degenerate */
+        int ta, tb;
+        if (it < 6) {
+          const float b = (float)(chi - clo);
+          const float delta = fmaxf(0.9f * sqrtf(b), 2.f);
+          const float fa = (fmaxf((float)k + 0.5f - delta, (float)clo + 0.5f) - (float)clo) / b;
+          const float fb = (fminf((float)k + 0.5f + delta, (float)chi - 0.5f) - (float)clo) / b;
+          float Ta, Tb;
+          if (first) { /* count ~ dist^3: interpolate in dist²^1.5 */
+            const float vlo = flo * sqrtf(flo), vhi = fhi * sqrtf(fhi);
+            Ta = exp2f(log2f(vlo + (vhi - vlo) * fa) * (2.f / 3.f));
+            Tb = exp2f(log2f(vlo + (vhi - vlo) * fb) * (2.f / 3.f));
+          } else {
+            Ta = flo + (fhi - flo) * fa;
+            Tb = flo + (fhi - flo) * fb;
+          }
+          ta = min(max(__float_as_int(Ta), tlo + 1), thi - 2);
+          tb = min(max(__float_as_int(Tb), ta + 1), thi - 1);
+        } else {
+          const int w3 = (thi - tlo) / 3;
+          ta = tlo + w3; tb = tlo + 2 * w3;
+        }
+        int ca = 0, cb = 0;
+#pragma unroll
+        for (int s = 0; s < kSlots; s++) { ca += hb[s] <= ta; cb += hb[s] <= tb; }
+        ca = __reduce_add_sync(0xffffffffu, ca);
+        cb = __reduce_add_sync(0xffffffffu, cb);
+        if (k <= ca) { thi = ta; chi = ca; fhi = __int_as_float(ta); }
+        else if (k <= cb) { tlo = ta; clo = ca; flo = __int_as_float(ta); thi = tb; chi = cb; fhi = __int_as_float(tb); }
+        else { tlo = tb; clo = cb; flo = __int_as_float(tb); }
+        first = false;
+        it++;
+      }
+      if (give_up) {
+        if (lane == 0) fb_list[atomicAdd(fb_count, 1)] = qi;
+        __syncwarp();
+        continue;
+      }
+      /* the bracket (tlo, thi] holds chi - clo <= 32 candidates: one per lane, exact rank by key */
+      nb = chi - clo;
+      int filled = 0;
+#pragma unroll
+      for (int s = 0; s < kSlots; s++) {
+        const bool inb = hb[s] > tlo && hb[s] <= thi;
+        const unsigned b = __ballot_sync(0xffffffffu, inb);
+        if (inb) ws.keys[filled + __popc(b & lt)] = ((uint64_t)(uint32_t)hb[s] << 32) | idv[s];
+        filled += __popc(b);
+      }
+      __syncwarp();
+      if (lane < nb) mine = ws.keys[lane];
+      for (int j = 0; j < nb; j++) rank += ws.keys[j] < mine;
+      __syncwarp();
+    }
+    const int need = kk - clo; /* accepted from the bracket (0 when n <= k) */
+    const bool acc_b = lane < nb && rank < need;
+
+    /* ---- output ------------------------------------------------------------------- */
+    int r2b = 0;
+#pragma unroll
+    for (int s = 0; s < kSlots; s++) if (hb[s] <= tlo) r2b = max(r2b, hb[s]);
+    if (acc_b) r2b = max(r2b, (int)(mine >> 32));
+    r2b = __reduce_max_sync(0xffffffffu, r2b);
+    const float r2 = kk == k ? __int_as_float(r2b) : io.cutoff2;
+    if (!GATHER) {
+      int32_t* ids = io.ids + (size_t)qi * k;
+      float* d2o = io.d2 ? io.d2 + (size_t)qi * k : nullptr;
+      int base = 0;
+#pragma unroll
+      for (int s = 0; s < kSlots; s++) {
+        const bool a = hb[s] <= tlo;
+        const unsigned b = __ballot_sync(0xffffffffu, a);
+        if (a) {
+          const int pos = base + __popc(b & lt);
+          ids[pos] = (int)idv[s];
+          if (d2o) d2o[pos] = __int_as_float(hb[s]);
+        }
+        base += __popc(b);
+      }
+      if (acc_b) {
+        ids[clo + rank] = (int)(uint32_t)mine;
+        if (d2o) d2o[clo + rank] = __uint_as_float((uint32_t)(mine >> 32));
+      }
+      for (int p = kk + lane; p < k; p += 32) { /* unfilled slots of the candidate list (knn.h:298-306) */
+        ids[p] = -1;
+        if (d2o) d2o[p] = io.cutoff2;
+      }
+      if (io.r2 && lane == 0) io.r2[qi] = r2;
+    } else {
+      /* gatherPhotons (ray-tracer/cuda/shading.h:93-121), summed across the warp */
+      const float rad = __fsqrt_rn(r2);
+      float fr = 0.f, fg = 0.f, fb = 0.f;
+#pragma unroll
+      for (int s = 0; s <= kSlots; s++) {
+        bool a; int h; uint32_t id;
+        if (s < kSlots) { a = hb[s] <= tlo; h = hb[s]; id = idv[s]; }
+        else { a = acc_b; h = (int)(mine >> 32); id = (uint32_t)mine; }
+        if (a) {
+          const float4 c = __ldg(color4 + id);
+          const float dist = __fsqrt_rn(__int_as_float(h));
+          const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
+          const float sc = __fmul_rn(__fmul_rn(brdf, c.w), w);
+          fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
+          fg = __fadd_rn(fg, __fmul_rn(sc, c.y));
+          fb = __fadd_rn(fb, __fmul_rn(sc, c.z));
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        fr = __fadd_rn(fr, __shfl_xor_sync(0xffffffffu, fr, o));
+        fg = __fadd_rn(fg, __shfl_xor_sync(0xffffffffu, fg, o));
+        fb = __fadd_rn(fb, __shfl_xor_sync(0xffffffffu, fb, o));
+      }
+      const float k1 = (1 - (2.f / 3.f) * (1.f / 1.1f));
+      const float denom = __fmul_rn(__fmul_rn(__fmul_rn(k1, 2.f), 3.14159274101257324f), r2);
+      if (lane == 0) {
+        io.rgb[(size_t)qi * 3 + 0] = __fdiv_rn(fr, denom);
+        io.rgb[(size_t)qi * 3 + 1] = __fdiv_rn(fg, denom);
+        io.rgb[(size_t)qi * 3 + 2] = __fdiv_rn(fb, denom);
+      }
+    }
+    __syncwarp();
+  }
+}
+
+/* ---- grid construction ------------------------------------------------------------------ */
+__global__ void k_cell_ids(const float4* __restrict__ nodes, int n, GridView g, uint32_t* __restrict__ keys,
+                           int* __restrict__ vals) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 p = __ldg(nodes + i);
+  const int cx = cell_of(p.x, g.lo[0], g.inv_cell, g.nx), cy = cell_of(p.y, g.lo[1], g.inv_cell, g.ny),
+            cz = cell_of(p.z, g.lo[2], g.inv_cell, g.nz);
+  keys[i] = (uint32_t)(((size_t)cz * g.ny + cy) * g.nx + cx);
+  vals[i] = i;
+}
+
+/* sorted (cell, node) pairs -> cell-ordered records and the offset table (empty cells included) */
+__global__ void k_grid_fill(const float4* __restrict__ nodes, int n, const uint32_t* __restrict__ keys,
+                            const int* __restrict__ vals, uint32_t n_cells, float4* __restrict__ pts,
+                            uint32_t* __restrict__ cell_start) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > n) return;
+  const int64_t prev = i == 0 ? -1 : (int64_t)keys[i - 1];
+  const int64_t cur = i == n ? (int64_t)n_cells : (int64_t)keys[i];
+  for (int64_t c = prev + 1; c <= cur; c++) cell_start[c] = (uint32_t)i;
+  if (i < n) {
+    const int id = vals[i];
+    const float4 p = __ldg(nodes + id);
+    pts[i] = make_float4(p.x, p.y, p.z, __int_as_float(id));
+  }
+}
+
+__global__ void k_sample_queries(const float4* __restrict__ nodes, int n, int ns, float* __restrict__ q) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ns) return;
+  /* a strided sample of the level-order array touches every level, i.e. it is spread over the cloud */
+  const float4 p = __ldg(nodes + (size_t)i * (n / ns));
+  q[3 * i + 0] = p.x; q[3 * i + 1] = p.y; q[3 * i + 2] = p.z;
+}
+
+GridView view_of(const pm_map* m) {
+  GridView g;
+  g.pts = m->grid_pts; g.cell_start = m->cell_start;
+  for (int d = 0; d < 3; d++) g.lo[d] = m->bounds[d];
+  g.cell = m->cell; g.inv_cell = m->inv_cell; g.margin = m->cell_margin;
+  g.nx = m->gdim[0]; g.ny = m->gdim[1]; g.nz = m->gdim[2];
+  return g;
+}
+
+int host_cell_of(float v, float lo, float inv_cell) {
+  const float u = (v - lo) * inv_cell; /* same float arithmetic as cell_of() */
+  return (int)std::floor(u);
+}
+
+}  // namespace
+
+namespace pm {
+
+int grid_build(pm_ctx* ctx, pm_map* m) {
+  if (m->n < kMinGridNodes) return PM_OK;
+  const int n = (int)m->n;
+  cudaStream_t st = ctx->stream;
+
+  /* 1. sample of exact k-th-neighbour distances (kd-tree kernel on kTuneSamples node positions) */
+  const int ns = kTuneSamples;
+  float *sq = nullptr, *sr2 = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)ns * 3, &sq));
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)ns, &sr2));
+  k_sample_queries<<<(unsigned)div_up(ns, 256), 256, 0, st>>>(m->nodes4, n, ns, sq);
+  ctx->launches++;
+  pmk::QueryIO io;
+  io.q = sq; io.nq = ns; io.k = kTuneK; io.cutoff2 = INFINITY; io.r2 = sr2;
+  PM_CHECK(kd_query(ctx, m, io, false, nullptr, nullptr));
+  std::vector<float> r2(ns);
+  PM_CUDA(cudaMemcpyAsync(r2.data(), sr2, sizeof(float) * ns, cudaMemcpyDeviceToHost, st));
+  PM_CUDA(cudaStreamSynchronize(st));
+  std::sort(r2.begin(), r2.end());
+  const float r50 = std::sqrt(r2[ns / 2]), r98 = std::sqrt(r2[(size_t)(ns * 0.98)]);
+  if (!(r98 > 0.f) || !std::isfinite(r98)) return PM_OK; /* degenerate cloud: kd-tree kernels only */
+  /* G >= 2 cells: two cells must cover the k-th-neighbour distance of nearly every query. Tight
+   * distributions (uniform clouds) take the 98th percentile plus a little; broad ones would pay
+   * for their tail in every dense neighbourhood, so they take the 90th and leave the rest to the
+   * kd-tree kernel. */
+  const float rk = r98 < 1.25f * r50 ? r98 * 1.03f : std::sqrt(r2[(size_t)(ns * 0.90)]);
+  float cell = 0.5f * rk;
+  float maxabs = 0.f;
+  for (int d = 0; d < 3; d++) {
+    maxabs = std::max(maxabs, std::max(std::fabs(m->bounds[d]), std::fabs(m->bounds[3 + d])));
+  }
+  int dim[3];
+  while (true) {
+    const float inv = 1.f / cell;
+    int64_t cells = 1;
+    for (int d = 0; d < 3; d++) {
+      dim[d] = host_cell_of(m->bounds[3 + d], m->bounds[d], inv) + 1;
+      if (dim[d] < 1) dim[d] = 1;
+      cells *= dim[d];
+    }
+    if (cells <= kMaxCells && dim[0] < 32768 && dim[1] < 32768 && dim[2] < 32768) break;
+    cell *= 1.26f;
+  }
+  m->cell = cell; m->inv_cell = 1.f / cell; m->tuned_rk = rk;
+  m->cell_margin = 1e-3f * cell + 16.f * FLT_EPSILON * maxabs;
+  m->gdim[0] = dim[0]; m->gdim[1] = dim[1]; m->gdim[2] = dim[2];
+  const int64_t n_cells = (int64_t)dim[0] * dim[1] * dim[2];
+
+  /* 2. sort node ids by cell, emit the cell-ordered records and the offset table */
+  uint32_t *keys_in, *keys_out; int *vals_in, *vals_out;
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)n, &keys_in));
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)n, &keys_out));
+  PM_CHECK(ctx->get_scratch(pm::S_VALS0, (size_t)n, &vals_in));
+  PM_CHECK(ctx->get_scratch(pm::S_VALS1, (size_t)n, &vals_out));
+  if (cudaMalloc(&m->grid_pts, sizeof(float4) * (size_t)n) != cudaSuccess ||
+      cudaMalloc(&m->cell_start, sizeof(uint32_t) * (size_t)(n_cells + 1)) != cudaSuccess) {
+    cudaGetLastError();
+    if (m->grid_pts) cudaFree(m->grid_pts);
+    m->grid_pts = nullptr; m->cell_start = nullptr; /* no grid: the kd-tree kernels answer everything */
+    return PM_OK;
+  }
+  GridView g = view_of(m);
+  k_cell_ids<<<(unsigned)div_up(n, 256), 256, 0, st>>>(m->nodes4, n, g, keys_in, vals_in);
+  int bits = 1;
+  while (((int64_t)1 << bits) < n_cells) bits++;
+  size_t tb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_in, keys_out, vals_in, vals_out, n, 0, bits, st);
+  void* tmp = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_CUB, tb, &tmp));
+  PM_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, keys_in, keys_out, vals_in, vals_out, n, 0, bits, st));
+  k_grid_fill<<<(unsigned)div_up((int64_t)n + 1, 256), 256, 0, st>>>(m->nodes4, n, keys_out, vals_out, (uint32_t)n_cells,
+                                                                    m->grid_pts, m->cell_start);
+  ctx->launches += 6;
+  PM_CUDA(cudaGetLastError());
+  return PM_OK;
+}
+
+int grid_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gather, int* fb_list, int* fb_count) {
+  const GridView g = view_of(map);
+  int64_t grid = div_up(io.nq, kWarps);
+  const int64_t cap = (int64_t)ctx->sm_count * 64;
+  if (grid > cap) grid = cap;
+  if (gather) k_grid_query<true><<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fb_list, fb_count);
+  else k_grid_query<false><<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fb_list, fb_count);
+  ctx->launches++;
+  PM_CUDA(cudaGetLastError());
+  return PM_OK;
+}
+
+}  // namespace pm

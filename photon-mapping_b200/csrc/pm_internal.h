@@ -103,9 +103,20 @@ struct pm_map {
   float4* nodes4 = nullptr;                  /* (x, y, z, bits(split_dim)) per node, tree order */
   float4* color4 = nullptr;                  /* (r, g, b, power) per node */
   float bounds[6] = {0, 0, 0, 0, 0, 0};
+  /* uniform-grid copy for the warp-cooperative query kernels (pm_grid.cu); absent for small maps */
+  float4* grid_pts = nullptr;                /* (x, y, z, bits(node id)) sorted by cell, x fastest */
+  uint32_t* cell_start = nullptr;            /* n_cells + 1 offsets into grid_pts */
+  float cell = 0.f, inv_cell = 0.f, cell_margin = 0.f;
+  int gdim[3] = {0, 0, 0};
+  float tuned_rk = 0.f;                      /* sampled k-th neighbour distance the cell size came from */
 };
 
 namespace pm {
+/* pm_grid.cu: builds the uniform-grid copy of a map whose nodes4 and bounds are valid; maps it
+ * leaves without a grid are answered by the kd-tree kernels alone. */
+int grid_build(pm_ctx* ctx, pm_map* m);
+/* pm_knn.cu: axis-aligned bounds of nodes4 into m->bounds (maps wrapped with pm_map_from_tree) */
+int map_bounds(pm_ctx* ctx, pm_map* m);
 /* pm_knn.cu: fused kNN + radiance estimate on device pointers (used by pm_gather and pm_render).
  * Queries whose brdf is not > 0 are not evaluated and yield (0,0,0). */
 int gather_device(pm_ctx* ctx, const pm_map* map, const float* hit_dev, const float* brdf_dev, int64_t nq, int k,

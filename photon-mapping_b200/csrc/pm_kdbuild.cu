@@ -332,6 +332,8 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   if (!dev_in) PM_BC(cudaMemcpyAsync(photons, tree, sizeof(pm_photon44) * (size_t)n, cudaMemcpyDeviceToHost, st));
   PM_BC(cudaStreamSynchronize(st));
   if (bounds_host) memcpy(bounds_host, m->bounds, sizeof(float) * 6);
+  PM_B(pm::grid_build(ctx, m));
+  PM_BC(cudaStreamSynchronize(st));
 #undef PM_B
 #undef PM_BC
   *out = m;
@@ -357,6 +359,8 @@ int pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map*
     m->photons_dev = m->owned_photons;
   }
   int r = make_soa(ctx, m);
+  if (r == PM_OK) r = pm::map_bounds(ctx, m);
+  if (r == PM_OK) r = pm::grid_build(ctx, m);
   if (r == PM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) { pm::set_error("pm_map_from_tree: sync failed"); r = PM_ERR_CUDA; }
   if (r != PM_OK) { pm_map_destroy(m); return r; }
   *out = m;
@@ -370,6 +374,8 @@ void pm_map_destroy(pm_map* m) {
   if (m->owned_photons) cudaFree(m->owned_photons);
   if (m->nodes4) cudaFree(m->nodes4);
   if (m->color4) cudaFree(m->color4);
+  if (m->grid_pts) cudaFree(m->grid_pts);
+  if (m->cell_start) cudaFree(m->cell_start);
   delete m;
 }
 

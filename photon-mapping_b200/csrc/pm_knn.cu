@@ -21,15 +21,13 @@
  */
 #include <cub/cub.cuh>
 #include <cfloat>
-#include "pm_internal.h"
+#include "pm_knn.cuh"
 
 namespace {
 
-constexpr int kBlock = 128;
+using pmk::encode;
 
-__device__ __forceinline__ uint64_t encode(float d2, int id) {
-  return ((uint64_t)__float_as_uint(d2) << 32) | (uint32_t)id;
-}
+constexpr int kBlock = 128;
 
 /* expands 10 bits into every third bit */
 __device__ __forceinline__ uint32_t part1by2(uint32_t v) {
@@ -136,69 +134,66 @@ __device__ __forceinline__ void traverse(const float4* __restrict__ nodes, int n
   }
 }
 
-template <int K>
+/* one thread per query; with `list` the queries are list[0 .. *list_count), else order[t] (or t) */
+template <int K, bool GATHER>
 __global__ void __launch_bounds__(kBlock)
-k_knn(const float4* __restrict__ nodes, int n, const float* __restrict__ queries, const int* __restrict__ perm, int nq,
-      float cutoff2, int32_t* __restrict__ out_ids, float* __restrict__ out_d2, float* __restrict__ out_r2) {
+k_kd(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n, pmk::QueryIO io,
+     const int* __restrict__ list, const int* __restrict__ list_count) {
   extern __shared__ uint64_t smem_heap[];
-  const int t = blockIdx.x * kBlock + threadIdx.x;
-  SmemHeap<K> heap;
-  heap.init(smem_heap, cutoff2);
-  if (t >= nq) return;
-  const int qi = perm ? perm[t] : t;
-  const float qx = queries[(size_t)qi * 3 + 0], qy = queries[(size_t)qi * 3 + 1], qz = queries[(size_t)qi * 3 + 2];
-  traverse<K>(nodes, n, qx, qy, qz, heap);
-  if (out_r2) out_r2[qi] = heap.max_dist2();
-  /* each thread streams its own row; K is even so rows are 8-byte aligned */
-  int2* ids2 = reinterpret_cast<int2*>(out_ids + (size_t)qi * K);
-  float2* d22 = out_d2 ? reinterpret_cast<float2*>(out_d2 + (size_t)qi * K) : nullptr;
+  const int total = list ? *list_count : io.nq;
+  for (int t = blockIdx.x * kBlock + threadIdx.x; t < total; t += gridDim.x * kBlock) {
+    const int qi = list ? list[t] : (io.order ? io.order[t] : t);
+    float f = 0.f;
+    if (GATHER) {
+      f = io.brdf[qi];
+      if (!(f > 0.f)) { /* flux = brdf * ... is +0 for brdf == 0; negative marks "no query" (render pipeline) */
+        io.rgb[(size_t)qi * 3 + 0] = 0.f; io.rgb[(size_t)qi * 3 + 1] = 0.f; io.rgb[(size_t)qi * 3 + 2] = 0.f;
+        continue;
+      }
+    }
+    SmemHeap<K> heap;
+    heap.init(smem_heap, io.cutoff2);
+    const float qx = io.q[(size_t)qi * 3 + 0], qy = io.q[(size_t)qi * 3 + 1], qz = io.q[(size_t)qi * 3 + 2];
+    traverse<K>(nodes, n, qx, qy, qz, heap);
+    if (!GATHER) {
+      if (io.r2) io.r2[qi] = heap.max_dist2();
+      if (io.ids) {
+        /* each thread streams its own row; K is even so rows are 8-byte aligned */
+        int2* ids2 = reinterpret_cast<int2*>(io.ids + (size_t)qi * K);
+        float2* d22 = io.d2 ? reinterpret_cast<float2*>(io.d2 + (size_t)qi * K) : nullptr;
 #pragma unroll 4
-  for (int s = 0; s < K; s += 2) {
-    const uint64_t a = heap.col[s * kBlock], b = heap.col[(s + 1) * kBlock];
-    ids2[s >> 1] = make_int2((int)(uint32_t)a, (int)(uint32_t)b);
-    if (d22) d22[s >> 1] = make_float2(__uint_as_float((uint32_t)(a >> 32)), __uint_as_float((uint32_t)(b >> 32)));
+        for (int s = 0; s < K; s += 2) {
+          const uint64_t a = heap.col[s * kBlock], b = heap.col[(s + 1) * kBlock];
+          ids2[s >> 1] = make_int2((int)(uint32_t)a, (int)(uint32_t)b);
+          if (d22) d22[s >> 1] = make_float2(__uint_as_float((uint32_t)(a >> 32)), __uint_as_float((uint32_t)(b >> 32)));
+        }
+      }
+    } else {
+      /* gatherPhotons (shading.h:93-121); arithmetic as written there, one rounding per op */
+      const float r2 = heap.max_dist2();
+      const float rad = __fsqrt_rn(r2);
+      float fr = 0.f, fg = 0.f, fb = 0.f;
+      for (int s = 0; s < K; s++) {
+        const int id = (int)(uint32_t)heap.col[s * kBlock];
+        if (id < 0 || id > n) continue; /* sic, shading.h:105 */
+        const float4 p = __ldg(nodes + id);
+        const float4 c = __ldg(color4 + id);
+        const float dx = p.x - qx, dy = p.y - qy, dz = p.z - qz;
+        const float dist = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+        const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
+        const float sc = __fmul_rn(__fmul_rn(f, c.w), w);
+        fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
+        fg = __fadd_rn(fg, __fmul_rn(sc, c.y));
+        fb = __fadd_rn(fb, __fmul_rn(sc, c.z));
+      }
+      const float k1 = (1 - (2.f / 3.f) * (1.f / 1.1f));
+      const float denom = __fmul_rn(__fmul_rn(__fmul_rn(k1, 2.f), 3.14159274101257324f), r2);
+      io.rgb[(size_t)qi * 3 + 0] = __fdiv_rn(fr, denom);
+      io.rgb[(size_t)qi * 3 + 1] = __fdiv_rn(fg, denom);
+      io.rgb[(size_t)qi * 3 + 2] = __fdiv_rn(fb, denom);
+    }
+    __syncwarp();
   }
-}
-
-/* fused kNN + gatherPhotons (shading.h:93-121); arithmetic as written there, one rounding per op */
-template <int K>
-__global__ void __launch_bounds__(kBlock)
-k_gather(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n, const float* __restrict__ hit,
-         const float* __restrict__ brdf, const int* __restrict__ perm, int nq, float cutoff2, float* __restrict__ out_rgb) {
-  extern __shared__ uint64_t smem_heap[];
-  const int t = blockIdx.x * kBlock + threadIdx.x;
-  SmemHeap<K> heap;
-  heap.init(smem_heap, cutoff2);
-  if (t >= nq) return;
-  const int qi = perm ? perm[t] : t;
-  const float f = brdf[qi];
-  if (!(f > 0.f)) { /* flux = brdf * ... is +0 for brdf == 0; negative marks "no query" (render pipeline) */
-    out_rgb[(size_t)qi * 3 + 0] = 0.f; out_rgb[(size_t)qi * 3 + 1] = 0.f; out_rgb[(size_t)qi * 3 + 2] = 0.f;
-    return;
-  }
-  const float qx = hit[(size_t)qi * 3 + 0], qy = hit[(size_t)qi * 3 + 1], qz = hit[(size_t)qi * 3 + 2];
-  traverse<K>(nodes, n, qx, qy, qz, heap);
-  const float r2 = heap.max_dist2();
-  const float rad = __fsqrt_rn(r2);
-  float fr = 0.f, fg = 0.f, fb = 0.f;
-  for (int s = 0; s < K; s++) {
-    const int id = (int)(uint32_t)heap.col[s * kBlock];
-    if (id < 0 || id > n) continue; /* sic, shading.h:105 */
-    const float4 p = __ldg(nodes + id);
-    const float4 c = __ldg(color4 + id);
-    const float dx = p.x - qx, dy = p.y - qy, dz = p.z - qz;
-    const float dist = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
-    const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
-    const float sc = __fmul_rn(__fmul_rn(f, c.w), w);
-    fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
-    fg = __fadd_rn(fg, __fmul_rn(sc, c.y));
-    fb = __fadd_rn(fb, __fmul_rn(sc, c.z));
-  }
-  const float k1 = (1 - (2.f / 3.f) * (1.f / 1.1f));
-  const float denom = __fmul_rn(__fmul_rn(__fmul_rn(k1, 2.f), 3.14159274101257324f), r2);
-  out_rgb[(size_t)qi * 3 + 0] = __fdiv_rn(fr, denom);
-  out_rgb[(size_t)qi * 3 + 1] = __fdiv_rn(fg, denom);
-  out_rgb[(size_t)qi * 3 + 2] = __fdiv_rn(fb, denom);
 }
 
 /* Morton order of the queries inside the map's box → permutation in scratch slot S_PERM */
@@ -225,25 +220,16 @@ int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float
   return PM_OK;
 }
 
-template <int K>
-int launch_knn(pm_ctx* ctx, const pm_map* map, const float* q, const int* perm, int nq, float cutoff2, int32_t* ids,
-               float* d2, float* r2) {
+template <int K, bool GATHER>
+int launch_kd(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, const int* list, const int* list_count) {
   const size_t smem = sizeof(uint64_t) * K * kBlock;
-  PM_CUDA(cudaFuncSetAttribute(k_knn<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  k_knn<K><<<(unsigned)pm::div_up(nq, kBlock), kBlock, smem, ctx->stream>>>(map->nodes4, (int)map->n, q, perm, nq, cutoff2,
-                                                                          ids, d2, r2);
-  ctx->launches++;
-  PM_CUDA(cudaGetLastError());
-  return PM_OK;
-}
-
-template <int K>
-int launch_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, const int* perm, int nq,
-                  float cutoff2, float* rgb) {
-  const size_t smem = sizeof(uint64_t) * K * kBlock;
-  PM_CUDA(cudaFuncSetAttribute(k_gather<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  k_gather<K><<<(unsigned)pm::div_up(nq, kBlock), kBlock, smem, ctx->stream>>>(map->nodes4, map->color4, (int)map->n, hit,
-                                                                             brdf, perm, nq, cutoff2, rgb);
+  PM_CUDA(cudaFuncSetAttribute(k_kd<K, GATHER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  /* a list of unknown (device-side) length is served by a fixed, persistent grid */
+  int64_t grid = pm::div_up(io.nq, kBlock);
+  const int64_t cap = (int64_t)ctx->sm_count * (list ? 2 : 64);
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  k_kd<K, GATHER><<<(unsigned)grid, kBlock, smem, ctx->stream>>>(map->nodes4, map->color4, (int)map->n, io, list, list_count);
   ctx->launches++;
   PM_CUDA(cudaGetLastError());
   return PM_OK;
@@ -260,9 +246,85 @@ __global__ void k_fill_f(int64_t total, float* p, float v) {
   if (i < total) p[i] = v;
 }
 
+/* bounds of a tree-ordered map: ordered-uint atomics, one per block and axis */
+__device__ __forceinline__ uint32_t f2ord(float f) { const uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__global__ void k_bounds(const float4* __restrict__ nodes, int n, uint32_t* __restrict__ out /*lo xyz, hi xyz (ordered)*/) {
+  uint32_t lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 p = __ldg(nodes + i);
+    const uint32_t o[3] = {f2ord(p.x), f2ord(p.y), f2ord(p.z)};
+#pragma unroll
+    for (int d = 0; d < 3; d++) { lo[d] = min(lo[d], o[d]); hi[d] = max(hi[d], o[d]); }
+  }
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    lo[d] = __reduce_min_sync(0xffffffffu, lo[d]);
+    hi[d] = __reduce_max_sync(0xffffffffu, hi[d]);
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int d = 0; d < 3; d++) { atomicMin(out + d, lo[d]); atomicMax(out + 3 + d, hi[d]); }
+  }
+}
+
+template <bool GATHER>
+int dispatch_kd(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, const int* list, const int* list_count) {
+  switch (io.k) {
+    case 8: return launch_kd<8, GATHER>(ctx, map, io, list, list_count);
+    case 16: return launch_kd<16, GATHER>(ctx, map, io, list, list_count);
+    case 32: return launch_kd<32, GATHER>(ctx, map, io, list, list_count);
+    case 50: return launch_kd<50, GATHER>(ctx, map, io, list, list_count);
+    case 64: return launch_kd<64, GATHER>(ctx, map, io, list, list_count);
+    default: pm::set_error("k must be one of 8, 16, 32, 50, 64 (got %d)", io.k); return PM_ERR_UNSUPPORTED;
+  }
+}
+
+/* answers one batch on device pointers: Morton order, grid kernel, kd-tree kernel for the rest */
+int run_queries(pm_ctx* ctx, const pm_map* map, pmk::QueryIO io, bool gather, bool time_it) {
+  int* perm = nullptr;
+  PM_CHECK(sort_queries(ctx, map, io.q, gather ? io.brdf : nullptr, io.nq, &perm));
+  io.order = perm;
+  if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+  if (map->grid_pts) {
+    int *fb_list = nullptr, *fb_count = nullptr;
+    PM_CHECK(ctx->get_scratch(pm::S_MISC1, (size_t)io.nq, &fb_list));
+    PM_CHECK(ctx->get_scratch(pm::S_MISC2, (size_t)4, &fb_count));
+    PM_CUDA(cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
+    PM_CHECK(pm::grid_query(ctx, map, io, gather, fb_list, fb_count));
+    PM_CHECK(pm::kd_query(ctx, map, io, gather, fb_list, fb_count));
+  } else {
+    PM_CHECK(pm::kd_query(ctx, map, io, gather, nullptr, nullptr));
+  }
+  if (time_it) PM_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  return PM_OK;
+}
+
 }  // namespace
 
 namespace pm {
+
+int kd_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gather, const int* list, const int* list_count) {
+  return gather ? dispatch_kd<true>(ctx, map, io, list, list_count) : dispatch_kd<false>(ctx, map, io, list, list_count);
+}
+
+int map_bounds(pm_ctx* ctx, pm_map* m) {
+  uint32_t* d = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_MISC3, (size_t)8, &d));
+  const uint32_t init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+  PM_CUDA(cudaMemcpyAsync(d, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+  int64_t grid = div_up(m->n, 256);
+  if (grid > ctx->sm_count * 8) grid = ctx->sm_count * 8;
+  k_bounds<<<(unsigned)grid, 256, 0, ctx->stream>>>(m->nodes4, (int)m->n, d);
+  ctx->launches++;
+  uint32_t h[6];
+  PM_CUDA(cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  for (int i = 0; i < 6; i++) {
+    const uint32_t u = (h[i] & 0x80000000u) ? (h[i] & 0x7fffffffu) : ~h[i];
+    memcpy(&m->bounds[i], &u, 4);
+  }
+  return PM_OK;
+}
 
 /* device-pointer entry used by pm_gather and by the render pipeline */
 int gather_device(pm_ctx* ctx, const pm_map* map, const float* hit_dev, const float* brdf_dev, int64_t nq, int k,
@@ -273,21 +335,10 @@ int gather_device(pm_ctx* ctx, const pm_map* map, const float* hit_dev, const fl
     ctx->launches++;
     return PM_OK;
   }
-  const float cutoff2 = cutoff * cutoff;
-  int* perm = nullptr;
-  PM_CHECK(sort_queries(ctx, map, hit_dev, brdf_dev, (int)nq, &perm));
-  if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
-  int r;
-  switch (k) {
-    case 8: r = launch_gather<8>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
-    case 16: r = launch_gather<16>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
-    case 32: r = launch_gather<32>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
-    case 50: r = launch_gather<50>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
-    case 64: r = launch_gather<64>(ctx, map, hit_dev, brdf_dev, perm, (int)nq, cutoff2, rgb_dev); break;
-    default: set_error("k must be one of 8, 16, 32, 50, 64 (got %d)", k); return PM_ERR_UNSUPPORTED;
-  }
-  if (time_it) PM_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
-  return r;
+  if (!(k == 8 || k == 16 || k == 32 || k == 50 || k == 64)) { set_error("k must be one of 8, 16, 32, 50, 64 (got %d)", k); return PM_ERR_UNSUPPORTED; }
+  pmk::QueryIO io;
+  io.q = hit_dev; io.brdf = brdf_dev; io.nq = (int)nq; io.k = k; io.cutoff2 = cutoff * cutoff; io.rgb = rgb_dev;
+  return run_queries(ctx, map, io, true, time_it);
 }
 
 }  // namespace pm
@@ -314,19 +365,10 @@ int pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int
     if (o_r2.dev) k_fill_f<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(nq, (float*)o_r2.dev, cutoff2);
     ctx->launches += 2;
   } else {
-    int* perm = nullptr;
-    PM_CHECK(sort_queries(ctx, map, (const float*)q_dev, nullptr, (int)nq, &perm));
-    PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
-    int r;
-    switch (k) {
-      case 8: r = launch_knn<8>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
-      case 16: r = launch_knn<16>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
-      case 32: r = launch_knn<32>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
-      case 50: r = launch_knn<50>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
-      default: r = launch_knn<64>(ctx, map, (const float*)q_dev, perm, (int)nq, cutoff2, (int32_t*)o_ids.dev, (float*)o_d2.dev, (float*)o_r2.dev); break;
-    }
-    PM_CHECK(r);
-    PM_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+    pmk::QueryIO io;
+    io.q = (const float*)q_dev; io.nq = (int)nq; io.k = k; io.cutoff2 = cutoff2;
+    io.ids = (int32_t*)o_ids.dev; io.d2 = (float*)o_d2.dev; io.r2 = (float*)o_r2.dev;
+    PM_CHECK(run_queries(ctx, map, io, false, true));
   }
   PM_CHECK(pm::stage_out_finish(ctx, o_ids));
   PM_CHECK(pm::stage_out_finish(ctx, o_d2));
