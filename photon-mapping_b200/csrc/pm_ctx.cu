@@ -128,5 +128,6 @@ int pm_ctx_sync(pm_ctx* ctx) {
 int64_t pm_ctx_launch_count(pm_ctx* ctx) { return ctx ? ctx->launches : 0; }
 void pm_ctx_reset_launch_count(pm_ctx* ctx) { if (ctx) ctx->launches = 0; }
 float pm_ctx_last_kernel_ms(pm_ctx* ctx) { return ctx ? ctx->last_kernel_ms : 0.f; }
+int64_t pm_ctx_last_fallback_count(pm_ctx* ctx) { return ctx ? ctx->last_fallbacks : 0; }
 
 }  // extern "C"

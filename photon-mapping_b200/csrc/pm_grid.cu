@@ -40,6 +40,8 @@ constexpr int kBuf = 160;          /* compacted candidates per query */
 constexpr int kSlots = kBuf / 32;  /* candidates per lane in the selection phase */
 constexpr int kMaxScan = 1024;     /* nodes in the 5x5x5 block beyond which the kd-tree kernel takes over */
 constexpr int kWords = kMaxScan / 32;
+constexpr int kMaxH = 8;          /* widest block tried: (2 * 8 + 1)^3 cells */
+constexpr int kMaxAttempts = 12;
 constexpr int kTuneK = 64;         /* the cell size is tuned for the largest supported k */
 constexpr int kTuneSamples = 2048;
 constexpr int64_t kMinGridNodes = 4096;
@@ -65,13 +67,25 @@ __device__ __forceinline__ int cell_of(float v, float lo, float inv_cell, int n)
   return (int)fminf(fmaxf(floorf(u), 0.f), (float)(n - 1));
 }
 
+/* x / d for x < 1024 and 1 <= d <= 17 (checked exhaustively): rows of a block per lane */
+__device__ __forceinline__ int div_small(int x, int d) { return (x * ((1 << 16) / d + 1)) >> 16; }
+
+/* cell index of coordinate v: the same floor((v - lo) * inv_cell) the build uses, clamped */
+__device__ __forceinline__ int cell_idx(float v, float lo, float inv_cell, int n) {
+  return min(max(__float2int_rd((v - lo) * inv_cell), 0), n - 1);
+}
+
+/* x^(2/3) and x^(3/2) for the radius guesses: two MUFU ops, accuracy is irrelevant there */
+__device__ __forceinline__ float pow23(float x) { return __powf(x, 2.f / 3.f); }
+__device__ __forceinline__ float pow32(float x) { return __powf(x, 1.5f); }
+
 template <bool GATHER>
 __global__ void __launch_bounds__(kWarps * 32)
 k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::QueryIO io, int* __restrict__ fb_list,
              int* __restrict__ fb_count) {
   __shared__ WarpScratch scratch[kWarps];
   const int lane = threadIdx.x & 31;
-  const unsigned lt = (1u << lane) - 1u, le = lt | (1u << lane);
+  const unsigned lt = (1u << lane) - 1u, le_not0 = (lt | (1u << lane)) & ~1u;
   WarpScratch& ws = scratch[threadIdx.x >> 5];
   const int k = io.k;
   const float cell3 = g.cell * g.cell * g.cell;
@@ -87,98 +101,133 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
       }
     }
     const float qx = io.q[(size_t)qi * 3 + 0], qy = io.q[(size_t)qi * 3 + 1], qz = io.q[(size_t)qi * 3 + 2];
+    const int cx = cell_idx(qx, g.lo[0], g.inv_cell, g.nx), cy = cell_idx(qy, g.lo[1], g.inv_cell, g.ny),
+              cz = cell_idx(qz, g.lo[2], g.inv_cell, g.nz);
 
-    /* ---- the 5x5x5 block and the radius G it is guaranteed to cover ---------------------- */
-    const int cx = cell_of(qx, g.lo[0], g.inv_cell, g.nx), cy = cell_of(qy, g.lo[1], g.inv_cell, g.ny),
-              cz = cell_of(qz, g.lo[2], g.inv_cell, g.nz);
-    const int x0 = max(cx - 2, 0), x1 = min(cx + 2, g.nx - 1);
-    const int y0 = max(cy - 2, 0), y1 = min(cy + 2, g.ny - 1);
-    const int z0 = max(cz - 2, 0), z1 = min(cz + 2, g.nz - 1);
-    float G = INFINITY;
-    if (x0 > 0) G = fminf(G, qx - (g.lo[0] + (float)x0 * g.cell));
-    if (x1 < g.nx - 1) G = fminf(G, (g.lo[0] + (float)(x1 + 1) * g.cell) - qx);
-    if (y0 > 0) G = fminf(G, qy - (g.lo[1] + (float)y0 * g.cell));
-    if (y1 < g.ny - 1) G = fminf(G, (g.lo[1] + (float)(y1 + 1) * g.cell) - qy);
-    if (z0 > 0) G = fminf(G, qz - (g.lo[2] + (float)z0 * g.cell));
-    if (z1 < g.nz - 1) G = fminf(G, (g.lo[2] + (float)(z1 + 1) * g.cell) - qz);
-    G -= g.margin;
-    const float G2 = G > 0.f ? G * G : 0.f;
-    const bool complete = !(G2 < io.cutoff2); /* the block holds every node inside the cutoff ball */
-    const float Rmax2 = fminf(G2, io.cutoff2);
+    /* ---- candidate search: block of (2h+1)^3 cells, ball of radius sqrt(R2) inside it ------ */
+    int h = 2, n = 0;
+    float R2 = 0.f, R2lo = 0.f, R2hi = INFINITY;
+    bool give_up = false, take_max = false;
+    for (int attempt = 0;; attempt++) {
+      const int x0 = max(cx - h, 0), x1 = min(cx + h, g.nx - 1);
+      const int y0 = max(cy - h, 0), y1 = min(cy + h, g.ny - 1);
+      const int z0 = max(cz - h, 0), z1 = min(cz + h, g.nz - 1);
+      /* G: distance to the nearest block face that is not a face of the grid itself */
+      float G = INFINITY;
+      if (x0 > 0) G = fminf(G, qx - (g.lo[0] + (float)x0 * g.cell));
+      if (x1 < g.nx - 1) G = fminf(G, (g.lo[0] + (float)(x1 + 1) * g.cell) - qx);
+      if (y0 > 0) G = fminf(G, qy - (g.lo[1] + (float)y0 * g.cell));
+      if (y1 < g.ny - 1) G = fminf(G, (g.lo[1] + (float)(y1 + 1) * g.cell) - qy);
+      if (z0 > 0) G = fminf(G, qz - (g.lo[2] + (float)z0 * g.cell));
+      if (z1 < g.nz - 1) G = fminf(G, (g.lo[2] + (float)(z1 + 1) * g.cell) - qz);
+      G -= g.margin;
+      const float Rmax2 = fminf(G > 0.f ? G * G : 0.f, io.cutoff2);
+      const int ny_r = y1 - y0 + 1, nrows = ny_r * (z1 - z0 + 1);
+      if (attempt == 0) {
+        /* first radius from the block's mean density: expect ~1.3 k + 12 nodes inside it */
+        int c = 0;
+        if (lane < nrows) {
+          const int rzo = div_small(lane, ny_r);
+          const size_t base = ((size_t)(z0 + rzo) * g.ny + (y0 + lane - rzo * ny_r)) * g.nx;
+          c = (int)(__ldg(g.cell_start + base + x1 + 1) - __ldg(g.cell_start + base + x0));
+        }
+        const int m0 = __reduce_add_sync(0xffffffffu, c);
+        R2 = Rmax2;
+        if (m0 > 0) {
+          const float vol = (float)((x1 - x0 + 1) * nrows) * cell3;
+          R2 = fminf(Rmax2, pow23(__fdividef((1.3f * (float)k + 12.f) * vol, 4.18879f * (float)m0)));
+        }
+      } else if (take_max) {
+        R2 = Rmax2;
+        take_max = false;
+      }
 
-    /* ---- the runs: one per (y, z) row of the block ------------------------------------ */
-    const int ny_r = y1 - y0 + 1, nrows = ny_r * (z1 - z0 + 1);
-    int len = 0, st = 0;
-    if (lane < nrows) {
-      const int ry = y0 + lane % ny_r, rz = z0 + lane / ny_r;
-      const size_t base = ((size_t)rz * g.ny + ry) * g.nx;
-      st = (int)__ldg(g.cell_start + base + x0);
-      len = (int)__ldg(g.cell_start + base + x1 + 1) - st;
-    }
-    int incl = len;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
-    }
-    const int m = __shfl_sync(0xffffffffu, incl, 31);
-    bool give_up = m > kMaxScan;
-
-    int n = 0;
-    if (!give_up) {
-      /* flat index space: bitmap of run starts + per-run address offsets */
-      const int P = incl - len;
-      ws.words[lane] = make_uint2(0u, 0u);
-      __syncwarp();
-      if (len > 0) atomicOr(&ws.words[P >> 5].x, 1u << (P & 31));
-      const unsigned nonempty = __ballot_sync(0xffffffffu, len > 0);
-      if (len > 0) ws.run_off[__popc(nonempty & lt)] = st - P;
-      __syncwarp();
-      {
-        const int wc = __popc(ws.words[lane].x);
-        int wi = wc;
+      /* rows of the block, 32 at a time: trim each to the ball, flatten, scan */
+      n = 0;
+      bool dense = false;
+      for (int r0 = 0; r0 < nrows; r0 += 32) {
+        const int row = r0 + lane;
+        int len = 0, st = 0;
+        if (row < nrows) {
+          const int rzo = div_small(row, ny_r);
+          const int ry = y0 + row - rzo * ny_r, rz = z0 + rzo;
+          const float ylo = g.lo[1] + (float)ry * g.cell, zlo = g.lo[2] + (float)rz * g.cell;
+          const float dy = fmaxf(fmaxf(ylo - qy, qy - (ylo + g.cell)) - g.margin, 0.f);
+          const float dz = fmaxf(fmaxf(zlo - qz, qz - (zlo + g.cell)) - g.margin, 0.f);
+          const float dyz2 = dy * dy + dz * dz;
+          if (dyz2 < R2) {
+            const float w = __fsqrt_ru(R2 - dyz2) + g.margin;
+            const int xa = max(cell_idx(qx - w, g.lo[0], g.inv_cell, g.nx), x0);
+            const int xb = min(cell_idx(qx + w, g.lo[0], g.inv_cell, g.nx), x1);
+            if (xa <= xb) {
+              const size_t base = ((size_t)rz * g.ny + ry) * g.nx;
+              st = (int)__ldg(g.cell_start + base + xa);
+              len = (int)__ldg(g.cell_start + base + xb + 1) - st;
+            }
+          }
+        }
+        int incl = len;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-          const int v = __shfl_up_sync(0xffffffffu, wi, o);
-          if (lane >= o) wi += v;
+          const int v = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += v;
         }
-        ws.words[lane].y = (unsigned)(wi - wc);
-      }
-      __syncwarp();
-
-      /* first search radius from the block's mean density: expect ~1.3 k + 12 nodes inside it */
-      float R2 = Rmax2;
-      if (m > 0) {
-        const float vol = (float)((x1 - x0 + 1) * nrows) * cell3;
-        const float f3 = (1.3f * (float)k + 12.f) * vol / (4.18879f * (float)m);
-        R2 = fminf(Rmax2, exp2f(log2f(f3) * (2.f / 3.f)));
-      }
-      while (true) {
-        n = 0;
-        for (int i = 0; i * 32 < m; i++) {
+        const int mc = __shfl_sync(0xffffffffu, incl, 31);
+        if (mc == 0) continue;
+        if (mc > kMaxScan) { dense = true; break; }
+        /* flat index space of this chunk: words[i].x = bitmap of run starts among elements
+         * [32 i, 32 i + 32), words[i].y = the run holding element 32 i, run_off = address offsets */
+        const int P = incl - len;
+        __syncwarp();
+        ws.words[lane] = make_uint2(0u, 0u);
+        __syncwarp();
+        const unsigned nonempty = __ballot_sync(0xffffffffu, len > 0);
+        if (len > 0) {
+          const int d = __popc(nonempty & lt);
+          atomicOr(&ws.words[P >> 5].x, 1u << (P & 31));
+          ws.run_off[d] = st - P;
+          for (int i = (P + 31) >> 5; i * 32 < P + len; i++) ws.words[i].y = (unsigned)d;
+        }
+        __syncwarp();
+        for (int i = 0; i * 32 < mc; i++) {
           const int j = i * 32 + lane;
           const uint2 w = ws.words[i];
-          bool pass = false;
-          uint64_t key = 0;
-          if (j < m) {
-            const int run = (int)w.y + __popc(w.x & le) - 1;
+          float d2 = INFINITY;
+          int id = 0;
+          if (j < mc) {
+            const int run = (int)w.y + __popc(w.x & le_not0);
             const float4 p = __ldg(g.pts + (ws.run_off[run] + j));
-            const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
-            pass = d2 < R2;
-            key = encode(d2, __float_as_int(p.w));
+            d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+            id = __float_as_int(p.w);
           }
-          const unsigned b = __ballot_sync(0xffffffffu, pass);
-          if (pass) {
-            const int pos = n + __popc(b & lt);
-            if (pos < kBuf) ws.keys[pos] = key;
-          }
+          const unsigned b = __ballot_sync(0xffffffffu, d2 < R2);
+          const int pos = n + __popc(b & lt);
+          if (d2 < R2 && pos < kBuf) ws.keys[pos] = encode(d2, id);
           n += __popc(b);
         }
-        if (n >= k || !(R2 < Rmax2)) break;
-        R2 = Rmax2; /* too few inside the estimate: take everything the block guarantees */
-        __syncwarp();
       }
-      if (n > kBuf || (n < k && !complete)) give_up = true;
+      if (dense) { give_up = true; break; }
+      if (n >= k && n <= kBuf) break;
+      if (n < k && !(R2 < io.cutoff2)) break; /* the whole cutoff ball has been searched */
+      if (attempt >= kMaxAttempts) { give_up = true; break; }
+      /* adjust the radius inside the bracket (R2lo: too few, R2hi: more than the buffer holds) */
+      if (n > kBuf) {
+        R2hi = R2;
+        float c = R2 * pow23(__fdividef(1.2f * (float)k + 8.f, (float)n));
+        if (!(c > R2lo)) c = sqrtf(R2lo * R2hi);
+        R2 = c;
+      } else {
+        R2lo = R2;
+        const float c = R2 * pow23(__fdividef(1.4f * (float)k + 16.f, (float)max(n, k >> 2)));
+        if (c < R2hi) {
+          if (c < Rmax2) R2 = c;
+          else if (R2 < Rmax2) take_max = true;           /* everything this block guarantees */
+          else if (h < kMaxH) { h++; take_max = true; }   /* a wider block */
+          else { give_up = true; break; }
+        } else {
+          R2 = sqrtf(R2lo * R2hi);
+        }
+      }
     }
     if (give_up) {
       if (lane == 0) fb_list[atomicAdd(fb_count, 1)] = qi;
@@ -187,8 +236,9 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
     }
     __syncwarp();
 
-    /* ---- selection: the kk smallest keys among the n candidates ------------------------ */
+    /* ---- selection: the kk smallest keys among the n candidates -------------------------- */
     const int kk = min(n, k);
+    const int ns = (n + 31) >> 5; /* occupied register slots per lane */
     int hb[kSlots];
     uint32_t idv[kSlots];
 #pragma unroll
@@ -204,7 +254,7 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
     if (n > k) {
       int mx = 0;
 #pragma unroll
-      for (int s = 0; s < kSlots; s++) if (hb[s] != 0x7fffffff) mx = max(mx, hb[s]);
+      for (int s = 0; s < kSlots; s++) if (s < ns && hb[s] != 0x7fffffff) mx = max(mx, hb[s]);
       int thi = __reduce_max_sync(0xffffffffu, mx), chi = n;
       tlo = -1; clo = 0;
       float flo = 0.f, fhi = __int_as_float(thi);
@@ -214,15 +264,16 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
         if (thi - tlo <= 2) { give_up = true; break; } /* > 32 candidates at one distance: degenerate */
         int ta, tb;
         if (it < 6) {
+          /* two thresholds around the expected position of the k-th candidate */
           const float b = (float)(chi - clo);
-          const float delta = fmaxf(0.9f * sqrtf(b), 2.f);
-          const float fa = (fmaxf((float)k + 0.5f - delta, (float)clo + 0.5f) - (float)clo) / b;
-          const float fb = (fminf((float)k + 0.5f + delta, (float)chi - 0.5f) - (float)clo) / b;
+          const float delta = fmaxf(0.85f * b * rsqrtf(b), 2.f);
+          const float fa = __fdividef(fmaxf((float)k + 0.5f - delta, (float)clo + 0.5f) - (float)clo, b);
+          const float fb = __fdividef(fminf((float)k + 0.5f + delta, (float)chi - 0.5f) - (float)clo, b);
           float Ta, Tb;
           if (first) { /* count ~ dist^3: interpolate in dist²^1.5 */
-            const float vlo = flo * sqrtf(flo), vhi = fhi * sqrtf(fhi);
-            Ta = exp2f(log2f(vlo + (vhi - vlo) * fa) * (2.f / 3.f));
-            Tb = exp2f(log2f(vlo + (vhi - vlo) * fb) * (2.f / 3.f));
+            const float vlo = pow32(flo), vhi = pow32(fhi);
+            Ta = pow23(vlo + (vhi - vlo) * fa);
+            Tb = pow23(vlo + (vhi - vlo) * fb);
           } else {
             Ta = flo + (fhi - flo) * fa;
             Tb = flo + (fhi - flo) * fb;
@@ -235,7 +286,7 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
         }
         int ca = 0, cb = 0;
 #pragma unroll
-        for (int s = 0; s < kSlots; s++) { ca += hb[s] <= ta; cb += hb[s] <= tb; }
+        for (int s = 0; s < kSlots; s++) if (s < ns) { ca += hb[s] <= ta; cb += hb[s] <= tb; }
         ca = __reduce_add_sync(0xffffffffu, ca);
         cb = __reduce_add_sync(0xffffffffu, cb);
         if (k <= ca) { thi = ta; chi = ca; fhi = __int_as_float(ta); }
@@ -254,10 +305,12 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
       int filled = 0;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
-        const bool inb = hb[s] > tlo && hb[s] <= thi;
-        const unsigned b = __ballot_sync(0xffffffffu, inb);
-        if (inb) ws.keys[filled + __popc(b & lt)] = ((uint64_t)(uint32_t)hb[s] << 32) | idv[s];
-        filled += __popc(b);
+        if (s < ns) {
+          const bool inb = hb[s] > tlo && hb[s] <= thi;
+          const unsigned b = __ballot_sync(0xffffffffu, inb);
+          if (inb) ws.keys[filled + __popc(b & lt)] = ((uint64_t)(uint32_t)hb[s] << 32) | idv[s];
+          filled += __popc(b);
+        }
       }
       __syncwarp();
       if (lane < nb) mine = ws.keys[lane];
@@ -266,36 +319,38 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
     }
     const int need = kk - clo; /* accepted from the bracket (0 when n <= k) */
     const bool acc_b = lane < nb && rank < need;
-
-    /* ---- output ------------------------------------------------------------------- */
     int r2b = 0;
 #pragma unroll
-    for (int s = 0; s < kSlots; s++) if (hb[s] <= tlo) r2b = max(r2b, hb[s]);
+    for (int s = 0; s < kSlots; s++) if (s < ns && hb[s] <= tlo) r2b = max(r2b, hb[s]);
     if (acc_b) r2b = max(r2b, (int)(mine >> 32));
     r2b = __reduce_max_sync(0xffffffffu, r2b);
     const float r2 = kk == k ? __int_as_float(r2b) : io.cutoff2;
+
+    /* ---- output ------------------------------------------------------------------- */
     if (!GATHER) {
-      int32_t* ids = io.ids + (size_t)qi * k;
-      float* d2o = io.d2 ? io.d2 + (size_t)qi * k : nullptr;
+      /* accepted entries -> shared memory in slot order, then 8-byte coalesced row stores */
       int base = 0;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
-        const bool a = hb[s] <= tlo;
-        const unsigned b = __ballot_sync(0xffffffffu, a);
-        if (a) {
-          const int pos = base + __popc(b & lt);
-          ids[pos] = (int)idv[s];
-          if (d2o) d2o[pos] = __int_as_float(hb[s]);
+        if (s < ns) {
+          const bool a = hb[s] <= tlo;
+          const unsigned b = __ballot_sync(0xffffffffu, a);
+          if (a) ws.keys[base + __popc(b & lt)] = ((uint64_t)(uint32_t)hb[s] << 32) | idv[s];
+          base += __popc(b);
         }
-        base += __popc(b);
       }
-      if (acc_b) {
-        ids[clo + rank] = (int)(uint32_t)mine;
-        if (d2o) d2o[clo + rank] = __uint_as_float((uint32_t)(mine >> 32));
-      }
-      for (int p = kk + lane; p < k; p += 32) { /* unfilled slots of the candidate list (knn.h:298-306) */
-        ids[p] = -1;
-        if (d2o) d2o[p] = io.cutoff2;
+      if (acc_b) ws.keys[clo + rank] = mine;
+      __syncwarp();
+      int2* ids2 = reinterpret_cast<int2*>(io.ids + (size_t)qi * k); /* k is even: rows are 8-byte aligned */
+      float2* d22 = io.d2 ? reinterpret_cast<float2*>(io.d2 + (size_t)qi * k) : nullptr;
+      for (int p = 2 * lane; p < k; p += 64) {
+        /* unfilled slots of the candidate list keep (cutoff², -1) (knn.h:298-306) */
+        int2 iv = make_int2(-1, -1);
+        float2 dv = make_float2(io.cutoff2, io.cutoff2);
+        if (p < kk) { const uint64_t e = ws.keys[p]; iv.x = (int)(uint32_t)e; dv.x = __uint_as_float((uint32_t)(e >> 32)); }
+        if (p + 1 < kk) { const uint64_t e = ws.keys[p + 1]; iv.y = (int)(uint32_t)e; dv.y = __uint_as_float((uint32_t)(e >> 32)); }
+        ids2[p >> 1] = iv;
+        if (d22) d22[p >> 1] = dv;
       }
       if (io.r2 && lane == 0) io.r2[qi] = r2;
     } else {
@@ -304,12 +359,12 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
       float fr = 0.f, fg = 0.f, fb = 0.f;
 #pragma unroll
       for (int s = 0; s <= kSlots; s++) {
-        bool a; int h; uint32_t id;
-        if (s < kSlots) { a = hb[s] <= tlo; h = hb[s]; id = idv[s]; }
-        else { a = acc_b; h = (int)(mine >> 32); id = (uint32_t)mine; }
+        bool a; int hv; uint32_t id;
+        if (s < kSlots) { a = s < ns && hb[s] <= tlo; hv = hb[s]; id = idv[s]; }
+        else { a = acc_b; hv = (int)(mine >> 32); id = (uint32_t)mine; }
         if (a) {
           const float4 c = __ldg(color4 + id);
-          const float dist = __fsqrt_rn(__int_as_float(h));
+          const float dist = __fsqrt_rn(__int_as_float(hv));
           const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
           const float sc = __fmul_rn(__fmul_rn(brdf, c.w), w);
           fr = __fadd_rn(fr, __fmul_rn(sc, c.x));

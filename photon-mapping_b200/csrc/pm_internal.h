@@ -64,6 +64,8 @@ struct pm_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int64_t launches = 0;
   float last_kernel_ms = 0.f;
+  int64_t last_fallbacks = 0;      /* queries of the last pm_knn / pm_gather answered by the kd-tree kernel */
+  int* fb_count_dev = nullptr;     /* where the last query batch counted them (scratch) */
   pm::Scratch scratch[pm::S_COUNT];
 
   /* returns a device buffer of at least `bytes` in slot `slot` (contents undefined) */

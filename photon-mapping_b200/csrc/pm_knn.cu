@@ -284,18 +284,31 @@ int run_queries(pm_ctx* ctx, const pm_map* map, pmk::QueryIO io, bool gather, bo
   int* perm = nullptr;
   PM_CHECK(sort_queries(ctx, map, io.q, gather ? io.brdf : nullptr, io.nq, &perm));
   io.order = perm;
+  ctx->fb_count_dev = nullptr;
   if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   if (map->grid_pts) {
     int *fb_list = nullptr, *fb_count = nullptr;
     PM_CHECK(ctx->get_scratch(pm::S_MISC1, (size_t)io.nq, &fb_list));
     PM_CHECK(ctx->get_scratch(pm::S_MISC2, (size_t)4, &fb_count));
     PM_CUDA(cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
+    ctx->fb_count_dev = fb_count;
     PM_CHECK(pm::grid_query(ctx, map, io, gather, fb_list, fb_count));
     PM_CHECK(pm::kd_query(ctx, map, io, gather, fb_list, fb_count));
   } else {
     PM_CHECK(pm::kd_query(ctx, map, io, gather, nullptr, nullptr));
   }
   if (time_it) PM_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  return PM_OK;
+}
+
+/* end of a synchronous query call: wait, then read the kernel time and the fallback count */
+int finish_stats(pm_ctx* ctx, const pm_map* map) {
+  int fb = 0;
+  const bool have = map && map->n >= 1;
+  if (have && ctx->fb_count_dev) PM_CUDA(cudaMemcpyAsync(&fb, ctx->fb_count_dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (have) PM_CUDA(cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev0, ctx->ev1));
+  ctx->last_fallbacks = have && ctx->fb_count_dev ? fb : (have ? -1 : 0);
   return PM_OK;
 }
 
@@ -373,8 +386,7 @@ int pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int
   PM_CHECK(pm::stage_out_finish(ctx, o_ids));
   PM_CHECK(pm::stage_out_finish(ctx, o_d2));
   PM_CHECK(pm::stage_out_finish(ctx, o_r2));
-  PM_CUDA(cudaStreamSynchronize(ctx->stream));
-  if (map && map->n >= 1) PM_CUDA(cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev0, ctx->ev1));
+  PM_CHECK(finish_stats(ctx, map));
   return PM_OK;
 }
 
@@ -393,8 +405,7 @@ int pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brd
   PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT0, out_rgb, sizeof(float) * 3 * (size_t)nq, &o));
   PM_CHECK(pm::gather_device(ctx, map, (const float*)h_dev, (const float*)b_dev, nq, k, cutoff_radius, (float*)o.dev, true));
   PM_CHECK(pm::stage_out_finish(ctx, o));
-  PM_CUDA(cudaStreamSynchronize(ctx->stream));
-  if (map && map->n >= 1) PM_CUDA(cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev0, ctx->ev1));
+  PM_CHECK(finish_stats(ctx, map));
   return PM_OK;
 }
 
