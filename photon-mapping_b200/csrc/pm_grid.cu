@@ -36,7 +36,7 @@ namespace {
 using pmk::encode;
 
 constexpr int kWarps = 8;          /* warps (= queries in flight) per CTA */
-constexpr int kBuf = 160;          /* compacted candidates per query */
+constexpr int kBuf = 128;          /* compacted candidates per query */
 constexpr int kSlots = kBuf / 32;  /* candidates per lane in the selection phase */
 constexpr int kMaxScan = 1024;     /* nodes in the 5x5x5 block beyond which the kd-tree kernel takes over */
 constexpr int kWords = kMaxScan / 32;
@@ -75,12 +75,11 @@ __device__ __forceinline__ int cell_idx(float v, float lo, float inv_cell, int n
   return min(max(__float2int_rd((v - lo) * inv_cell), 0), n - 1);
 }
 
-/* x^(2/3) and x^(3/2) for the radius guesses: two MUFU ops, accuracy is irrelevant there */
+/* x^(2/3) for the radius guesses: two MUFU ops, accuracy is irrelevant there */
 __device__ __forceinline__ float pow23(float x) { return __powf(x, 2.f / 3.f); }
-__device__ __forceinline__ float pow32(float x) { return __powf(x, 1.5f); }
 
 template <bool GATHER>
-__global__ void __launch_bounds__(kWarps * 32)
+__global__ void __launch_bounds__(kWarps * 32, 5)
 k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::QueryIO io, int* __restrict__ fb_list,
              int* __restrict__ fb_count) {
   __shared__ WarpScratch scratch[kWarps];
@@ -236,77 +235,109 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
     }
     __syncwarp();
 
-    /* ---- selection: the kk smallest keys among the n candidates -------------------------- */
+    /* ---- selection: the kk smallest keys among the n candidates --------------------------
+     * One 32-bin histogram over dist² (linear bins between the distances at which k -/+ 3 sigma
+     * candidates are expected, everything nearer in bin 0, everything farther in bin 31) finds the
+     * bin holding the k-th candidate; that bin's few candidates are ranked exactly by 64-bit key. */
     const int kk = min(n, k);
     const int ns = (n + 31) >> 5; /* occupied register slots per lane */
-    int hb[kSlots];
+    int hb[kSlots], bin[kSlots];
     uint32_t idv[kSlots];
 #pragma unroll
     for (int s = 0; s < kSlots; s++) {
       const int idx = lane + 32 * s;
-      hb[s] = 0x7fffffff; idv[s] = 0xffffffffu;
-      if (idx < n) { const uint64_t e = ws.keys[idx]; hb[s] = (int)(e >> 32); idv[s] = (uint32_t)e; }
+      hb[s] = 0x7fffffff; idv[s] = 0xffffffffu; bin[s] = 64; /* never accepted */
+      if (s < ns && idx < n) { const uint64_t e = ws.keys[idx]; hb[s] = (int)(e >> 32); idv[s] = (uint32_t)e; bin[s] = 0; }
     }
     __syncwarp();
-    int tlo = 0x7ffffffe, clo = n; /* n <= k: everything is accepted */
+    int kbin = 1, clo = n; /* n <= k: bin 0 = everything is accepted */
     int nb = 0, rank = 0;
     uint64_t mine = ~0ull;
     if (n > k) {
       int mx = 0;
 #pragma unroll
-      for (int s = 0; s < kSlots; s++) if (s < ns && hb[s] != 0x7fffffff) mx = max(mx, hb[s]);
-      int thi = __reduce_max_sync(0xffffffffu, mx), chi = n;
-      tlo = -1; clo = 0;
-      float flo = 0.f, fhi = __int_as_float(thi);
-      bool first = true;
-      int it = 0;
-      while (chi - clo > 32) {
-        if (thi - tlo <= 2) { give_up = true; break; } /* > 32 candidates at one distance: degenerate */
-        int ta, tb;
-        if (it < 6) {
-          /* two thresholds around the expected position of the k-th candidate */
-          const float b = (float)(chi - clo);
-          const float delta = fmaxf(0.85f * b * rsqrtf(b), 2.f);
-          const float fa = __fdividef(fmaxf((float)k + 0.5f - delta, (float)clo + 0.5f) - (float)clo, b);
-          const float fb = __fdividef(fminf((float)k + 0.5f + delta, (float)chi - 0.5f) - (float)clo, b);
-          float Ta, Tb;
-          if (first) { /* count ~ dist^3: interpolate in dist²^1.5 */
-            const float vlo = pow32(flo), vhi = pow32(fhi);
-            Ta = pow23(vlo + (vhi - vlo) * fa);
-            Tb = pow23(vlo + (vhi - vlo) * fb);
-          } else {
-            Ta = flo + (fhi - flo) * fa;
-            Tb = flo + (fhi - flo) * fb;
-          }
-          ta = min(max(__float_as_int(Ta), tlo + 1), thi - 2);
-          tb = min(max(__float_as_int(Tb), ta + 1), thi - 1);
-        } else {
-          const int w3 = (thi - tlo) / 3;
-          ta = tlo + w3; tb = tlo + 2 * w3;
-        }
-        int ca = 0, cb = 0;
+      for (int s = 0; s < kSlots; s++) if (s < ns && bin[s] == 0) mx = max(mx, hb[s]);
+      const float fhi = __int_as_float(__reduce_max_sync(0xffffffffu, mx));
+      /* count(dist² < T) ~ n (T / fhi)^1.5; its spread at the k-th candidate is binomial */
+      const float fk = (float)k, fn = (float)n;
+      const float delta = 3.f * sqrtf(fk * (1.f - __fdividef(fk, fn))) + 2.f;
+      const float Ta = fhi * pow23(__fdividef(fmaxf(fk - delta, 0.5f), fn));
+      const float Tb = fhi * pow23(__fdividef(fminf(fk + delta, fn - 0.5f), fn));
+      const float scale = Tb > Ta ? __fdividef(30.f, Tb - Ta) : 0.f;
+      ws.run_off[lane] = 0; /* the histogram */
+      __syncwarp();
 #pragma unroll
-        for (int s = 0; s < kSlots; s++) if (s < ns) { ca += hb[s] <= ta; cb += hb[s] <= tb; }
-        ca = __reduce_add_sync(0xffffffffu, ca);
-        cb = __reduce_add_sync(0xffffffffu, cb);
-        if (k <= ca) { thi = ta; chi = ca; fhi = __int_as_float(ta); }
-        else if (k <= cb) { tlo = ta; clo = ca; flo = __int_as_float(ta); thi = tb; chi = cb; fhi = __int_as_float(tb); }
-        else { tlo = tb; clo = cb; flo = __int_as_float(tb); }
-        first = false;
-        it++;
+      for (int s = 0; s < kSlots; s++) {
+        if (s < ns && bin[s] == 0) {
+          /* monotone in dist²: subtraction, multiplication by a positive constant, floor, clamp */
+          bin[s] = min(max(__float2int_rd((__int_as_float(hb[s]) - Ta) * scale) + 1, 0), 31);
+          atomicAdd(&ws.run_off[bin[s]], 1);
+        }
       }
-      if (give_up) {
-        if (lane == 0) fb_list[atomicAdd(fb_count, 1)] = qi;
-        __syncwarp();
-        continue;
+      __syncwarp();
+      const int cnt = ws.run_off[lane];
+      int incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
       }
-      /* the bracket (tlo, thi] holds chi - clo <= 32 candidates: one per lane, exact rank by key */
-      nb = chi - clo;
+      kbin = __popc(__ballot_sync(0xffffffffu, incl < k)); /* first bin whose running count reaches k */
+      clo = __shfl_sync(0xffffffffu, incl - cnt, kbin);
+      nb = __shfl_sync(0xffffffffu, cnt, kbin);
+      if (nb > 32) {
+        /* rare (the k-th candidate fell outside the window, or many equal distances): narrow the
+         * bracket (tlo, thi] of dist² bit patterns with pairs of counting thresholds */
+        int a = -1, b2 = 0;
+#pragma unroll
+        for (int s = 0; s < kSlots; s++) {
+          if (s < ns && bin[s] < kbin) a = max(a, hb[s]);
+          if (s < ns && bin[s] <= kbin) b2 = max(b2, hb[s]);
+        }
+        int tlo = __reduce_max_sync(0xffffffffu, a), thi = __reduce_max_sync(0xffffffffu, b2), chi = clo + nb;
+        float flo = tlo < 0 ? 0.f : __int_as_float(tlo), fh = __int_as_float(thi);
+        int it = 0;
+        while (chi - clo > 32) {
+          if (thi - tlo <= 2) { give_up = true; break; } /* > 32 candidates at one distance: degenerate */
+          int ta, tb;
+          if (it < 6) {
+            const float bw = (float)(chi - clo);
+            const float dl = fmaxf(0.85f * bw * rsqrtf(bw), 2.f);
+            const float fa = __fdividef(fmaxf(fk + 0.5f - dl, (float)clo + 0.5f) - (float)clo, bw);
+            const float fb = __fdividef(fminf(fk + 0.5f + dl, (float)chi - 0.5f) - (float)clo, bw);
+            ta = min(max(__float_as_int(flo + (fh - flo) * fa), tlo + 1), thi - 2);
+            tb = min(max(__float_as_int(flo + (fh - flo) * fb), ta + 1), thi - 1);
+          } else {
+            const int w3 = (thi - tlo) / 3;
+            ta = tlo + w3; tb = tlo + 2 * w3;
+          }
+          int ca = 0, cb = 0;
+#pragma unroll
+          for (int s = 0; s < kSlots; s++) if (s < ns) { ca += hb[s] <= ta; cb += hb[s] <= tb; }
+          ca = __reduce_add_sync(0xffffffffu, ca);
+          cb = __reduce_add_sync(0xffffffffu, cb);
+          if (k <= ca) { thi = ta; chi = ca; fh = __int_as_float(ta); }
+          else if (k <= cb) { tlo = ta; clo = ca; flo = __int_as_float(ta); thi = tb; chi = cb; fh = __int_as_float(tb); }
+          else { tlo = tb; clo = cb; flo = __int_as_float(tb); }
+          it++;
+        }
+        if (give_up) {
+          if (lane == 0) fb_list[atomicAdd(fb_count, 1)] = qi;
+          __syncwarp();
+          continue;
+        }
+        nb = chi - clo;
+        kbin = 1;
+#pragma unroll
+        for (int s = 0; s < kSlots; s++)
+          if (s < ns && bin[s] < 64) bin[s] = hb[s] <= tlo ? 0 : (hb[s] <= thi ? 1 : 2);
+      }
+      /* the bracket: nb <= 32 candidates, one per lane, exact rank by key */
       int filled = 0;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
         if (s < ns) {
-          const bool inb = hb[s] > tlo && hb[s] <= thi;
+          const bool inb = bin[s] == kbin;
           const unsigned b = __ballot_sync(0xffffffffu, inb);
           if (inb) ws.keys[filled + __popc(b & lt)] = ((uint64_t)(uint32_t)hb[s] << 32) | idv[s];
           filled += __popc(b);
@@ -319,12 +350,20 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
     }
     const int need = kk - clo; /* accepted from the bracket (0 when n <= k) */
     const bool acc_b = lane < nb && rank < need;
-    int r2b = 0;
+    /* returned radius: the k-th smallest dist² (the last accepted bracket entry), cutoff² if not full */
+    float r2 = io.cutoff2;
+    if (kk == k) {
+      int r2b = 0;
+      if (n > k) {
+        const unsigned last = __ballot_sync(0xffffffffu, acc_b && rank == need - 1);
+        r2b = __shfl_sync(0xffffffffu, (int)(mine >> 32), __ffs(last) - 1);
+      } else {
 #pragma unroll
-    for (int s = 0; s < kSlots; s++) if (s < ns && hb[s] <= tlo) r2b = max(r2b, hb[s]);
-    if (acc_b) r2b = max(r2b, (int)(mine >> 32));
-    r2b = __reduce_max_sync(0xffffffffu, r2b);
-    const float r2 = kk == k ? __int_as_float(r2b) : io.cutoff2;
+        for (int s = 0; s < kSlots; s++) if (s < ns && bin[s] == 0) r2b = max(r2b, hb[s]);
+        r2b = __reduce_max_sync(0xffffffffu, r2b);
+      }
+      r2 = __int_as_float(r2b);
+    }
 
     /* ---- output ------------------------------------------------------------------- */
     if (!GATHER) {
@@ -333,7 +372,7 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
         if (s < ns) {
-          const bool a = hb[s] <= tlo;
+          const bool a = bin[s] < kbin;
           const unsigned b = __ballot_sync(0xffffffffu, a);
           if (a) ws.keys[base + __popc(b & lt)] = ((uint64_t)(uint32_t)hb[s] << 32) | idv[s];
           base += __popc(b);
@@ -360,7 +399,7 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
 #pragma unroll
       for (int s = 0; s <= kSlots; s++) {
         bool a; int hv; uint32_t id;
-        if (s < kSlots) { a = s < ns && hb[s] <= tlo; hv = hb[s]; id = idv[s]; }
+        if (s < kSlots) { a = s < ns && bin[s] < kbin; hv = hb[s]; id = idv[s]; }
         else { a = acc_b; hv = (int)(mine >> 32); id = (uint32_t)mine; }
         if (a) {
           const float4 c = __ldg(color4 + id);
