@@ -147,11 +147,11 @@ def peaks():
 
 
 def traffic_per_launch():
-    """dram bytes per launch of the kNN kernel from the committed ncu capture, or None."""
+    """dram bytes per launch of the kNN kernel (k_grid_query) from the committed ncu capture, or None."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("k_knn_64_dram_bytes_per_launch")
+            return json.load(open(p)).get("k_grid_query_k64_dram_bytes_per_launch")
         except Exception:
             return None
     return None
@@ -244,7 +244,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         dist.barrier()
     torch.cuda.synchronize()
     ctx.reset_launch_count()
-    step_ms, kern_ms = [], []
+    step_ms, kern_ms, fallbacks = [], [], 0
     wall0 = time.perf_counter()
     with torch.cuda.stream(ext_stream):
         for _ in range(args.steps):
@@ -256,6 +256,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             e1.synchronize()
             step_ms.append(e0.elapsed_time(e1))
             kern_ms.append(ctx.last_kernel_ms)
+            fallbacks = max(fallbacks, ctx.last_fallback_count)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -323,7 +324,9 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                     "api": "pm_knn with pinned host buffers (queries in, ids + r2 out)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic_per_launch(), "kernel": "k_knn<64>", "kernel_ms": k_ms,
+                         "traffic": traffic_per_launch(),
+                         "kernel": "k_grid_query<false> (+ k_kd<64> on the queries it hands over)", "kernel_ms": k_ms,
+                         "kd_tree_fallback_queries": int(fallbacks),
                          "algorithmic_bytes_per_launch": BYTES_PER_QUERY * N_QUERIES, "peak_source": peak_src},
             "cpu_baseline": cpu,
             "clocks": clocks,

@@ -9,7 +9,7 @@
  * (the contraction nvcc emits for cukd's dot(d,d) in the reference kernel).
  *
  * B200 design (v1):
- *   - queries are Morton-sorted (30-bit code inside the map's AABB, radix sort of 4-byte ids) so the
+ *   - queries are Morton-sorted (24-bit code inside the map's AABB, radix sort of 4-byte ids) so the
  *     32 lanes of a warp walk nearly the same root-to-leaf paths: node fetches coalesce into a few
  *     sectors and the traversal stays convergent;
  *   - the tree is traversed through a 16-byte (x, y, z, split_dim) copy — one LDG.128 per node
@@ -47,12 +47,12 @@ __global__ void k_morton(const float* __restrict__ q, const float* __restrict__ 
   if (i >= nq) return;
   ids[i] = i;
   /* queries that will not be evaluated (brdf <= 0) sort to the end so that whole warps retire at once */
-  if (skip_if_not_positive && !(skip_if_not_positive[i] > 0.f)) { keys[i] = 0x3FFFFFFFu; return; }
+  if (skip_if_not_positive && !(skip_if_not_positive[i] > 0.f)) { keys[i] = 0x00FFFFFFu; return; }
   uint32_t code = 0;
 #pragma unroll
   for (int d = 0; d < 3; d++) {
     float t = (q[(size_t)i * 3 + d] - box.lo[d]) * box.inv[d];
-    t = fminf(fmaxf(t, 0.f), 1023.f);
+    t = fminf(fmaxf(t, 0.f), 255.f);
     code |= part1by2((uint32_t)t) << d;
   }
   keys[i] = code;
@@ -207,15 +207,15 @@ int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float
   for (int d = 0; d < 3; d++) {
     box.lo[d] = map->bounds[d];
     const float w = map->bounds[3 + d] - map->bounds[d];
-    box.inv[d] = w > 0.f ? 1024.f / w : 0.f;
+    box.inv[d] = w > 0.f ? 256.f / w : 0.f;
   }
   k_morton<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, keys_in, ids_in);
   size_t tb = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_in, keys_out, ids_in, perm, nq, 0, 30, ctx->stream);
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_in, keys_out, ids_in, perm, nq, 0, 24, ctx->stream);
   void* tmp = nullptr;
   PM_CHECK(ctx->get_scratch(pm::S_CUB, tb, &tmp));
-  PM_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, keys_in, keys_out, ids_in, perm, nq, 0, 30, ctx->stream));
-  ctx->launches += 5;
+  PM_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, keys_in, keys_out, ids_in, perm, nq, 0, 24, ctx->stream));
+  ctx->launches += 6; /* k_morton + histogram + scan + 3 onesweep passes */
   *perm_out = perm;
   return PM_OK;
 }
