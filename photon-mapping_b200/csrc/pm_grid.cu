@@ -67,8 +67,11 @@ __device__ __forceinline__ int cell_of(float v, float lo, float inv_cell, int n)
   return (int)fminf(fmaxf(floorf(u), 0.f), (float)(n - 1));
 }
 
-/* x / d for x < 1024 and 1 <= d <= 17 (checked exhaustively): rows of a block per lane */
-__device__ __forceinline__ int div_small(int x, int d) { return (x * ((1 << 16) / d + 1)) >> 16; }
+/* x / d for x < 1024 and 1 <= d <= 17 by multiplication with 2^16 / d + 1 (checked exhaustively):
+ * which row of a block a lane owns */
+__constant__ int c_rdiv[18] = {0, 65537, 32769, 21846, 16385, 13108, 10923, 9363, 8193, 7282, 6554, 5958, 5462,
+                               5042, 4682, 4370, 4097, 3856};
+__device__ __forceinline__ int div_small(int x, int d) { return (x * c_rdiv[d]) >> 16; }
 
 /* cell index of coordinate v: the same floor((v - lo) * inv_cell) the build uses, clamped */
 __device__ __forceinline__ int cell_idx(float v, float lo, float inv_cell, int n) {
@@ -100,8 +103,9 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
       }
     }
     const float qx = io.q[(size_t)qi * 3 + 0], qy = io.q[(size_t)qi * 3 + 1], qz = io.q[(size_t)qi * 3 + 2];
-    const int cx = cell_idx(qx, g.lo[0], g.inv_cell, g.nx), cy = cell_idx(qy, g.lo[1], g.inv_cell, g.ny),
-              cz = cell_idx(qz, g.lo[2], g.inv_cell, g.nz);
+    const float fx = (qx - g.lo[0]) * g.inv_cell, fy = (qy - g.lo[1]) * g.inv_cell, fz = (qz - g.lo[2]) * g.inv_cell;
+    const int cx = min(max(__float2int_rd(fx), 0), g.nx - 1), cy = min(max(__float2int_rd(fy), 0), g.ny - 1),
+              cz = min(max(__float2int_rd(fz), 0), g.nz - 1);
 
     /* ---- candidate search: block of (2h+1)^3 cells, ball of radius sqrt(R2) inside it ------ */
     int h = 2, n = 0;
@@ -111,15 +115,16 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
       const int x0 = max(cx - h, 0), x1 = min(cx + h, g.nx - 1);
       const int y0 = max(cy - h, 0), y1 = min(cy + h, g.ny - 1);
       const int z0 = max(cz - h, 0), z1 = min(cz + h, g.nz - 1);
-      /* G: distance to the nearest block face that is not a face of the grid itself */
-      float G = INFINITY;
-      if (x0 > 0) G = fminf(G, qx - (g.lo[0] + (float)x0 * g.cell));
-      if (x1 < g.nx - 1) G = fminf(G, (g.lo[0] + (float)(x1 + 1) * g.cell) - qx);
-      if (y0 > 0) G = fminf(G, qy - (g.lo[1] + (float)y0 * g.cell));
-      if (y1 < g.ny - 1) G = fminf(G, (g.lo[1] + (float)(y1 + 1) * g.cell) - qy);
-      if (z0 > 0) G = fminf(G, qz - (g.lo[2] + (float)z0 * g.cell));
-      if (z1 < g.nz - 1) G = fminf(G, (g.lo[2] + (float)(z1 + 1) * g.cell) - qz);
-      G -= g.margin;
+      /* G: distance to the nearest block face that is not a face of the grid itself (measured in
+       * cells first; the margin covers the rounding of both this and the build's cell assignment) */
+      float Gc = INFINITY;
+      if (x0 > 0) Gc = fminf(Gc, fx - (float)x0);
+      if (x1 < g.nx - 1) Gc = fminf(Gc, (float)(x1 + 1) - fx);
+      if (y0 > 0) Gc = fminf(Gc, fy - (float)y0);
+      if (y1 < g.ny - 1) Gc = fminf(Gc, (float)(y1 + 1) - fy);
+      if (z0 > 0) Gc = fminf(Gc, fz - (float)z0);
+      if (z1 < g.nz - 1) Gc = fminf(Gc, (float)(z1 + 1) - fz);
+      const float G = Gc * g.cell - g.margin;
       const float Rmax2 = fminf(G > 0.f ? G * G : 0.f, io.cutoff2);
       const int ny_r = y1 - y0 + 1, nrows = ny_r * (z1 - z0 + 1);
       if (attempt == 0) {
@@ -155,7 +160,8 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
           const float dz = fmaxf(fmaxf(zlo - qz, qz - (zlo + g.cell)) - g.margin, 0.f);
           const float dyz2 = dy * dy + dz * dz;
           if (dyz2 < R2) {
-            const float w = __fsqrt_ru(R2 - dyz2) + g.margin;
+            const float t2 = R2 - dyz2; /* > 0; half-width of the ball in this row, rounded up generously */
+            const float w = (t2 < 1e30f ? t2 * rsqrtf(t2) * 1.0001f : INFINITY) + g.margin;
             const int xa = max(cell_idx(qx - w, g.lo[0], g.inv_cell, g.nx), x0);
             const int xb = min(cell_idx(qx + w, g.lo[0], g.inv_cell, g.nx), x1);
             if (xa <= xb) {
@@ -190,18 +196,16 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
         __syncwarp();
         for (int i = 0; i * 32 < mc; i++) {
           const int j = i * 32 + lane;
+          const int jj = min(j, mc - 1); /* lanes past the end re-read the last record and drop it */
           const uint2 w = ws.words[i];
-          float d2 = INFINITY;
-          int id = 0;
-          if (j < mc) {
-            const int run = (int)w.y + __popc(w.x & le_not0);
-            const float4 p = __ldg(g.pts + (ws.run_off[run] + j));
-            d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
-            id = __float_as_int(p.w);
-          }
-          const unsigned b = __ballot_sync(0xffffffffu, d2 < R2);
-          const int pos = n + __popc(b & lt);
-          if (d2 < R2 && pos < kBuf) ws.keys[pos] = encode(d2, id);
+          const int run = (int)w.y + __popc(w.x & le_not0);
+          const float4 p = __ldg(g.pts + (ws.run_off[run] + jj));
+          float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+          if (j >= mc) d2 = INFINITY;
+          const bool pass = d2 < R2;
+          const unsigned b = __ballot_sync(0xffffffffu, pass);
+          /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
+          if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = encode(d2, __float_as_int(p.w));
           n += __popc(b);
         }
       }
