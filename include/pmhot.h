@@ -145,6 +145,16 @@ int  pm_emit_photons(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_
                      pm_photon40* out, int64_t capacity, int64_t* count,
                      int64_t* n_paths, int64_t* n_segments);
 
+/* Same, and also writes one 64-bit key per stored photon: light << 56 | launch index << 8 | ordinal of
+ * the store on its path. Ranks that trace disjoint launch indices (first_photon = rank, photon_stride =
+ * ranks) gather their shards and sort by key to obtain exactly the single-GPU output order.
+ * out and out_keys must both be host or both be device memory. */
+int  pm_emit_photons_keyed(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host, int n_lights,
+                           int64_t casted, int max_depth, int caustics_mode,
+                           uint64_t seed, int rng_mode, int64_t first_photon, int64_t photon_stride,
+                           pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
+                           int64_t* n_paths, int64_t* n_segments);
+
 /* pass-1 → pass-2 record conversion done by ray-tracer/src/hostCode.cu:65-83:
  * global map = non-caustic (power 1.0) followed by caustic (power 0.5); caustic map = caustic (0.5).
  * `out_global` needs n_global + n_caustic records, `out_caustic` n_caustic. Device or host pointers. */

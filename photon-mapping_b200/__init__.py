@@ -60,6 +60,11 @@ _SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p,
          c_int64, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64)],
     ),
+    "pm_emit_photons_keyed": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p,
+         c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64)],
+    ),
     "pm_photons_to_maps": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "pm_map_build": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, POINTER(c_void_p)]),
     "pm_map_from_tree": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_void_p)]),
@@ -287,6 +292,20 @@ class Scene:
         occ = np.empty(len(rays), np.uint8)
         _check(lib().pm_trace_occluded(self.ctx.handle, self.handle, rays.ctypes.data, len(rays), occ.ctypes.data))
         return occ
+
+    def emit_photons_keyed(self, lights: np.ndarray, casted: int, max_depth: int, caustics: bool, seed: int = 0,
+                           rng_mode: int = RNG_LCG_PARITY, first_photon: int = 0, photon_stride: int = 1):
+        """pm_emit_photons_keyed on host buffers: (photons[:count], keys[:count] uint64, n_paths, n_segments)."""
+        lights = np.ascontiguousarray(lights, LIGHT)
+        capacity = (int(casted) // max(1, photon_stride) + len(lights) + 1) * max(1, int(max_depth))
+        out = np.empty(capacity, PHOTON40)
+        keys = np.empty(capacity, np.uint64)
+        count, npaths, nseg = c_int64(0), c_int64(0), c_int64(0)
+        _check(lib().pm_emit_photons_keyed(self.ctx.handle, self.handle, lights.ctypes.data, len(lights), casted, max_depth,
+                                           1 if caustics else 0, seed, rng_mode, first_photon, photon_stride,
+                                           out.ctypes.data, keys.ctypes.data, capacity, ctypes.byref(count),
+                                           ctypes.byref(npaths), ctypes.byref(nseg)))
+        return out[: count.value], keys[: count.value], npaths.value, nseg.value
 
     def emit_photons(self, lights: np.ndarray, casted: int, max_depth: int, caustics: bool, seed: int = 0,
                      rng_mode: int = RNG_LCG_PARITY, first_photon: int = 0, photon_stride: int = 1, out=None,

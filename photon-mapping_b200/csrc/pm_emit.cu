@@ -138,9 +138,18 @@ k_walk(const EmitParams P, unsigned long long* __restrict__ next_path, pm_photon
 }
 
 /* path p copies its counts[p] records to dst[offsets[p] - base ...) while below `limit` records */
+/* key of a stored photon: light << 56 | launch index << 8 | ordinal of the store on its path — sorting the
+ * shards of several ranks by it restores the single-GPU output order */
+struct KeyInfo {
+  uint64_t* keys; /* NULL: no keys wanted */
+  int n_lights;
+  int64_t light_first[kMaxLights + 1];
+  int64_t first_photon, photon_stride, batch_begin;
+};
+
 __global__ void k_compact(int64_t n_paths, int slots_per_path, const pm_photon40* __restrict__ slots,
                           const int* __restrict__ counts, const int64_t* __restrict__ offsets, int64_t limit,
-                          pm_photon40* __restrict__ dst) {
+                          pm_photon40* __restrict__ dst, const KeyInfo ki) {
   /* 5 threads per path-record word pair: thread t handles 8-byte word (t % 5) of record stream */
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t p = t / 5;
@@ -150,9 +159,17 @@ __global__ void k_compact(int64_t n_paths, int slots_per_path, const pm_photon40
   const int64_t o = offsets[p];
   const float2* src = reinterpret_cast<const float2*>(slots + (size_t)p * slots_per_path);
   float2* out = reinterpret_cast<float2*>(dst);
+  int l = 0;
+  uint64_t idx = 0;
+  if (ki.keys && w == 0) {
+    const int64_t g = ki.batch_begin + p;
+    while (l + 1 < ki.n_lights && g >= ki.light_first[l + 1]) l++;
+    idx = (uint64_t)(ki.first_photon + (g - ki.light_first[l]) * ki.photon_stride);
+  }
   for (int k = 0; k < c; k++) {
     if (o + k >= limit) break;
     out[(size_t)(o + k) * 5 + w] = src[(size_t)k * 5 + w];
+    if (ki.keys && w == 0) ki.keys[o + k] = ((uint64_t)l << 56) | (idx << 8) | (uint64_t)k;
   }
 }
 
@@ -179,10 +196,10 @@ __global__ void k_conv44(int64_t n, const pm_photon40* __restrict__ in, float po
 
 extern "C" {
 
-int pm_emit_photons(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_lights, int64_t casted,
-                    int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
-                    int64_t photon_stride, pm_photon40* out, int64_t capacity, int64_t* count, int64_t* n_paths,
-                    int64_t* n_segments) {
+static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_lights, int64_t casted,
+                     int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
+                     int64_t photon_stride, pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
+                     int64_t* n_paths, int64_t* n_segments) {
   PM_REQUIRE(ctx && scene && count, "ctx/scene/count is NULL");
   PM_REQUIRE(n_lights >= 0 && n_lights <= kMaxLights, "n_lights out of range (max 64)");
   PM_REQUIRE(n_lights == 0 || lights, "lights is NULL");
@@ -242,6 +259,12 @@ int pm_emit_photons(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, 
   PM_CUDA(cudaMemsetAsync(ctrs, 0, sizeof(unsigned long long) * 4, st));
 
   const bool dev_out = pm::is_device_ptr(out);
+  PM_REQUIRE(!out_keys || capacity == 0 || pm::is_device_ptr(out_keys) == dev_out, "out and out_keys must both be host or both be device memory");
+  KeyInfo ki;
+  memset(&ki, 0, sizeof ki);
+  ki.n_lights = n_lights;
+  for (int l = 0; l <= n_lights; l++) ki.light_first[l] = P.light_first[l];
+  ki.first_photon = first_photon; ki.photon_stride = photon_stride;
   int blocks_per_sm = 0;
   PM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_walk, 128, 0));
   if (blocks_per_sm < 1) blocks_per_sm = 1;
@@ -276,12 +299,20 @@ int pm_emit_photons(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, 
     const int64_t take = batch_total < room ? batch_total : room;
     if (take > 0) {
       pm_photon40* dst = nullptr;
-      if (dev_out) dst = out + written;
-      else PM_CHECK(ctx->get_scratch(pm::S_BUILD3, (size_t)take, &dst));
-      k_compact<<<(unsigned)pm::div_up(nb * 5, 256), 256, 0, st>>>(nb, P.slots_per_path, slots, counts, offsets, take, dst);
+      uint64_t* kdst = nullptr;
+      if (dev_out) { dst = out + written; kdst = out_keys ? out_keys + written : nullptr; }
+      else {
+        PM_CHECK(ctx->get_scratch(pm::S_BUILD3, (size_t)take, &dst));
+        if (out_keys) PM_CHECK(ctx->get_scratch(pm::S_BUILD4, (size_t)take, &kdst));
+      }
+      ki.keys = kdst; ki.batch_begin = b0;
+      k_compact<<<(unsigned)pm::div_up(nb * 5, 256), 256, 0, st>>>(nb, P.slots_per_path, slots, counts, offsets, take, dst, ki);
       ctx->launches++;
       PM_CUDA(cudaGetLastError());
-      if (!dev_out) PM_CUDA(cudaMemcpyAsync(out + written, dst, sizeof(pm_photon40) * (size_t)take, cudaMemcpyDeviceToHost, st));
+      if (!dev_out) {
+        PM_CUDA(cudaMemcpyAsync(out + written, dst, sizeof(pm_photon40) * (size_t)take, cudaMemcpyDeviceToHost, st));
+        if (out_keys) PM_CUDA(cudaMemcpyAsync(out_keys + written, kdst, sizeof(uint64_t) * (size_t)take, cudaMemcpyDeviceToHost, st));
+      }
       PM_CUDA(cudaStreamSynchronize(st));
     }
     written += batch_total;
@@ -297,6 +328,23 @@ int pm_emit_photons(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, 
     return PM_ERR_CAPACITY;
   }
   return PM_OK;
+}
+
+int pm_emit_photons(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_lights, int64_t casted,
+                    int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
+                    int64_t photon_stride, pm_photon40* out, int64_t capacity, int64_t* count, int64_t* n_paths,
+                    int64_t* n_segments) {
+  return emit_impl(ctx, scene, lights, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
+                   photon_stride, out, nullptr, capacity, count, n_paths, n_segments);
+}
+
+int pm_emit_photons_keyed(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_lights, int64_t casted,
+                          int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
+                          int64_t photon_stride, pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
+                          int64_t* n_paths, int64_t* n_segments) {
+  PM_REQUIRE(out_keys || capacity == 0, "out_keys is NULL");
+  return emit_impl(ctx, scene, lights, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
+                   photon_stride, out, out_keys, capacity, count, n_paths, n_segments);
 }
 
 int pm_photons_to_maps(pm_ctx* ctx, const pm_photon40* global_in, int64_t n_global, const pm_photon40* caustic_in,

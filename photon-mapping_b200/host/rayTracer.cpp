@@ -1,0 +1,111 @@
+// rayTracer — the render pass host (drop-in for ray-tracer/src/hostCode.cu:180-246).
+// Reads the same config.toml keys ([camera], [data], [ray-tracer]), the scene, and the two photon text
+// files written by photonMapping; builds the two photon maps (≙ cukd::buildTree ×2, hostCode.cu:93-98),
+// renders through libpmhot (≙ owlRayGenLaunch2D, :231-237) and writes the PNG (:239-240).
+//
+//   rayTracer [config.toml]
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <iostream>
+
+#include "pm_assets.hpp"
+#include "pm_config.hpp"
+#include "pm_png.hpp"
+
+#define LOG(message) std::cout << "\033[1;37m#pm.host: " << message << "\033[0m" << std::endl
+#define LOG_OK(message) std::cout << "\033[1;32m#pm.host: " << message << "\033[0m" << std::endl
+
+static void check(int rc) {
+  if (rc != PM_OK) throw std::runtime_error(std::string("libpmhot: ") + pm_last_error());
+}
+
+struct V3 { float x, y, z; };
+static V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+static V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+static V3 operator*(float s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+// owl/common/math/vec.h:330-356: cross, dot = (x*x + y*y) + z*z, normalize = v * (1 / sqrt(dot))
+static V3 cross(V3 a, V3 b) { return {a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y}; }
+static V3 normalize(V3 v) { return (1.f / std::sqrt(v.x * v.x + v.y * v.y + v.z * v.z)) * v; }
+
+// setupCamera (ray-tracer/src/hostCode.cu:100-108): cos(fovy) scales the image plane
+static pm_camera setup_camera(V3 from, V3 at, V3 up, float fovy, int W, int H) {
+  const float aspect = W / static_cast<float>(H);
+  const float cosFovy = std::cos(fovy);
+  V3 d00 = normalize(at - from);
+  const V3 du = (cosFovy * aspect) * normalize(cross(d00, up));
+  const V3 dv = cosFovy * normalize(cross(du, d00));
+  d00 = d00 - 0.5f * (du + dv);
+  pm_camera c{{from.x, from.y, from.z}, {d00.x, d00.y, d00.z}, {du.x, du.y, du.z}, {dv.x, dv.y, dv.z}};
+  return c;
+}
+
+static std::vector<pm_photon40> read_photons(const std::string& path) {
+  int64_t n = 0;
+  check(pm_photons_read_text(path.c_str(), nullptr, 0, &n));
+  std::vector<pm_photon40> v((size_t)n);
+  if (n) check(pm_photons_read_text(path.c_str(), v.data(), n, &n));
+  return v;
+}
+
+int main(int argc, char** argv) {
+  try {
+    const std::string config_path = argc > 1 ? argv[1] : "../config.toml";
+    LOG("Loading Config file...");
+    const pmh::Config cfg = pmh::Config::load(config_path);
+    const std::string global_file = cfg.str("data", "photons_file");
+    const std::string caustic_file = cfg.str("data", "caustics_photons_file");
+    const std::string model_path = cfg.str("data", "model_path");
+    const auto at = cfg.array("camera", "look_at", 3), from = cfg.array("camera", "look_from", 3), up = cfg.array("camera", "look_up", 3);
+    const float fovy = (float)cfg.num("camera", "fovy");
+    const auto sky = cfg.array("ray-tracer", "sky_colour", 3);
+    const std::string output = cfg.str("ray-tracer", "output_filename");
+    const auto fb_size = cfg.array("ray-tracer", "fb_size", 2);
+    const int W = (int)fb_size[0], H = (int)fb_size[1];
+    const int spp = (int)cfg.integer("ray-tracer", "samples_per_pixel");
+    const int depth = (int)cfg.integer("ray-tracer", "depth");
+
+    LOG("Loading Model...");
+    pmh::World world = pmh::import_scene(model_path);
+    pm_ctx* ctx = nullptr;
+    pm_scene* scene = nullptr;
+    check(pm_ctx_create(0, &ctx));
+    check(pm_scene_create(ctx, world.verts.data(), (int)(world.verts.size() / 3), world.tris.data(), (int)(world.tris.size() / 3),
+                          world.tri_mesh.data(), world.mats.data(), (int)world.mats.size(), &scene));
+
+    // loadPhotons (hostCode.cu:54-99)
+    const std::vector<pm_photon40> g40 = read_photons(global_file), c40 = read_photons(caustic_file);
+    printf("Loaded %d photons and %d caustic photons\n", (int)g40.size(), (int)c40.size());
+    std::vector<pm_photon44> g44(g40.size() + c40.size()), c44(c40.size());
+    check(pm_photons_to_maps(ctx, g40.data(), (int64_t)g40.size(), c40.data(), (int64_t)c40.size(), g44.data(), c44.data()));
+    pm_map *gmap = nullptr, *cmap = nullptr;
+    float gb[6], cb[6];
+    const auto t0 = std::chrono::steady_clock::now();
+    check(pm_map_build(ctx, g44.data(), (int64_t)g44.size(), gb, &gmap));
+    check(pm_map_build(ctx, c44.data(), (int64_t)c44.size(), cb, &cmap));
+    const auto t1 = std::chrono::steady_clock::now();
+    printf("Photon maps built in %.3f ms\n", std::chrono::duration<double, std::milli>(t1 - t0).count());
+
+    const pm_camera cam = setup_camera({(float)from[0], (float)from[1], (float)from[2]}, {(float)at[0], (float)at[1], (float)at[2]},
+                                       {(float)up[0], (float)up[1], (float)up[2]}, fovy, W, H);
+    const float sky3[3] = {(float)sky[0], (float)sky[1], (float)sky[2]};
+    std::vector<uint32_t> fb((size_t)W * H, 0u);
+    LOG("Launching...");
+    const auto t2 = std::chrono::steady_clock::now();
+    check(pm_render(ctx, scene, world.light_sources.data(), (int)world.light_sources.size(), gmap, cmap, &cam, W, H, spp, depth, sky3,
+                    0, (int64_t)W * H, fb.data()));
+    const auto t3 = std::chrono::steady_clock::now();
+    printf("Rendered in %.3f ms (gather kernels %.3f ms)\n", std::chrono::duration<double, std::milli>(t3 - t2).count(),
+           pm_ctx_last_kernel_ms(ctx));
+    if (!pmh::write_png_rgba8(output, fb.data(), W, H)) throw std::runtime_error("cannot write " + output);
+    LOG_OK("Written rendered frame buffer to file " << output);
+    pm_map_destroy(gmap);
+    pm_map_destroy(cmap);
+    pm_scene_destroy(scene);
+    pm_ctx_destroy(ctx);
+    return 0;
+  } catch (const std::exception& e) {
+    std::cerr << "rayTracer: " << e.what() << std::endl;
+    return 2;
+  }
+}

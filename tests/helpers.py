@@ -213,3 +213,121 @@ def oracle_render(orc, sc, gmap, cmap, cam, W, H, spp, depth, sky=(1, 1, 1), beg
                    vp(cmap) if cmap is not None and len(cmap) else None, 0 if cmap is None else len(cmap),
                    vp(cam), W, H, spp, depth, vp(sky), begin, end, vp(fb), vp(rgb))
     return fb, rgb
+
+
+# ---- C++ hosts (photon-mapping_b200/host) -------------------------------------------------------
+HOST_DIR = os.path.join(ROOT, "photon-mapping_b200", "host")
+
+
+def write_glb(path, meshes, node_transforms=None):
+    """Minimal binary glTF writer for tests. meshes: list of (material_name, verts[nv,3] f32, tris[nt,3]);
+    node_transforms: optional list of dicts (translation / rotation / scale) per mesh node."""
+    import json
+    import struct
+
+    bin_parts, views, accessors, gl_meshes, nodes, materials = [], [], [], [], [], []
+    off = 0
+    for i, (name, v, t) in enumerate(meshes):
+        v = np.ascontiguousarray(v, np.float32)
+        idx = np.ascontiguousarray(t, np.uint32).reshape(-1)
+        for data, target in ((v.tobytes(), 34962), (idx.tobytes(), 34963)):
+            pad = (-len(data)) % 4
+            views.append({"buffer": 0, "byteOffset": off, "byteLength": len(data), "target": target})
+            bin_parts.append(data + b"\0" * pad)
+            off += len(data) + pad
+        accessors.append({"bufferView": 2 * i, "componentType": 5126, "count": len(v), "type": "VEC3",
+                          "min": v.min(0).tolist(), "max": v.max(0).tolist()})
+        accessors.append({"bufferView": 2 * i + 1, "componentType": 5125, "count": len(idx), "type": "SCALAR"})
+        materials.append({"name": name})
+        gl_meshes.append({"primitives": [{"attributes": {"POSITION": 2 * i}, "indices": 2 * i + 1, "material": i}]})
+        node = {"mesh": i, "name": f"node{i}"}
+        if node_transforms and node_transforms[i]:
+            node.update(node_transforms[i])
+        nodes.append(node)
+    root = {"name": "root", "children": list(range(len(nodes)))}
+    nodes.append(root)
+    j = {"asset": {"version": "2.0"}, "scene": 0, "scenes": [{"nodes": [len(nodes) - 1]}], "nodes": nodes,
+         "meshes": gl_meshes, "materials": materials, "accessors": accessors, "bufferViews": views,
+         "buffers": [{"byteLength": off}]}
+    js = json.dumps(j).encode()
+    js += b" " * ((-len(js)) % 4)
+    blob = b"".join(bin_parts)
+    total = 12 + 8 + len(js) + 8 + len(blob)
+    with open(path, "wb") as f:
+        f.write(struct.pack("<III", 0x46546C67, 2, total))
+        f.write(struct.pack("<II", len(js), 0x4E4F534A) + js)
+        f.write(struct.pack("<II", len(blob), 0x004E4942) + blob)
+
+
+def write_scene_files(dirpath, sc, name="scene", node_transforms=None):
+    """Writes <dir>/<name>.glb, <name>.mtl and lights.txt for a fixture scene dict (load_scene); returns the glb path."""
+    meshes = []
+    for mi in range(len(sc["mats"])):
+        sel = sc["tri_mesh"] == mi
+        tris = sc["tris"][sel]
+        used, inv = np.unique(tris.reshape(-1), return_inverse=True)
+        meshes.append((f"mat{mi}", sc["verts"][used], inv.reshape(-1, 3)))
+    glb = os.path.join(dirpath, name + ".glb")
+    write_glb(glb, meshes, node_transforms)
+    with open(os.path.join(dirpath, name + ".mtl"), "w") as f:
+        f.write("# material_name albedo_r albedo_g albedo_b diffuse specular transmission ior\n\n")
+        for mi, m in enumerate(sc["mats"]):
+            f.write(f"mat{mi} {m['albedo'][0]:.9g} {m['albedo'][1]:.9g} {m['albedo'][2]:.9g} {m['diffuse']:.9g} "
+                    f"{m['specular']:.9g} {m['transmission']:.9g} {m['refraction_idx']:.9g}\n")
+    with open(os.path.join(dirpath, "lights.txt"), "w") as f:
+        f.write("# posx posy posz colourr colourg colourb power\n")
+        for l in sc["lights"]:
+            f.write(" ".join(f"{x:.9g}" for x in (*l["pos"], *l["rgb"], l["power"])) + "\n")
+    return glb
+
+
+def write_config(path, model, photons, caustics, out_png, W=64, H=48, spp=1, depth=1, max_depth=6, casted=(20000, 10000),
+                 camera=((80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87)):
+    frm, at, up, fovy = camera
+    with open(path, "w") as f:
+        f.write(f"""[camera]
+look_from = [{frm[0]}, {frm[1]}, {frm[2]}]
+look_at = [{at[0]}, {at[1]}, {at[2]}]
+look_up = [{up[0]}, {up[1]}, {up[2]}]
+fovy = {fovy}
+
+[data]
+photons_file = "{photons}"   # written by photonMapping
+caustics_photons_file = "{caustics}"
+model_path = "{model}"
+
+[ray-tracer]
+sky_colour = [1.0, 1.0, 1.0]
+output_filename = "{out_png}"
+fb_size = [{W}, {H}]
+samples_per_pixel = {spp}
+depth = {depth}
+
+[photon-mapper]
+max_depth = {max_depth}
+casted_diffuse_photons = {casted[0]:_}
+casted_caustics_photons = {casted[1]:_}
+""")
+
+
+def read_png_rgba8(path):
+    """Decoder for the PNGs the hosts write (8-bit RGBA, filter 0)."""
+    import struct
+    import zlib
+
+    b = open(path, "rb").read()
+    assert b[:8] == b"\x89PNG\r\n\x1a\n"
+    off, idat, W, H = 8, b"", 0, 0
+    while off < len(b):
+        n, typ = struct.unpack(">I4s", b[off:off + 8])
+        data = b[off + 8:off + 8 + n]
+        assert zlib.crc32(typ + data) == struct.unpack(">I", b[off + 8 + n:off + 12 + n])[0]
+        if typ == b"IHDR":
+            W, H, depth, ctype = struct.unpack(">IIBB", data[:10])
+            assert depth == 8 and ctype == 6
+        elif typ == b"IDAT":
+            idat += data
+        off += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(H, 1 + 4 * W)
+    assert (raw[:, 0] == 0).all()
+    return np.ascontiguousarray(raw[:, 1:]).view("<u4").reshape(H, W)

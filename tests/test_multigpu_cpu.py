@@ -1,0 +1,101 @@
+"""Host-side multi-GPU logic on the CPU: world_size-2 gloo process group. The device work is
+replaced by a deterministic fake emitter with the same contract as pm_emit_photons_keyed (records + keys
+for launch indices first, first + stride, ...), so what is tested is the sharding arithmetic, the
+variable-length all-gather and the key merge that restores the single-GPU order."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import __graft_entry__ as graft
+
+LIGHT = np.dtype([("pos", "<f4", 3), ("rgb", "<f4", 3), ("power", "<f8")])
+
+
+def _lights():
+    l = np.zeros(3, LIGHT)
+    l["power"] = [10.0, 2.5, 7.5]
+    return l
+
+
+def fake_emit(sizes, first, stride):
+    """records (uint8[n,40]) and keys (uint64[n]) for launch indices first, first+stride, ... of every light."""
+    rec, keys = [], []
+    for l, n in enumerate(sizes):
+        for i in range(first, n, stride):
+            stores = (i * 2654435761 + l * 97) % 4  # 0..3 stored photons on this path
+            for k in range(stores):
+                key = (l << 56) | (i << 8) | k
+                keys.append(key)
+                rec.append(np.frombuffer(np.random.default_rng(key % (2**32)).bytes(40), np.uint8))
+    if not rec:
+        return np.zeros((0, 40), np.uint8), np.zeros(0, np.uint64)
+    return np.stack(rec), np.array(keys, np.uint64)
+
+
+def test_shard_arithmetic():
+    mg = graft.load_package_module("multigpu")
+    assert [mg.shard_range(10, r, 4) for r in range(4)] == [(0, 3), (3, 6), (6, 8), (8, 10)]
+    assert mg.shard_range(0, 0, 2) == (0, 0)
+    for total in (1, 7, 64, 1001):
+        for world in (1, 2, 3, 8):
+            spans = [mg.shard_range(total, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == total
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+    sizes = mg.light_launch_sizes(_lights(), 200000)
+    assert sizes == [100000, 25000, 75000]  # int(casted / 20) = 10000 per watt (hostCode.cu:102-110)
+    for world in (1, 2, 3, 8):
+        assert sum(mg.rank_path_count(sizes, r, world) for r in range(world)) == sum(sizes)
+    assert mg.light_launch_sizes(_lights(), 7) == [0, 0, 0]  # truncation to 0 photons per watt
+
+
+def test_merge_restores_single_gpu_order():
+    mg = graft.load_package_module("multigpu")
+    sizes = [40, 13, 27]
+    full_rec, full_keys = fake_emit(sizes, 0, 1)
+    for world in (2, 3, 5):
+        shards = [fake_emit(sizes, r, world) for r in range(world)]
+        rec, keys = mg.merge_shards([s[0] for s in shards], [s[1] for s in shards])
+        assert np.array_equal(keys, full_keys) and np.array_equal(rec, full_rec)
+
+
+def _worker(rank, world, port, sizes, out_dir):
+    import torch
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    mg = graft.load_package_module("multigpu")
+    rec, keys = fake_emit(sizes, rank, world)
+    all_rec, all_keys = mg.allgather_photons(torch.from_numpy(rec.copy()).reshape(-1), torch.from_numpy(keys.view(np.int64).copy()))
+    np.save(os.path.join(out_dir, f"rec{rank}.npy"), all_rec.numpy())
+    np.save(os.path.join(out_dir, f"key{rank}.npy"), all_keys.numpy())
+    # stage 3: disjoint pixel ranges merged by a sum
+    W, H = 37, 11
+    b, e = mg.shard_range(W * H, rank, world)
+    fb = np.zeros(W * H, np.int64)
+    fb[b:e] = (np.arange(b, e) * 2654435761) % (2**32)
+    t = torch.from_numpy(fb)
+    dist.all_reduce(t)
+    np.save(os.path.join(out_dir, f"fb{rank}.npy"), t.numpy())
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_allgather_and_tiles(tmp_path):
+    import torch.multiprocessing as mp
+
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    sizes = [50, 0, 21]
+    world = 2
+    mp.spawn(_worker, args=(world, port, sizes, str(tmp_path)), nprocs=world, join=True)
+    full_rec, full_keys = fake_emit(sizes, 0, 1)
+    for r in range(world):
+        assert np.array_equal(np.load(tmp_path / f"key{r}.npy").view(np.uint64), full_keys)
+        assert np.array_equal(np.load(tmp_path / f"rec{r}.npy"), full_rec)
+        want = (np.arange(37 * 11) * 2654435761) % (2**32)
+        assert np.array_equal(np.load(tmp_path / f"fb{r}.npy"), want)
