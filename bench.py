@@ -157,6 +157,56 @@ def traffic_per_launch():
     return None
 
 
+def run_stage_extras(pkg, ctx):
+    """Secondary figures of the metric (photons traced/s, fused-gather queries/s) on the reference's Cornell
+    box (tests/golden/scene_cornell_box.npz, extracted from assets/models/cornell-box): stage 1 at 4 M cast
+    photons (counter RNG, max_depth 8), C1 render (200 k + 100 k photons, LCG parity RNG, k = 50, 512x512)."""
+    import torch
+
+    z = np.load(os.path.join(ROOT, "tests", "golden", "scene_cornell_box.npz"))
+    mats = z["mats"].view(pkg.MATERIAL).reshape(-1)
+    lights = z["lights"].view(pkg.LIGHT).reshape(-1)
+    scene = pkg.Scene(ctx, z["verts"], z["tris"], z["tri_mesh"], mats)
+    out = {}
+    # ---- stage 1: device-resident output, two passes timed after one warm-up -------------------------
+    casted, depth = 4_000_000, 8
+    cap = casted * depth
+    d_out = torch.empty(cap * 40, dtype=torch.uint8, device="cuda")
+    res = []
+    for it in range(3):
+        t0 = time.perf_counter()
+        _, n, paths, segs = scene.emit_photons(lights, casted, depth, False, seed=1, rng_mode=pkg.RNG_COUNTER, out=d_out, capacity=cap)
+        wall = time.perf_counter() - t0
+        res.append((ctx.last_kernel_ms, wall, n, paths, segs))
+    k_ms, wall, n, paths, segs = min(res[1:])
+    out["stage1_cornell"] = {"casted": casted, "max_depth": depth, "paths": paths, "segments": segs, "stored": n,
+                             "walk_kernel_ms": k_ms, "call_ms": 1e3 * wall, "paths_per_s": paths / wall,
+                             "segments_per_s": segs / wall, "stored_photons_per_s": n / wall,
+                             "algorithmic_GBps": (96.0 * segs + 40.0 * n) / wall / 1e9}
+    # ---- C1: 200 k + 100 k cast photons, maps, 512x512 render (spp 1, depth 1) ----------------------
+    g40, ng, _, _ = scene.emit_photons(lights, 200_000, 10, False)
+    c40, nc, _, _ = scene.emit_photons(lights, 100_000, 10, True)
+    g44, c44 = pkg.photons_to_maps(ctx, g40, c40)
+    t0 = time.perf_counter()
+    gmap = pkg.PhotonMap.build(ctx, g44)
+    cmap = pkg.PhotonMap.build(ctx, c44) if len(c44) else None
+    build_ms = 1e3 * (time.perf_counter() - t0)
+    W = H = 512
+    cam = pkg.make_camera((80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87, W, H)
+    best = None
+    for it in range(3):
+        t0 = time.perf_counter()
+        scene.render(lights, gmap, cmap, cam, W, H, 1, 1)
+        wall = time.perf_counter() - t0
+        if it and (best is None or wall < best[0]):
+            best = (wall, ctx.last_kernel_ms)
+    queries = W * H * 21  # 1 caustic + 20 final-gather queries per pixel (upper bound: misses are skipped)
+    out["c1_render"] = {"photons_global_map": int(len(g44)), "photons_caustic_map": int(len(c44)), "k": 50, "fb": [W, H],
+                        "maps_build_ms": build_ms, "render_ms": 1e3 * best[0], "global_gather_kernel_ms": best[1],
+                        "gather_queries_issued_upper_bound": queries, "pixels_per_s": W * H / best[0]}
+    return out
+
+
 def run_reference(args, rank: int):
     """CPU arm: oracle port of the reference's kNN (no GPU work at all)."""
     if rank != 0:
@@ -334,6 +384,11 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                              "photons_per_s": N_PHOTONS / (build_ms_warm * 1e-3)},
             "wall_ms_timed_region": wall_ms,
         }
+        if world == 1 and not args.no_stage_extras:
+            try:
+                line["stages"] = run_stage_extras(pkg, ctx)
+            except Exception as e:  # secondary figures must never cost the headline line
+                line["stages"] = {"error": repr(e)}
         print(json.dumps(line), flush=True)
     pmap.close()
     ctx.close()
@@ -348,6 +403,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-stage-extras", action="store_true", help="skip the stage-1 / C1-render secondary figures")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
