@@ -73,6 +73,8 @@ def load_oracle():
                                 ctypes.c_float, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     L.orc_kd_build.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
     L.orc_omp_threads.restype = ctypes.c_int
+    L.orc_omp_set_threads.argtypes = [ctypes.c_int]
+    L.orc_omp_set_threads(len(os.sched_getaffinity(0)))  # torchrun exports OMP_NUM_THREADS=1
     return L
 
 

@@ -284,5 +284,7 @@ int orc_kd_check(const pm_photon44* nodes, int n) {
 }
 
 int orc_omp_threads(void) { return omp_get_max_threads(); }
+/* launchers (torchrun) export OMP_NUM_THREADS=1; the timed CPU arm uses every host thread */
+void orc_omp_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 }  // extern "C"
