@@ -111,6 +111,11 @@ void pm_ctx_destroy(pm_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   for (auto& s : ctx->scratch)
     if (s.ptr) cudaFree(s.ptr);
+  if (ctx->copy_stream) {
+    cudaStreamSynchronize(ctx->copy_stream);
+    cudaStreamDestroy(ctx->copy_stream);
+    for (int i = 0; i < 2; i++) { cudaEventDestroy(ctx->ev_kernel[i]); cudaEventDestroy(ctx->ev_copy[i]); }
+  }
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->stream);

@@ -312,6 +312,48 @@ int finish_stats(pm_ctx* ctx, const pm_map* map) {
   return PM_OK;
 }
 
+/* pm_knn with HOST output buffers: the batch is cut into chunks so that the device-to-host copy of
+ * chunk c (PCIe, the slow part: k * 8 bytes per query) overlaps the kernels of chunk c + 1. Outputs are
+ * staged in two alternating device buffers; a chunk's kernels wait for the copy that last used its buffer. */
+constexpr int64_t kPipeChunk = 131072;
+
+int knn_pipelined(pm_ctx* ctx, const pm_map* map, const float* q_dev, int64_t nq, int k, float cutoff2, int32_t* out_ids,
+                  float* out_d2, float* out_r2) {
+  if (!ctx->copy_stream) {
+    PM_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) {
+      PM_CUDA(cudaEventCreateWithFlags(&ctx->ev_kernel[i], cudaEventDisableTiming));
+      PM_CUDA(cudaEventCreateWithFlags(&ctx->ev_copy[i], cudaEventDisableTiming));
+    }
+  }
+  int32_t* s_ids = nullptr; float *s_d2 = nullptr, *s_r2 = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_STAGE_OUT0, (size_t)(2 * kPipeChunk * k), &s_ids));
+  if (out_d2) PM_CHECK(ctx->get_scratch(pm::S_STAGE_OUT1, (size_t)(2 * kPipeChunk * k), &s_d2));
+  if (out_r2) PM_CHECK(ctx->get_scratch(pm::S_STAGE_OUT2, (size_t)(2 * kPipeChunk), &s_r2));
+  PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+  int c = 0;
+  for (int64_t b = 0; b < nq; b += kPipeChunk, c++) {
+    const int64_t cnt = nq - b < kPipeChunk ? nq - b : kPipeChunk;
+    const int buf = c & 1;
+    if (c >= 2) PM_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_copy[buf], 0));
+    pmk::QueryIO io;
+    io.q = q_dev + 3 * b; io.nq = (int)cnt; io.k = k; io.cutoff2 = cutoff2;
+    io.ids = s_ids + (size_t)buf * kPipeChunk * k;
+    io.d2 = s_d2 ? s_d2 + (size_t)buf * kPipeChunk * k : nullptr;
+    io.r2 = s_r2 ? s_r2 + (size_t)buf * kPipeChunk : nullptr;
+    PM_CHECK(run_queries(ctx, map, io, false, false));
+    PM_CUDA(cudaEventRecord(ctx->ev_kernel[buf], ctx->stream));
+    PM_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_kernel[buf], 0));
+    PM_CUDA(cudaMemcpyAsync(out_ids + (size_t)b * k, io.ids, sizeof(int32_t) * (size_t)cnt * k, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    if (out_d2) PM_CUDA(cudaMemcpyAsync(out_d2 + (size_t)b * k, io.d2, sizeof(float) * (size_t)cnt * k, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    if (out_r2) PM_CUDA(cudaMemcpyAsync(out_r2 + b, io.r2, sizeof(float) * (size_t)cnt, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    PM_CUDA(cudaEventRecord(ctx->ev_copy[buf], ctx->copy_stream));
+  }
+  PM_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  PM_CUDA(cudaStreamSynchronize(ctx->copy_stream));
+  return PM_OK;
+}
+
 }  // namespace
 
 namespace pm {
@@ -369,6 +411,12 @@ int pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int
   const float cutoff2 = cutoff_radius * cutoff_radius;
   const void* q_dev = nullptr;
   PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN0, queries, sizeof(float) * 3 * (size_t)nq, &q_dev));
+  if (map && map->n >= 1 && nq >= 2 * kPipeChunk && !pm::is_device_ptr(out_ids) && !pm::is_device_ptr(out_dist2) &&
+      !pm::is_device_ptr(out_r2)) {
+    PM_CHECK(knn_pipelined(ctx, map, (const float*)q_dev, nq, k, cutoff2, out_ids, out_dist2, out_r2));
+    PM_CHECK(finish_stats(ctx, map));
+    return PM_OK;
+  }
   pm::OutStage o_ids, o_d2, o_r2;
   PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT0, out_ids, sizeof(int32_t) * (size_t)k * nq, &o_ids));
   PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT1, out_dist2, sizeof(float) * (size_t)k * nq, &o_d2));
