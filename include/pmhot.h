@@ -204,6 +204,11 @@ int  pm_photons_write_text(const char* path, const pm_photon40* photons_host, in
 /* reads at most capacity records; *count = number of records in the file */
 int  pm_photons_read_text(const char* path, pm_photon40* photons_host, int64_t capacity, int64_t* count);
 
+/* binary variant of the same hand-off (not in the reference: SURVEY §8f rank 1): "PMPH", version 1, int64
+ * count, then the 40-byte records; lossless where the text format rounds to 6 decimals */
+int  pm_photons_write_bin(const char* path, const pm_photon40* photons_host, int64_t n);
+int  pm_photons_read_bin(const char* path, pm_photon40* photons_host, int64_t capacity, int64_t* count);
+
 #ifdef __cplusplus
 }
 #endif

@@ -79,6 +79,8 @@ _SIGNATURES = {
     ),
     "pm_photons_write_text": (c_int, [c_char_p, c_void_p, c_int64]),
     "pm_photons_read_text": (c_int, [c_char_p, c_void_p, c_int64, POINTER(c_int64)]),
+    "pm_photons_write_bin": (c_int, [c_char_p, c_void_p, c_int64]),
+    "pm_photons_read_bin": (c_int, [c_char_p, c_void_p, c_int64, POINTER(c_int64)]),
 }
 ABI_SYMBOLS = tuple(_SIGNATURES)
 
@@ -388,4 +390,18 @@ def read_photons_text(path: str) -> np.ndarray:
     out = np.zeros(cnt.value, PHOTON40)
     if cnt.value:
         _check(lib().pm_photons_read_text(path.encode(), out.ctypes.data, cnt.value, ctypes.byref(cnt)))
+    return out
+
+
+def write_photons_bin(path: str, photons: np.ndarray) -> None:
+    p = np.ascontiguousarray(photons, PHOTON40)
+    _check(lib().pm_photons_write_bin(path.encode(), p.ctypes.data, len(p)))
+
+
+def read_photons_bin(path: str) -> np.ndarray:
+    cnt = c_int64(0)
+    _check(lib().pm_photons_read_bin(path.encode(), None, 0, ctypes.byref(cnt)))
+    out = np.zeros(cnt.value, PHOTON40)
+    if cnt.value:
+        _check(lib().pm_photons_read_bin(path.encode(), out.ctypes.data, cnt.value, ctypes.byref(cnt)))
     return out

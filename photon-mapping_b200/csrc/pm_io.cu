@@ -49,4 +49,44 @@ int pm_photons_read_text(const char* path, pm_photon40* out, int64_t capacity, i
   return PM_OK;
 }
 
+/* Binary hand-off between the passes: "PMPH", version, count, then the 40-byte records
+ * as they are in memory. Lossless (the text format rounds to 1e-6) and ~60x faster to parse. */
+static const uint32_t kBinMagic = 0x48504D50u; /* "PMPH" little endian */
+
+int pm_photons_write_bin(const char* path, const pm_photon40* p, int64_t n) {
+  PM_REQUIRE(path && (p || n == 0) && n >= 0, "bad arguments");
+  FILE* f = fopen(path, "wb");
+  if (!f) { pm::set_error("pm_photons_write_bin: cannot open %s: %s", path, strerror(errno)); return PM_ERR_IO; }
+  const uint32_t head[2] = {kBinMagic, 1u};
+  bool ok = fwrite(head, sizeof head, 1, f) == 1 && fwrite(&n, sizeof n, 1, f) == 1;
+  if (ok && n > 0) ok = fwrite(p, sizeof(pm_photon40), (size_t)n, f) == (size_t)n;
+  if (fclose(f) != 0 || !ok) { pm::set_error("pm_photons_write_bin: write to %s failed", path); return PM_ERR_IO; }
+  return PM_OK;
+}
+
+int pm_photons_read_bin(const char* path, pm_photon40* out, int64_t capacity, int64_t* count) {
+  PM_REQUIRE(path && count && capacity >= 0, "bad arguments");
+  *count = 0;
+  FILE* f = fopen(path, "rb");
+  if (!f) { pm::set_error("pm_photons_read_bin: cannot open %s: %s", path, strerror(errno)); return PM_ERR_IO; }
+  uint32_t head[2] = {0, 0};
+  int64_t n = -1;
+  if (fread(head, sizeof head, 1, f) != 1 || fread(&n, sizeof n, 1, f) != 1 || head[0] != kBinMagic || head[1] != 1u || n < 0) {
+    fclose(f);
+    pm::set_error("pm_photons_read_bin: %s is not a photon file of this format", path);
+    return PM_ERR_IO;
+  }
+  *count = n;
+  if (out && capacity > 0) {
+    const int64_t take = n < capacity ? n : capacity;
+    if (take > 0 && fread(out, sizeof(pm_photon40), (size_t)take, f) != (size_t)take) {
+      fclose(f);
+      pm::set_error("pm_photons_read_bin: %s is truncated", path);
+      return PM_ERR_IO;
+    }
+  }
+  fclose(f);
+  return PM_OK;
+}
+
 }  // extern "C"

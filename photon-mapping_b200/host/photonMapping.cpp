@@ -77,7 +77,8 @@ int main(int argc, char** argv) {
       const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
       LOG_OK(p.what << " pass: " << paths << " paths, " << segments << " segments, " << count << " photons stored in " << ms
                     << " ms (device " << pm_ctx_last_kernel_ms(ctx) << " ms)");
-      check(pm_photons_write_text(p.file->c_str(), photons.data(), count));
+      const bool bin = p.file->size() > 4 && p.file->compare(p.file->size() - 4, 4, ".bin") == 0;  // lossless hand-off
+      check(bin ? pm_photons_write_bin(p.file->c_str(), photons.data(), count) : pm_photons_write_text(p.file->c_str(), photons.data(), count));
       LOG_OK("Wrote " << *p.file);
     }
     pm_scene_destroy(scene);

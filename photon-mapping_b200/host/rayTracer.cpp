@@ -42,9 +42,11 @@ static pm_camera setup_camera(V3 from, V3 at, V3 up, float fovy, int W, int H) {
 
 static std::vector<pm_photon40> read_photons(const std::string& path) {
   int64_t n = 0;
-  check(pm_photons_read_text(path.c_str(), nullptr, 0, &n));
+  const bool bin = path.size() > 4 && path.compare(path.size() - 4, 4, ".bin") == 0;  // written by photonMapping for *.bin names
+  auto rd = bin ? pm_photons_read_bin : pm_photons_read_text;
+  check(rd(path.c_str(), nullptr, 0, &n));
   std::vector<pm_photon40> v((size_t)n);
-  if (n) check(pm_photons_read_text(path.c_str(), v.data(), n, &n));
+  if (n) check(rd(path.c_str(), v.data(), n, &n));
   return v;
 }
 

@@ -92,3 +92,27 @@ def test_config_errors(hosts, tmp_path):
     assert r.returncode != 0 and "missing" in r.stderr
     r = subprocess.run([os.path.join(hosts, "rayTracer"), str(tmp_path / "nope.toml")], capture_output=True, text=True)
     assert r.returncode != 0 and "cannot open config" in r.stderr
+
+
+def test_photon_file_formats_roundtrip(pkg, tmp_path):
+    """text (≙ writeAlivePhotons / readPhotonsFromFile: 9 floats, 6 decimals) and the lossless binary hand-off"""
+    rng = np.random.default_rng(5)
+    p = np.zeros(1000, pkg.PHOTON40)
+    p["pos"] = (rng.random((1000, 3)) * 80 - 40).astype(np.float32)
+    p["dir"] = rng.standard_normal((1000, 3)).astype(np.float32)
+    p["color"] = rng.random((1000, 3)).astype(np.float32)
+    txt, binf = str(tmp_path / "p.txt"), str(tmp_path / "p.bin")
+    pkg.write_photons_text(txt, p)
+    first = open(txt).readline().split()
+    assert len(first) == 9 and all(len(t.split(".")[1]) == 6 for t in first)  # std::fixed, setprecision(6)
+    back = pkg.read_photons_text(txt)
+    assert len(back) == 1000 and np.abs(back["pos"] - p["pos"]).max() <= 1e-5 and (back["power"] == 0).all()
+    pkg.write_photons_bin(binf, p)
+    assert os.path.getsize(binf) == 16 + 40 * 1000
+    assert pkg.read_photons_bin(binf).tobytes() == p.tobytes()
+    pkg.write_photons_bin(binf, p[:0])
+    assert len(pkg.read_photons_bin(binf)) == 0
+    with pytest.raises(pkg.PmError):
+        pkg.read_photons_bin(txt)  # wrong magic
+    with pytest.raises(pkg.PmError):
+        pkg.read_photons_text(str(tmp_path / "missing.txt"))
