@@ -189,6 +189,13 @@ int  pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, in
 int  pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, int64_t nq,
                int k, float cutoff_radius, float* out_rgb);
 
+/* fixed-radius gather: one progressive-photon-mapping pass (BASELINE config 5; the reference has only the
+ * cutoff radius of its candidate list, cukd/knn.h:298-306 — this entry point is new). For every hit point i:
+ * out_flux[3i..] = brdf[i] * sum(power * colour) over the nodes with dist² < radius2[i] (dist² as in pm_knn),
+ * out_count[i] = their number. Hit points with brdf <= 0 or radius2 <= 0 yield zeros. Host or device pointers. */
+int  pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, const float* radius2,
+                      int64_t nq, float* out_flux, int32_t* out_count);
+
 /* render (≙ simpleRayGen launch): fb is W*H RGBA8, rows as the reference writes them
  * (row H - py; row 0 stays 0, the reference's out-of-bounds row H is not written).
  * maps may be NULL (empty). Pixels [pixel_begin, pixel_end) of the launch grid (index = px + W*py)

@@ -283,6 +283,29 @@ int orc_kd_check(const pm_photon44* nodes, int n) {
   return check_rec(nodes, n, 0, lo, hi) ? 1 : 0;
 }
 
+/* Fixed-radius gather (the progressive pass of BASELINE config 5; no reference code exists, this is the
+ * definition libpmhot implements): flux = brdf * sum(power * colour) over nodes with dist² < radius²,
+ * dist² as in the kNN contract; brute force, float accumulation in node order. */
+void orc_gather_radius(const pm_photon44* nodes, int n, const float* hit, const float* brdf, const float* radius2,
+                       int64_t nq, float* out_flux, int32_t* out_count) {
+#pragma omp parallel for schedule(dynamic, 16)
+  for (int64_t i = 0; i < nq; i++) {
+    float s[3] = {0.f, 0.f, 0.f};
+    int cnt = 0;
+    if (brdf[i] > 0.f && radius2[i] > 0.f) {
+      for (int j = 0; j < n; j++) {
+        if (sqr_dist(nodes[j].pos, hit + 3 * i) < radius2[i]) {
+          for (int c = 0; c < 3; c++) s[c] = s[c] + nodes[j].power * nodes[j].color[c];
+          cnt++;
+        }
+      }
+    }
+    const float f = brdf[i] > 0.f ? brdf[i] : 0.f;
+    for (int c = 0; c < 3; c++) out_flux[3 * i + c] = f * s[c];
+    out_count[i] = cnt;
+  }
+}
+
 int orc_omp_threads(void) { return omp_get_max_threads(); }
 /* launchers (torchrun) export OMP_NUM_THREADS=1; the timed CPU arm uses every host thread */
 void orc_omp_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }

@@ -72,6 +72,7 @@ _SIGNATURES = {
     "pm_map_size": (c_int64, [c_void_p]),
     "pm_knn": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "pm_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p]),
+    "pm_gather_radius": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "pm_render": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
@@ -246,6 +247,25 @@ class PhotonMap:
                 out_rgb = torch.empty((nq, 3), dtype=torch.float32, device=hit.device)
         _check(lib().pm_gather(self.ctx.handle, self.handle, _ptr(hit), _ptr(brdf), nq, k, cutoff, _ptr(out_rgb)))
         return out_rgb
+
+
+def _gather_radius(self, hit, brdf, radius2, out_flux=None, out_count=None):
+    """pm_gather_radius: (flux[nq,3], count[nq]) for per-point squared radii (one progressive pass)."""
+    nq = _count(hit, 12)
+    if isinstance(hit, np.ndarray):
+        out_flux = np.empty((nq, 3), np.float32) if out_flux is None else out_flux
+        out_count = np.empty(nq, np.int32) if out_count is None else out_count
+    else:
+        import torch
+
+        out_flux = torch.empty((nq, 3), dtype=torch.float32, device=hit.device) if out_flux is None else out_flux
+        out_count = torch.empty(nq, dtype=torch.int32, device=hit.device) if out_count is None else out_count
+    _check(lib().pm_gather_radius(self.ctx.handle, self.handle, _ptr(hit), _ptr(brdf), _ptr(radius2), nq, _ptr(out_flux),
+                                  _ptr(out_count)))
+    return out_flux, out_count
+
+
+PhotonMap.gather_radius = _gather_radius
 
 
 def _count(x, rec_bytes: int) -> int:

@@ -433,6 +433,181 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
   }
 }
 
+/* ---- fixed-radius gather (progressive photon mapping pass; SURVEY appendix B — no reference code) ------
+ * Per hit point: flux = brdf * sum(power * colour) over the nodes with dist² < radius², count = their number.
+ * Same candidate enumeration as k_grid_query (ball-trimmed rows of the smallest block that covers the ball),
+ * no selection. Hit points whose ball no block of up to (2 kMaxH + 1)^3 cells covers, or whose rows are too
+ * dense for the flat index space, go to the kd-tree range kernel below. */
+__global__ void __launch_bounds__(kWarps * 32)
+k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
+              const float* __restrict__ radius2, const int* __restrict__ order, int nq, float* __restrict__ out_flux,
+              int32_t* __restrict__ out_count, int* __restrict__ fb_list, int* __restrict__ fb_count) {
+  __shared__ WarpScratch scratch[kWarps];
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u, le_not0 = (lt | (1u << lane)) & ~1u;
+  WarpScratch& ws = scratch[threadIdx.x >> 5];
+  for (int t = blockIdx.x * kWarps + (threadIdx.x >> 5); t < nq; t += gridDim.x * kWarps) {
+    const int qi = order ? order[t] : t;
+    const float f = brdf[qi], R2 = radius2[qi];
+    if (!(f > 0.f) || !(R2 > 0.f)) { /* no hit point here */
+      if (lane < 3) out_flux[(size_t)qi * 3 + lane] = 0.f;
+      if (lane == 0) out_count[qi] = 0;
+      continue;
+    }
+    const float qx = q[(size_t)qi * 3 + 0], qy = q[(size_t)qi * 3 + 1], qz = q[(size_t)qi * 3 + 2];
+    const float fx = (qx - g.lo[0]) * g.inv_cell, fy = (qy - g.lo[1]) * g.inv_cell, fz = (qz - g.lo[2]) * g.inv_cell;
+    const int cx = min(max(__float2int_rd(fx), 0), g.nx - 1), cy = min(max(__float2int_rd(fy), 0), g.ny - 1),
+              cz = min(max(__float2int_rd(fz), 0), g.nz - 1);
+    /* smallest block whose guaranteed radius covers the ball */
+    int h = min(max(__float2int_ru(sqrtf(R2) * g.inv_cell), 1), kMaxH);
+    int x0, x1, y0, y1, z0, z1;
+    bool covered = false;
+    for (; h <= kMaxH; h++) {
+      x0 = max(cx - h, 0); x1 = min(cx + h, g.nx - 1);
+      y0 = max(cy - h, 0); y1 = min(cy + h, g.ny - 1);
+      z0 = max(cz - h, 0); z1 = min(cz + h, g.nz - 1);
+      float Gc = INFINITY;
+      if (x0 > 0) Gc = fminf(Gc, fx - (float)x0);
+      if (x1 < g.nx - 1) Gc = fminf(Gc, (float)(x1 + 1) - fx);
+      if (y0 > 0) Gc = fminf(Gc, fy - (float)y0);
+      if (y1 < g.ny - 1) Gc = fminf(Gc, (float)(y1 + 1) - fy);
+      if (z0 > 0) Gc = fminf(Gc, fz - (float)z0);
+      if (z1 < g.nz - 1) Gc = fminf(Gc, (float)(z1 + 1) - fz);
+      const float G = Gc * g.cell - g.margin;
+      if (G > 0.f && !(G * G < R2)) { covered = true; break; }
+    }
+    bool give_up = !covered;
+    float sr = 0.f, sg = 0.f, sb = 0.f;
+    int cnt = 0;
+    if (!give_up) {
+      const int ny_r = y1 - y0 + 1, nrows = ny_r * (z1 - z0 + 1);
+      for (int r0 = 0; r0 < nrows; r0 += 32) {
+        const int row = r0 + lane;
+        int len = 0, st = 0;
+        if (row < nrows) {
+          const int rzo = div_small(row, ny_r);
+          const int ry = y0 + row - rzo * ny_r, rz = z0 + rzo;
+          const float ylo = g.lo[1] + (float)ry * g.cell, zlo = g.lo[2] + (float)rz * g.cell;
+          const float dy = fmaxf(fmaxf(ylo - qy, qy - (ylo + g.cell)) - g.margin, 0.f);
+          const float dz = fmaxf(fmaxf(zlo - qz, qz - (zlo + g.cell)) - g.margin, 0.f);
+          const float dyz2 = dy * dy + dz * dz;
+          if (dyz2 < R2) {
+            const float t2 = R2 - dyz2;
+            const float w = (t2 < 1e30f ? t2 * rsqrtf(t2) * 1.0001f : INFINITY) + g.margin;
+            const int xa = max(cell_idx(qx - w, g.lo[0], g.inv_cell, g.nx), x0);
+            const int xb = min(cell_idx(qx + w, g.lo[0], g.inv_cell, g.nx), x1);
+            if (xa <= xb) {
+              const size_t base = ((size_t)rz * g.ny + ry) * g.nx;
+              st = (int)__ldg(g.cell_start + base + xa);
+              len = (int)__ldg(g.cell_start + base + xb + 1) - st;
+            }
+          }
+        }
+        int incl = len;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int v = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += v;
+        }
+        const int mc = __shfl_sync(0xffffffffu, incl, 31);
+        if (mc == 0) continue;
+        if (mc > kMaxScan) { give_up = true; break; }
+        const int P = incl - len;
+        __syncwarp();
+        ws.words[lane] = make_uint2(0u, 0u);
+        __syncwarp();
+        const unsigned nonempty = __ballot_sync(0xffffffffu, len > 0);
+        if (len > 0) {
+          const int d = __popc(nonempty & lt);
+          atomicOr(&ws.words[P >> 5].x, 1u << (P & 31));
+          ws.run_off[d] = st - P;
+          for (int i = (P + 31) >> 5; i * 32 < P + len; i++) ws.words[i].y = (unsigned)d;
+        }
+        __syncwarp();
+        for (int i = 0; i * 32 < mc; i++) {
+          const int j = i * 32 + lane;
+          const int jj = min(j, mc - 1);
+          const uint2 w = ws.words[i];
+          const int run = (int)w.y + __popc(w.x & le_not0);
+          const float4 p = __ldg(g.pts + (ws.run_off[run] + jj));
+          const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+          if (j < mc && d2 < R2) {
+            const float4 c = __ldg(color4 + __float_as_int(p.w));
+            sr = __fadd_rn(sr, __fmul_rn(c.w, c.x));
+            sg = __fadd_rn(sg, __fmul_rn(c.w, c.y));
+            sb = __fadd_rn(sb, __fmul_rn(c.w, c.z));
+            cnt++;
+          }
+        }
+      }
+    }
+    if (give_up) {
+      if (lane == 0) fb_list[atomicAdd(fb_count, 1)] = qi;
+      __syncwarp();
+      continue;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      sr = __fadd_rn(sr, __shfl_xor_sync(0xffffffffu, sr, o));
+      sg = __fadd_rn(sg, __shfl_xor_sync(0xffffffffu, sg, o));
+      sb = __fadd_rn(sb, __shfl_xor_sync(0xffffffffu, sb, o));
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if (lane == 0) {
+      out_flux[(size_t)qi * 3 + 0] = __fmul_rn(f, sr);
+      out_flux[(size_t)qi * 3 + 1] = __fmul_rn(f, sg);
+      out_flux[(size_t)qi * 3 + 2] = __fmul_rn(f, sb);
+      out_count[qi] = cnt;
+    }
+    __syncwarp();
+  }
+}
+
+/* kd-tree range query, one thread per hit point: the fallback of k_grid_radius and the only path of maps
+ * without a grid. Same visiting order as cukd's stack traversal with a fixed cull radius. */
+__global__ void __launch_bounds__(128)
+k_kd_radius(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n, const float* __restrict__ q,
+            const float* __restrict__ brdf, const float* __restrict__ radius2, int nq, const int* __restrict__ list,
+            const int* __restrict__ list_count, float* __restrict__ out_flux, int32_t* __restrict__ out_count) {
+  const int total = list ? *list_count : nq;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+    const int qi = list ? list[t] : t;
+    const float f = brdf[qi], R2 = radius2[qi];
+    float sr = 0.f, sg = 0.f, sb = 0.f;
+    int cnt = 0;
+    if (f > 0.f && R2 > 0.f) {
+      const float qx = q[(size_t)qi * 3 + 0], qy = q[(size_t)qi * 3 + 1], qz = q[(size_t)qi * 3 + 2];
+      int stack[48];
+      int sp = 0, curr = 0;
+      while (true) {
+        while (curr < n) {
+          const float4 nd = __ldg(nodes + curr);
+          const int dim = __float_as_int(nd.w);
+          const float d2 = pmk::dist2(nd.x, nd.y, nd.z, qx, qy, qz);
+          if (d2 < R2) {
+            const float4 c = __ldg(color4 + curr);
+            sr = __fadd_rn(sr, __fmul_rn(c.w, c.x));
+            sg = __fadd_rn(sg, __fmul_rn(c.w, c.y));
+            sb = __fadd_rn(sb, __fmul_rn(c.w, c.z));
+            cnt++;
+          }
+          const float dp = dim == 0 ? qx - nd.x : (dim == 1 ? qy - nd.y : qz - nd.z);
+          const int l = 2 * curr + 1;
+          const int far_child = dp < 0.f ? l + 1 : l;
+          if (__fmul_rn(dp, dp) < R2 && far_child < n && sp < 48) stack[sp++] = far_child;
+          curr = dp < 0.f ? l : l + 1;
+        }
+        if (sp == 0) break;
+        curr = stack[--sp];
+      }
+    }
+    out_flux[(size_t)qi * 3 + 0] = __fmul_rn(f > 0.f ? f : 0.f, sr);
+    out_flux[(size_t)qi * 3 + 1] = __fmul_rn(f > 0.f ? f : 0.f, sg);
+    out_flux[(size_t)qi * 3 + 2] = __fmul_rn(f > 0.f ? f : 0.f, sb);
+    out_count[qi] = cnt;
+  }
+}
+
 /* ---- grid construction ------------------------------------------------------------------ */
 __global__ void k_cell_ids(const float4* __restrict__ nodes, int n, GridView g, uint32_t* __restrict__ keys,
                            int* __restrict__ vals) {
@@ -572,6 +747,30 @@ int grid_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gath
   if (gather) k_grid_query<true><<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fb_list, fb_count);
   else k_grid_query<false><<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fb_list, fb_count);
   ctx->launches++;
+  PM_CUDA(cudaGetLastError());
+  return PM_OK;
+}
+
+int radius_query(pm_ctx* ctx, const pm_map* map, const float* q, const float* brdf, const float* radius2, const int* order,
+                 int nq, float* out_flux, int32_t* out_count, int* fb_list, int* fb_count) {
+  int64_t kd_grid = div_up(nq, 128);
+  if (map->grid_pts) {
+    const GridView g = view_of(map);
+    int64_t grid = div_up(nq, kWarps);
+    const int64_t cap = (int64_t)ctx->sm_count * 64;
+    if (grid > cap) grid = cap;
+    k_grid_radius<<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, out_flux, out_count,
+                                                                  fb_list, fb_count);
+    if (kd_grid > ctx->sm_count * 2) kd_grid = ctx->sm_count * 2;
+    k_kd_radius<<<(unsigned)kd_grid, 128, 0, ctx->stream>>>(map->nodes4, map->color4, (int)map->n, q, brdf, radius2, nq, fb_list,
+                                                           fb_count, out_flux, out_count);
+    ctx->launches += 2;
+  } else {
+    if (kd_grid > ctx->sm_count * 64) kd_grid = ctx->sm_count * 64;
+    k_kd_radius<<<(unsigned)kd_grid, 128, 0, ctx->stream>>>(map->nodes4, map->color4, (int)map->n, q, brdf, radius2, nq, nullptr,
+                                                           nullptr, out_flux, out_count);
+    ctx->launches++;
+  }
   PM_CUDA(cudaGetLastError());
   return PM_OK;
 }

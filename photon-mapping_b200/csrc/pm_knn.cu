@@ -457,4 +457,42 @@ int pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brd
   return PM_OK;
 }
 
+/* fixed-radius gather: one progressive-photon-mapping pass over a set of hit points */
+int pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, const float* radius2, int64_t nq,
+                     float* out_flux, int32_t* out_count) {
+  PM_REQUIRE(ctx, "ctx is NULL");
+  PM_REQUIRE(nq >= 0 && nq < ((int64_t)1 << 31), "nq out of range");
+  if (nq == 0) return PM_OK;
+  PM_REQUIRE(hit && brdf && radius2 && out_flux && out_count, "hit/brdf/radius2/out_flux/out_count is NULL");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  const void *h_dev = nullptr, *b_dev = nullptr, *r_dev = nullptr;
+  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN0, hit, sizeof(float) * 3 * (size_t)nq, &h_dev));
+  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN1, brdf, sizeof(float) * (size_t)nq, &b_dev));
+  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN2, radius2, sizeof(float) * (size_t)nq, &r_dev));
+  pm::OutStage of, oc;
+  PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT0, out_flux, sizeof(float) * 3 * (size_t)nq, &of));
+  PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT1, out_count, sizeof(int32_t) * (size_t)nq, &oc));
+  ctx->fb_count_dev = nullptr;
+  if (!map || map->n < 1) {
+    PM_CUDA(cudaMemsetAsync(of.dev, 0, sizeof(float) * 3 * (size_t)nq, ctx->stream));
+    PM_CUDA(cudaMemsetAsync(oc.dev, 0, sizeof(int32_t) * (size_t)nq, ctx->stream));
+  } else {
+    int* perm = nullptr;
+    PM_CHECK(sort_queries(ctx, map, (const float*)h_dev, (const float*)b_dev, (int)nq, &perm));
+    int *fb_list = nullptr, *fb_count = nullptr;
+    PM_CHECK(ctx->get_scratch(pm::S_MISC1, (size_t)nq, &fb_list));
+    PM_CHECK(ctx->get_scratch(pm::S_MISC2, (size_t)4, &fb_count));
+    PM_CUDA(cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
+    if (map->grid_pts) ctx->fb_count_dev = fb_count;
+    PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+    PM_CHECK(pm::radius_query(ctx, map, (const float*)h_dev, (const float*)b_dev, (const float*)r_dev, perm, (int)nq,
+                              (float*)of.dev, (int32_t*)oc.dev, fb_list, fb_count));
+    PM_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  }
+  PM_CHECK(pm::stage_out_finish(ctx, of));
+  PM_CHECK(pm::stage_out_finish(ctx, oc));
+  PM_CHECK(finish_stats(ctx, map));
+  return PM_OK;
+}
+
 }  // extern "C"

@@ -1,0 +1,57 @@
+"""Progressive (fixed-radius) photon mapping — BASELINE config 5. No reference implementation exists, so parity is
+self-consistency: the host loop's update arithmetic (CPU), and the GPU passes against the same loop driven by the
+oracle (oracle photon walk with the counter RNG + brute-force fixed-radius gather)."""
+import ctypes
+from ctypes import c_int64, c_void_p
+
+import numpy as np
+import pytest
+
+import __graft_entry__ as graft
+from helpers import PHOTON44, load_scene, oracle_emit, vp
+
+
+def test_ppm_update_arithmetic():
+    ppm = graft.load_package_module("ppm")
+    N = np.array([0, 10, 10, 5], np.float32)
+    r2 = np.array([4, 4, 4, 1], np.float32)
+    tau = np.ones((4, 3), np.float32)
+    flux = np.full((4, 3), 2, np.float32)
+    flux[2] = 0
+    count = np.array([8, 10, 0, 5], np.int32)
+    ppm.ppm_update(N, r2, tau, flux, count, 0.7)
+    assert np.allclose(N, [5.6, 17, 10, 8.5])
+    assert np.allclose(r2, [4 * 5.6 / 8, 4 * 17 / 20, 4, 8.5 / 10])
+    assert np.allclose(tau[:, 0], [3 * 5.6 / 8, 3 * 17 / 20, 1, 3 * 8.5 / 10])
+    assert (r2 <= [4, 4, 4, 1]).all()  # radii never grow
+
+
+@pytest.mark.gpu
+def test_progressive_passes_match_oracle_loop(pkg, ctx, orc):
+    ppm = graft.load_package_module("ppm")
+    sc = load_scene("cornell_box")
+    scene = pkg.Scene(ctx, sc["verts"], sc["tris"], sc["tri_mesh"], sc["mats"])
+    W, H, passes, per_pass, r0, alpha, depth = 48, 32, 3, 20000, 3.0, 0.7, 6
+    cam = pkg.make_camera((80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87, W, H)
+    got = ppm.progressive_render(pkg, ctx, scene, sc["tri_mesh"], sc["mats"], sc["lights"], cam, W, H, passes, per_pass, r0, alpha,
+                                 depth, seed=5)
+    # the same loop on the oracle
+    rays = ppm.camera_rays(pkg, cam, W, H)
+    pos, brdf, albedo = ppm.hit_points(pkg, scene, sc["tri_mesh"], sc["mats"], rays)
+    assert (brdf > 0).mean() > 0.5
+    N = np.zeros(W * H, np.float32)
+    r2 = np.full(W * H, np.float32(r0) ** 2, np.float32)
+    tau = np.zeros((W * H, 3), np.float32)
+    orc.orc_gather_radius.argtypes = [c_void_p, ctypes.c_int, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]
+    for p in range(passes):
+        g40, _, _ = oracle_emit(orc, sc, per_pass, depth, False, seed=5 + p, rng_mode=1)
+        g44 = np.zeros(len(g40), PHOTON44)
+        g44["pos"], g44["dir"], g44["color"], g44["power"] = g40["pos"], g40["dir"], g40["color"], 1.0
+        flux = np.zeros((W * H, 3), np.float32)
+        cnt = np.zeros(W * H, np.int32)
+        orc.orc_gather_radius(vp(g44), len(g44), vp(pos), vp(brdf), vp(r2), W * H, vp(flux), vp(cnt))
+        ppm.ppm_update(N, r2, tau, flux, cnt, alpha)
+    assert np.array_equal(got["N"], N) and np.array_equal(got["r2"], r2)  # counts are exact, so are N and r²
+    assert np.allclose(got["tau"], tau, rtol=2e-4, atol=1e-6)
+    assert got["emitted"] == passes * per_pass and np.isfinite(got["radiance"]).all() and got["radiance"].max() > 0
+    assert (r2 < np.float32(r0) ** 2).any()
