@@ -29,9 +29,12 @@ for r in rows[h + 1:]:
         a[0] += 1; a[1] += t
         seq.append((name, t))
 tot = sum(v[1] for v in agg.values())
-# one timed step = the launches from one k_morton to the next; report the last complete one
+# one timed step = the launches from one k_morton to the next; report one device-resident 1M-query step
 starts = [i for i, (nm, _) in enumerate(seq) if nm.endswith("k_morton")]
-step = seq[starts[-2]:starts[-1]] if len(starts) >= 2 else []
+# (the longest one: bench.py's later end-to-end steps run the same kernels on 131 072-query chunks)
+groups = [seq[a:b] for a, b in zip(starts, starts[1:])]
+groups = [g for g in groups if not any("k_split" in nm or "k_partition" in nm for nm, _ in g)]  # not a map build
+step = max(groups, key=lambda g: sum(t for _, t in g)) if groups else []
 with open(os.path.join(out, f"{tag}_step_launches.csv"), "w") as f:
     f.write("# launches of ONE pm_knn step (k_morton .. last query kernel), in launch order; same ncu pass as the full list\n")
     f.write("kernel,us,share_of_step\n")
