@@ -296,7 +296,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         dist.barrier()
     torch.cuda.synchronize()
     ctx.reset_launch_count()
-    step_ms, kern_ms, fallbacks = [], [], 0
+    step_ms, kern_ms, fallbacks, handovers = [], [], 0, 0
     wall0 = time.perf_counter()
     with torch.cuda.stream(ext_stream):
         for _ in range(args.steps):
@@ -309,6 +309,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             step_ms.append(e0.elapsed_time(e1))
             kern_ms.append(ctx.last_kernel_ms)
             fallbacks = max(fallbacks, ctx.last_fallback_count)
+            handovers = max(handovers, ctx.last_handover_count)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -378,7 +379,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic_per_launch(),
                          "kernel": "k_grid_query<false> (+ k_kd<64> on the queries it hands over)", "kernel_ms": k_ms,
-                         "kd_tree_fallback_queries": int(fallbacks),
+                         "kd_tree_fallback_queries": int(fallbacks), "general_grid_kernel_queries": int(handovers),
                          "algorithmic_bytes_per_launch": BYTES_PER_QUERY * N_QUERIES, "peak_source": peak_src},
             "cpu_baseline": cpu,
             "clocks": clocks,

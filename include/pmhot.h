@@ -121,6 +121,9 @@ float pm_ctx_last_kernel_ms(pm_ctx* ctx);
 /* queries of the most recent pm_knn / pm_gather that the uniform-grid kernel handed to the kd-tree
  * kernel (sparse or very dense neighbourhoods); -1 if the map has no grid (small maps) */
 int64_t pm_ctx_last_fallback_count(pm_ctx* ctx);
+/* queries of the most recent pm_knn / pm_gather that the descriptor fast path (uniform-like clouds)
+ * handed to the general uniform-grid kernel; 0 if the fast path was not used */
+int64_t pm_ctx_last_handover_count(pm_ctx* ctx);
 
 /* ---- scene: LBVH build + traversal  (≙ loadGeometry, common/src/world.cpp:3-58) ------- */
 /* verts: 3*nv floats; tris: 3*nt vertex indices; tri_mesh: nt mesh ids; mats: n_mesh records */

@@ -51,6 +51,7 @@ _SIGNATURES = {
     "pm_ctx_reset_launch_count": (None, [c_void_p]),
     "pm_ctx_last_kernel_ms": (c_float, [c_void_p]),
     "pm_ctx_last_fallback_count": (c_int64, [c_void_p]),
+    "pm_ctx_last_handover_count": (c_int64, [c_void_p]),
     "pm_scene_create": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, POINTER(c_void_p)]),
     "pm_scene_destroy": (None, [c_void_p]),
     "pm_trace_closest": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
@@ -175,6 +176,10 @@ class Context:
     @property
     def last_fallback_count(self) -> int:
         return lib().pm_ctx_last_fallback_count(self.handle)
+
+    @property
+    def last_handover_count(self) -> int:
+        return lib().pm_ctx_last_handover_count(self.handle)
 
 
 class PhotonMap:

@@ -134,5 +134,6 @@ int64_t pm_ctx_launch_count(pm_ctx* ctx) { return ctx ? ctx->launches : 0; }
 void pm_ctx_reset_launch_count(pm_ctx* ctx) { if (ctx) ctx->launches = 0; }
 float pm_ctx_last_kernel_ms(pm_ctx* ctx) { return ctx ? ctx->last_kernel_ms : 0.f; }
 int64_t pm_ctx_last_fallback_count(pm_ctx* ctx) { return ctx ? ctx->last_fallbacks : 0; }
+int64_t pm_ctx_last_handover_count(pm_ctx* ctx) { return ctx ? ctx->last_handovers : 0; }
 
 }  // extern "C"

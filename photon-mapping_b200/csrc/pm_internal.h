@@ -52,6 +52,7 @@ enum ScratchSlot {
   S_BUILD9, S_BUILD10, S_BUILD11, S_BUILD12, S_BUILD13, S_BUILD14, S_BUILD15,
   S_RENDER0, S_RENDER1, S_RENDER2, S_RENDER3, S_RENDER4, S_RENDER5, S_RENDER6, S_RENDER7,
   S_RENDER8, S_RENDER9, S_RENDER10, S_RENDER11,
+  S_FAST0, S_FAST1, S_FAST2,
   S_COUNT
 };
 
@@ -69,6 +70,8 @@ struct pm_ctx {
   float last_kernel_ms = 0.f;
   int64_t last_fallbacks = 0;      /* queries of the last pm_knn / pm_gather answered by the kd-tree kernel */
   int* fb_count_dev = nullptr;     /* where the last query batch counted them (scratch) */
+  int* ho_count_dev = nullptr;     /* queries the descriptor fast path handed to k_grid_query (scratch) */
+  int64_t last_handovers = 0;
   pm::Scratch scratch[pm::S_COUNT];
 
   /* returns a device buffer of at least `bytes` in slot `slot` (contents undefined) */
@@ -114,6 +117,7 @@ struct pm_map {
   float cell = 0.f, inv_cell = 0.f, cell_margin = 0.f;
   int gdim[3] = {0, 0, 0};
   float tuned_rk = 0.f;                      /* sampled k-th neighbour distance the cell size came from */
+  bool fast_path = false;                    /* uniform-like cloud: k_fast_prep + k_grid_fast answer most queries */
 };
 
 namespace pm {

@@ -285,6 +285,7 @@ int run_queries(pm_ctx* ctx, const pm_map* map, pmk::QueryIO io, bool gather, bo
   PM_CHECK(sort_queries(ctx, map, io.q, gather ? io.brdf : nullptr, io.nq, &perm));
   io.order = perm;
   ctx->fb_count_dev = nullptr;
+  ctx->ho_count_dev = nullptr;
   if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   if (map->grid_pts) {
     int *fb_list = nullptr, *fb_count = nullptr;
@@ -303,12 +304,14 @@ int run_queries(pm_ctx* ctx, const pm_map* map, pmk::QueryIO io, bool gather, bo
 
 /* end of a synchronous query call: wait, then read the kernel time and the fallback count */
 int finish_stats(pm_ctx* ctx, const pm_map* map) {
-  int fb = 0;
+  int fb = 0, ho = 0;
   const bool have = map && map->n >= 1;
   if (have && ctx->fb_count_dev) PM_CUDA(cudaMemcpyAsync(&fb, ctx->fb_count_dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  if (have && ctx->ho_count_dev) PM_CUDA(cudaMemcpyAsync(&ho, ctx->ho_count_dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   PM_CUDA(cudaStreamSynchronize(ctx->stream));
   if (have) PM_CUDA(cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev0, ctx->ev1));
   ctx->last_fallbacks = have && ctx->fb_count_dev ? fb : (have ? -1 : 0);
+  ctx->last_handovers = have && ctx->ho_count_dev ? ho : 0;
   return PM_OK;
 }
 
