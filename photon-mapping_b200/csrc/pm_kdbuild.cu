@@ -171,6 +171,156 @@ __global__ void k_partition(int n, int level_first, const int* __restrict__ seg_
   ord_out[dst] = e;
 }
 
+/* ---- the last kLocalLevels levels: one CTA per subtree, everything in shared memory ----------
+ * Once a subtree holds at most kLocalCap elements its three index lists, coordinates and segment tables
+ * fit in shared memory, and the remaining levels (the same split / mark / stable-partition steps as
+ * above, on 16-bit local ids) cost no global traffic beyond one read of the lists and the node writes.
+ * At 10 M photons this replaces 10 of 24 level passes over the whole array. */
+constexpr int kLocalLevels = 10;
+constexpr int kLocalCap = (1 << kLocalLevels) - 1; /* elements of a subtree with kLocalLevels levels */
+constexpr int kLocalThreads = 256;
+constexpr int kLocalItems = 4;                     /* positions per thread: 256 * 4 >= kLocalCap */
+constexpr int kLocalSegs = 1 << (kLocalLevels - 1);
+constexpr uint16_t kDead16 = 0xffffu;
+
+struct LocalSmem {
+  float c[3][kLocalCap + 1];
+  int gid[kLocalCap + 1];
+  uint32_t scanv[kLocalCap + 1];
+  uint16_t lst[2][3][kLocalCap + 1];
+  uint16_t segid[2][kLocalCap + 1];
+  uint8_t side[kLocalCap + 1];
+  float box[2][kLocalSegs][6];
+  uint16_t seg_begin[2][kLocalSegs];
+  uint16_t seg_pivot[kLocalSegs];
+  uint8_t seg_dim[kLocalSegs];
+};
+
+__global__ void __launch_bounds__(kLocalThreads)
+k_finish_subtrees(int level_first, int level_count, int n, const int* __restrict__ ord0, const int* __restrict__ ord1,
+                  const int* __restrict__ ord2, const float* __restrict__ cx, const float* __restrict__ cy,
+                  const float* __restrict__ cz, const float* __restrict__ box_cur, const int* __restrict__ begin_cur,
+                  int* __restrict__ local_of, int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  LocalSmem& sm = *reinterpret_cast<LocalSmem*>(smem_raw);
+  using Scan = cub::BlockScan<uint32_t, kLocalThreads>;
+  __shared__ typename Scan::TempStorage scan_tmp;
+  const int j = blockIdx.x;
+  if (j >= level_count) return;
+  const int s0 = level_first + j;
+  const int begin0 = begin_cur[j];
+  const int m = (int)subtree_size(s0, n);
+  const int tid = threadIdx.x;
+
+  for (int i = tid; i < m; i += kLocalThreads) {
+    const int e = ord0[begin0 + i];
+    sm.gid[i] = e;
+    sm.c[0][i] = cx[e]; sm.c[1][i] = cy[e]; sm.c[2][i] = cz[e];
+    sm.lst[0][0][i] = (uint16_t)i;
+    sm.segid[0][i] = 0;
+    local_of[e] = i;
+  }
+  if (tid < 6) sm.box[0][0][tid] = box_cur[(size_t)j * 6 + tid];
+  if (tid == 0) sm.seg_begin[0][0] = 0;
+  __threadfence_block();
+  __syncthreads();
+  for (int i = tid; i < m; i += kLocalThreads) {
+    sm.lst[0][1][i] = (uint16_t)local_of[ord1[begin0 + i]];
+    sm.lst[0][2][i] = (uint16_t)local_of[ord2[begin0 + i]];
+  }
+  __syncthreads();
+
+  int cur = 0;
+  for (int t = 0;; t++) {
+    const int64_t first = ((int64_t)(s0 + 1) << t) - 1; /* first node of this subtree's level t */
+    if (first >= n) break;
+    const int nseg = (int)min((int64_t)1 << t, (int64_t)n - first);
+    const int tb = t & 1;
+    /* split: one thread per node of the level */
+    for (int q = tid; q < nseg; q += kLocalThreads) {
+      const int s = (int)first + q;
+      float box[6];
+#pragma unroll
+      for (int d = 0; d < 6; d++) box[d] = sm.box[tb][q][d];
+      const int dim = widest_dim(box);
+      const int begin = sm.seg_begin[tb][q];
+      const int64_t lchild = 2 * (int64_t)s + 1;
+      const int left = lchild < n ? (int)subtree_size(lchild, n) : 0;
+      const int pivot = begin + left;
+      const int el = sm.lst[cur][dim][pivot];
+      const float split = sm.c[dim][el];
+      elem_of_node[s] = sm.gid[el];
+      dim_of_node[s] = (uint8_t)dim;
+      sm.seg_pivot[q] = (uint16_t)pivot;
+      sm.seg_dim[q] = (uint8_t)dim;
+      if (t + 1 < kLocalLevels) {
+        if (lchild < n) {
+#pragma unroll
+          for (int d = 0; d < 6; d++) sm.box[tb ^ 1][2 * q][d] = box[d];
+          sm.box[tb ^ 1][2 * q][3 + dim] = fminf(split, box[3 + dim]);
+          sm.seg_begin[tb ^ 1][2 * q] = (uint16_t)begin;
+        }
+        if (lchild + 1 < n) {
+#pragma unroll
+          for (int d = 0; d < 6; d++) sm.box[tb ^ 1][2 * q + 1][d] = box[d];
+          sm.box[tb ^ 1][2 * q + 1][dim] = fmaxf(split, box[dim]);
+          sm.seg_begin[tb ^ 1][2 * q + 1] = (uint16_t)(pivot + 1);
+        }
+      }
+    }
+    __syncthreads();
+    if (2 * first + 1 >= n || t + 1 >= kLocalLevels) break; /* no level below */
+    /* mark: the element found at position i of its segment's split-axis list goes left / right / is the pivot */
+    for (int i = tid; i < m; i += kLocalThreads) {
+      const uint16_t sg = sm.segid[tb][i];
+      if (sg == kDead16) { sm.segid[tb ^ 1][i] = kDead16; continue; }
+      const int piv = sm.seg_pivot[sg];
+      const int el = sm.lst[cur][sm.seg_dim[sg]][i];
+      sm.side[el] = i < piv ? 0 : (i > piv ? 1 : 2);
+      sm.segid[tb ^ 1][i] = i < piv ? (uint16_t)(2 * sg) : (i > piv ? (uint16_t)(2 * sg + 1) : kDead16);
+    }
+    __syncthreads();
+    /* stable partition of the three lists inside every segment */
+    for (int d = 0; d < 3; d++) {
+      uint32_t f[kLocalItems], ex[kLocalItems];
+#pragma unroll
+      for (int it = 0; it < kLocalItems; it++) {
+        const int i = tid * kLocalItems + it;
+        f[it] = 0u;
+        if (i < m && sm.segid[tb][i] != kDead16) {
+          const uint8_t sd = sm.side[sm.lst[cur][d][i]];
+          f[it] = sd == 0 ? 1u : (sd == 1 ? 1u << 16 : 0u);
+        }
+      }
+      Scan(scan_tmp).ExclusiveSum(f, ex);
+#pragma unroll
+      for (int it = 0; it < kLocalItems; it++) {
+        const int i = tid * kLocalItems + it;
+        if (i < m) sm.scanv[i] = ex[it];
+      }
+      __syncthreads();
+#pragma unroll
+      for (int it = 0; it < kLocalItems; it++) {
+        const int i = tid * kLocalItems + it;
+        if (i >= m) continue;
+        const uint16_t sg = sm.segid[tb][i];
+        if (sg == kDead16) continue;
+        const int begin = sm.seg_begin[tb][sg], pivot = sm.seg_pivot[sg];
+        const uint16_t el = sm.lst[cur][d][i];
+        const uint8_t sd = sm.side[el];
+        const uint32_t here = ex[it], base = sm.scanv[begin];
+        int dst;
+        if (sd == 0) dst = begin + (int)((here & 0xffffu) - (base & 0xffffu));
+        else if (sd == 1) dst = pivot + 1 + (int)((here >> 16) - (base >> 16));
+        else dst = pivot;
+        sm.lst[cur ^ 1][d][dst] = el;
+      }
+      __syncthreads();
+    }
+    cur ^= 1;
+  }
+}
+
 /* final gather: node j <- element elem_of_node[j]; 11 threads per record so that both the random
  * 44-byte read and the streaming write are full-width */
 __global__ void k_emit_nodes(int n, const int* __restrict__ elem_of_node, const uint8_t* __restrict__ dim_of_node,
@@ -300,9 +450,18 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   PM_BC(cudaMemsetAsync(seg[0], 0, sizeof(int) * (size_t)n, st)); /* everything starts in subtree 0 */
 
   int cur = 0;
+  const int local_from = num_levels > kLocalLevels ? num_levels - kLocalLevels : 0; /* first level finished per CTA */
   for (int L = 0; L < num_levels; L++) {
     const int level_first = (1 << L) - 1;
     const int level_count = (n - level_first < (1 << L)) ? n - level_first : (1 << L);
+    if (L == local_from) {
+      PM_BC(cudaFuncSetAttribute(k_finish_subtrees, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSmem)));
+      k_finish_subtrees<<<(unsigned)level_count, kLocalThreads, sizeof(LocalSmem), st>>>(
+          level_first, level_count, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
+          reinterpret_cast<int*>(scan), elem_of_node, dim_of_node);
+      ctx->launches++;
+      break;
+    }
     k_split<<<(unsigned)pm::div_up(level_count, 128), 128, 0, st>>>(
         level_first, level_count, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
         box[(L + 1) & 1], begin[(L + 1) & 1], seg_pivot, seg_dim, elem_of_node, dim_of_node);
