@@ -208,6 +208,20 @@ int  pm_render(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host, 
                int width, int height, int spp, int depth, const float sky[3],
                int64_t pixel_begin, int64_t pixel_end, uint32_t* fb_rgba8);
 
+/* ---- photon viewer (≙ photonViewer: photon-viewer/src/hostCode.cu:53-75 + photon-viewer/cuda/deviceCode.cu:10-49) --
+ * Splats photons into a W*H RGBA8 image: each photon is projected with the reference's glm::lookAt /
+ * glm::perspective(fovy, W/H, 0.1, 1000) pipeline (pixel = int((ndc + 1) * 0.5 * size), y flipped as H - int(..);
+ * clip z < 0 is dropped), tested for occlusion with a ray from the camera (tmin 1e-3, tmax = |photon - camera| - 1e-4)
+ * and, if visible, its pixel receives make_rgba(color). Pixels no photon reaches keep 0xFF000000. The reference
+ * leaves the winner among several photons of one pixel to a data race; here the photon with the HIGHEST index
+ * wins (what a sequential run of the reference's launch would leave). photons / fb: host or device. */
+int  pm_view_photons(pm_ctx* ctx, const pm_scene* scene, const pm_photon40* photons, int64_t n,
+                     const float look_from[3], const float look_at[3], const float look_up[3], float fovy,
+                     int width, int height, uint32_t* fb_rgba8);
+/* the 4x4 projection * view matrix (column-major, glm layout) pm_view_photons uses: test hook */
+void pm_view_matrix(const float look_from[3], const float look_at[3], const float look_up[3], float fovy,
+                    int width, int height, float out16[16]);
+
 /* ---- photon wire format (≙ writeAlivePhotons / readPhotonsFromFile) ------------------ */
 /* text: 9 floats "pos dir color", std::fixed, 6 decimals (photon-mapping/src/hostCode.cu:31-49) */
 int  pm_photons_write_text(const char* path, const pm_photon40* photons_host, int64_t n);

@@ -74,6 +74,9 @@ _SIGNATURES = {
     "pm_knn": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "pm_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p]),
     "pm_gather_radius": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "pm_view_photons": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int,
+                                c_void_p]),
+    "pm_view_matrix": (None, [c_void_p, c_void_p, c_void_p, c_float, c_int, c_int, c_void_p]),
     "pm_render": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
@@ -313,6 +316,15 @@ class Scene:
         hits = np.empty(len(rays), HIT)
         _check(lib().pm_trace_closest(self.ctx.handle, self.handle, rays.ctypes.data, len(rays), hits.ctypes.data))
         return hits
+
+    def view_photons(self, photons: np.ndarray, look_from, look_at, look_up, fovy: float, width: int, height: int) -> np.ndarray:
+        """pm_view_photons (≙ photonViewer): RGBA8 image (height, width) of the photons visible from the camera."""
+        photons = np.ascontiguousarray(photons, PHOTON40).reshape(-1)
+        cam = [np.ascontiguousarray(v, np.float32).reshape(3) for v in (look_from, look_at, look_up)]
+        fb = np.empty((height, width), np.uint32)
+        _check(lib().pm_view_photons(self.ctx.handle, self.handle, photons.ctypes.data, len(photons), cam[0].ctypes.data,
+                                     cam[1].ctypes.data, cam[2].ctypes.data, float(fovy), width, height, fb.ctypes.data))
+        return fb
 
     def trace_occluded(self, rays: np.ndarray) -> np.ndarray:
         rays = np.ascontiguousarray(rays, RAY)

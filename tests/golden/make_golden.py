@@ -3,6 +3,7 @@
 
 CPU part (runs here):   kdtree_ref.npz  — cukd::buildTree_host output for fixed inputs
                         lcg_kat.json    — owl::LCG<4> draws, owl normalize
+                        view_ref.npz    — the photon viewer's glm projection (photon-viewer/src/hostCode.cu:53-75)
 GPU part (--gpu, run on the B200 box through gpurun; writes into gpurun_out/ to travel back):
                         knn_ref.npz     — cukd::stackBased::knn<HeapCandidateList<k>> results
 """
@@ -52,6 +53,33 @@ def cpu():
     with open(os.path.join(HERE, "lcg_kat.json"), "w") as f:
         json.dump(kat, f, indent=1)
     print("wrote kdtree_ref.npz, lcg_kat.json")
+    view()
+
+
+VIEW_CASES = [((80, 30, 0), (10, 20, 0), (0, 1, 0), 0.87, 512, 512),          # config.toml.example camera
+              ((1.5, -2, 7), (0.3, 0.2, 0.1), (0.1, 1, 0.05), 1.2, 1920, 1080),
+              ((-30, 55, 20), (4, 4, 4), (0, 0, 1), 0.5, 333, 777)]
+
+
+def view():
+    """glm::lookAt / glm::perspective / mat4 * vec4 and the pixel rule, run with the reference's own glm."""
+    g = ctypes.CDLL(os.path.join(ROOT, "oracle", "_ref", "libglm_ref.so"))
+    rng = np.random.default_rng(2024)
+    out = {}
+    for i, (frm, at, up, fovy, W, H) in enumerate(VIEW_CASES):
+        frm, at, up = (np.array(v, np.float32) for v in (frm, at, up))
+        m = np.zeros(16, np.float32)
+        g.ref_glm_matrix(vp(frm), vp(at), vp(up), ctypes.c_float(fovy), W, H, vp(m))
+        n = 6000
+        pos = (rng.random((n, 3), dtype=np.float32) * np.float32(120) - np.float32(40)).astype(np.float32)
+        pix = np.zeros((n, 2), np.int32)
+        g.ref_glm_project(vp(frm), vp(at), vp(up), ctypes.c_float(fovy), W, H, vp(pos), ctypes.c_int64(n), vp(pix))
+        out[f"cam_{i}"] = np.concatenate([frm, at, up, np.array([fovy, W, H], np.float32)])
+        out[f"matrix_{i}"] = m
+        out[f"pos_{i}"] = pos
+        out[f"pix_{i}"] = pix
+    np.savez_compressed(os.path.join(HERE, "view_ref.npz"), **out)
+    print("wrote view_ref.npz")
 
 
 def gpu():

@@ -307,6 +307,11 @@ depth = {depth}
 max_depth = {max_depth}
 casted_diffuse_photons = {casted[0]:_}
 casted_caustics_photons = {casted[1]:_}
+
+[photon-viewer]
+output_filename = "{out_png}.viewer.png"
+caustics_output_filename = "{out_png}.caustics-viewer.png"
+fb_size = [{W}, {H}]
 """)
 
 

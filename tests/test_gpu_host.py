@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 def test_two_pass_workflow_matches_python_host(pkg, ctx, tmp_path):
     import importlib.util
 
-    for exe in ("photonMapping", "rayTracer"):
+    for exe in ("photonMapping", "rayTracer", "photonViewer"):
         assert os.path.exists(os.path.join(HOST_DIR, exe)), "hosts are built by __graft_entry__.build()"
     sc0 = load_scene("cornell_box")
     glb = write_scene_files(str(tmp_path), sc0, "box")
@@ -54,3 +54,10 @@ def test_two_pass_workflow_matches_python_host(pkg, ctx, tmp_path):
     a, b = img.view(np.uint8).reshape(H, W, 4).astype(int), fb.view(np.uint8).reshape(H, W, 4).astype(int)
     assert (np.abs(a - b) <= 1).mean() > 0.995 and (a[..., 3] == b[..., 3]).all()
     assert (img[1:] != 0).any()
+    # third executable: the photon viewer on the same files (≙ photonViewer), against the binding
+    r = subprocess.run([os.path.join(HOST_DIR, "photonViewer"), cfg], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    for path, photons in ((png + ".viewer.png", got_g), (png + ".caustics-viewer.png", got_c)):
+        want = scene.view_photons(photons, (80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87, W, H)
+        assert np.array_equal(read_png_rgba8(path), want)
+    assert (read_png_rgba8(png + ".viewer.png") != 0xFF000000).sum() > 500
