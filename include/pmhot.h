@@ -77,6 +77,17 @@ typedef struct pm_light {
   double power;
 } pm_light;
 
+/* emitter shapes: LightSource::source_type / normal / side_length (common/src/world.h:8-20). The reference declares
+ * them and parses every light as POINT_LIGHT (common/src/assetImporter.cxx:122); the square emitter is ours
+ * (SURVEY §8f rank 4): uniform point on the square centred at pm_light::pos, cosine-distributed direction. */
+#define PM_LIGHT_POINT  0
+#define PM_LIGHT_SQUARE 1
+typedef struct pm_light_shape {
+  int32_t type;
+  float   normal[3];
+  float   side_length;
+} pm_light_shape;
+
 /* ray-tracer/include/deviceCode.h:29-34 (already set up as in hostCode.cu:100-108) */
 typedef struct pm_camera {
   float pos[3];
@@ -157,6 +168,14 @@ int  pm_emit_photons_keyed(pm_ctx* ctx, const pm_scene* scene, const pm_light* l
                            uint64_t seed, int rng_mode, int64_t first_photon, int64_t photon_stride,
                            pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
                            int64_t* n_paths, int64_t* n_segments);
+
+/* pm_emit_photons_keyed with one pm_light_shape per light (shapes == NULL: all point lights; out_keys may be NULL) */
+int  pm_emit_photons_shaped(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host,
+                            const pm_light_shape* shapes_host, int n_lights,
+                            int64_t casted, int max_depth, int caustics_mode,
+                            uint64_t seed, int rng_mode, int64_t first_photon, int64_t photon_stride,
+                            pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
+                            int64_t* n_paths, int64_t* n_segments);
 
 /* pass-1 → pass-2 record conversion done by ray-tracer/src/hostCode.cu:65-83:
  * global map = non-caustic (power 1.0) followed by caustic (power 0.5); caustic map = caustic (0.5).

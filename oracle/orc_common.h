@@ -162,6 +162,19 @@ template <class R> static inline vec3 randomUnitVector(R& rng) {
 template <class R> static inline vec3 cosineSampleHemisphere(vec3 n, R& rng) {
   return normalize(n + randomPointInUnitSphere(rng) * (1 - ORC_EPS));
 }
+/* square emitter: LightSource::normal / side_length (common/src/world.h:17-20) are declared by the reference but
+ * never read (assetImporter.cxx:122 makes every light a point light), so these semantics are ours: uniform point on
+ * the square, cosine-distributed direction about the normal; draw order u, v, then cosineSampleHemisphere's two. */
+template <class R> static inline void sampleSquareLight(vec3 pos, vec3 nrm, float side, R& rng, vec3* org, vec3* dir) {
+  const vec3 n = normalize(nrm);
+  const vec3 a = fabsf(n.x) > 0.9f ? v3(0.f, 1.f, 0.f) : v3(1.f, 0.f, 0.f);
+  const vec3 t = normalize(cross(a, n));
+  const vec3 b = cross(n, t);
+  const float u = rng.next();
+  const float v = rng.next();
+  *org = pos + ((u - 0.5f) * side) * t + ((v - 0.5f) * side) * b;
+  *dir = cosineSampleHemisphere(n, rng);
+}
 /* helpers.h:49-51: incoming - 2.f*dot(incoming,normal)*normal */
 static inline vec3 reflect(vec3 in, vec3 n) { return in - (2.f * dot(in, n)) * n; }
 /* helpers.h:57-74 (3-argument refract used by pass 1) */

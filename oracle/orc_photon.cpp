@@ -52,11 +52,13 @@ int trace_and_scatter(const Scene& sc, vec3 org, vec3 dir, vec3 color, Rng& rng,
 }
 
 /* one launch index of one light; appends to `store` */
-void walk(const Scene& sc, const pm_light& L, int max_depth, bool caustics, Rng rng, std::vector<pm_photon40>& store,
-          int64_t* segments) {
+void walk(const Scene& sc, const pm_light& L, const pm_light_shape* shape, int max_depth, bool caustics, Rng rng,
+          std::vector<pm_photon40>& store, int64_t* segments) {
   vec3 color = v3(L.rgb);
   vec3 org = v3(L.pos);
-  vec3 dir = randomPointInUnitSphere(rng);
+  vec3 dir;
+  if (shape && shape->type == PM_LIGHT_SQUARE) sampleSquareLight(v3(L.pos), v3(shape->normal), shape->side_length, rng, &org, &dir);
+  else dir = randomPointInUnitSphere(rng);
   for (int i = 0; i < max_depth; i++) {
     Scattered s;
     const int ev = trace_and_scatter(sc, org, dir, color, rng, &s);
@@ -90,11 +92,11 @@ int64_t orc_light_paths(const pm_light* lights, int n_lights, int64_t casted, in
 
 /* Same contract as pm_emit_photons. Returns the number of photons (also when it exceeds capacity;
  * only the first `capacity` are written). */
-int64_t orc_emit_photons(const float* verts, int nv, const int32_t* tris, int nt, const int32_t* tri_mesh,
-                         const pm_material* mats, int n_mesh, const pm_light* lights, int n_lights, int64_t casted,
-                         int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
-                         int64_t photon_stride, pm_photon40* out, int64_t capacity, int64_t* n_paths,
-                         int64_t* n_segments) {
+int64_t orc_emit_photons_shaped(const float* verts, int nv, const int32_t* tris, int nt, const int32_t* tri_mesh,
+                                const pm_material* mats, int n_mesh, const pm_light* lights, const pm_light_shape* shapes,
+                                int n_lights, int64_t casted, int max_depth, int caustics_mode, uint64_t seed, int rng_mode,
+                                int64_t first_photon, int64_t photon_stride, pm_photon40* out, int64_t capacity,
+                                int64_t* n_paths, int64_t* n_segments) {
   Scene sc{verts, nv, tris, nt, tri_mesh, mats, n_mesh};
   int64_t written = 0, paths = 0, segs = 0;
   for (int l = 0; l < n_lights; l++) {
@@ -114,7 +116,7 @@ int64_t orc_emit_photons(const float* verts, int nv, const int32_t* tris, int nt
         Rng rng;
         if (rng_mode == PM_RNG_LCG_PARITY) rng.init_lcg((uint32_t)idx, 0u); /* deviceCode.cu:59, id.y == 0 */
         else rng.init_counter(seed, ((uint64_t)((caustics_mode ? n_lights : 0) + l) << 32) | (uint64_t)idx);
-        walk(sc, lights[l], max_depth, caustics_mode != 0, rng, parts[t], &part_segs[t]);
+        walk(sc, lights[l], shapes ? &shapes[l] : nullptr, max_depth, caustics_mode != 0, rng, parts[t], &part_segs[t]);
       }
     }
     for (int t = 0; t < nth; t++) {
@@ -128,6 +130,15 @@ int64_t orc_emit_photons(const float* verts, int nv, const int32_t* tris, int nt
   if (n_paths) *n_paths = paths;
   if (n_segments) *n_segments = segs;
   return written;
+}
+
+int64_t orc_emit_photons(const float* verts, int nv, const int32_t* tris, int nt, const int32_t* tri_mesh,
+                         const pm_material* mats, int n_mesh, const pm_light* lights, int n_lights, int64_t casted,
+                         int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
+                         int64_t photon_stride, pm_photon40* out, int64_t capacity, int64_t* n_paths,
+                         int64_t* n_segments) {
+  return orc_emit_photons_shaped(verts, nv, tris, nt, tri_mesh, mats, n_mesh, lights, nullptr, n_lights, casted, max_depth,
+                                 caustics_mode, seed, rng_mode, first_photon, photon_stride, out, capacity, n_paths, n_segments);
 }
 
 /* record conversion of ray-tracer/src/hostCode.cu:65-83 */

@@ -28,6 +28,8 @@ MATERIAL = np.dtype(
     [("albedo", "<f4", 3), ("diffuse", "<f4"), ("specular", "<f4"), ("transmission", "<f4"), ("refraction_idx", "<f4")]
 )
 LIGHT = np.dtype([("pos", "<f4", 3), ("rgb", "<f4", 3), ("power", "<f8")])
+LIGHT_SHAPE = np.dtype([("type", "<i4"), ("normal", "<f4", 3), ("side_length", "<f4")])
+LIGHT_POINT, LIGHT_SQUARE = 0, 1
 CAMERA = np.dtype([("pos", "<f4", 3), ("dir_00", "<f4", 3), ("dir_du", "<f4", 3), ("dir_dv", "<f4", 3)])
 RAY = np.dtype([("org", "<f4", 3), ("tmin", "<f4"), ("dir", "<f4", 3), ("tmax", "<f4")])
 HIT = np.dtype([("prim", "<i4"), ("t", "<f4")])
@@ -64,6 +66,11 @@ _SIGNATURES = {
     "pm_emit_photons_keyed": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p,
+         c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64)],
+    ),
+    "pm_emit_photons_shaped": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p,
          c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64)],
     ),
     "pm_photons_to_maps": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
@@ -348,15 +355,24 @@ class Scene:
 
     def emit_photons(self, lights: np.ndarray, casted: int, max_depth: int, caustics: bool, seed: int = 0,
                      rng_mode: int = RNG_LCG_PARITY, first_photon: int = 0, photon_stride: int = 1, out=None,
-                     capacity: int | None = None):
+                     capacity: int | None = None, shapes: np.ndarray | None = None):
         """≙ runNormal / runCaustics (photon-mapping/src/hostCode.cu:112-138).
-        Returns (photons[:count], n_paths, n_segments)."""
+        Returns (photons[:count], n_paths, n_segments). `shapes` (LIGHT_SHAPE per light) selects square emitters."""
         lights = np.ascontiguousarray(lights, LIGHT)
         if capacity is None:
             capacity = int(casted) * int(max_depth)  # hostCode.cu:93
         if out is None:
             out = np.empty(capacity, PHOTON40)
         count, npaths, nseg = c_int64(0), c_int64(0), c_int64(0)
+        if shapes is not None:
+            shapes = np.ascontiguousarray(shapes, LIGHT_SHAPE).reshape(-1)
+            assert len(shapes) == len(lights)
+            _check(lib().pm_emit_photons_shaped(self.ctx.handle, self.handle, lights.ctypes.data, shapes.ctypes.data, len(lights),
+                                                casted, max_depth, 1 if caustics else 0, seed, rng_mode, first_photon,
+                                                photon_stride, _ptr(out), None, capacity, ctypes.byref(count),
+                                                ctypes.byref(npaths), ctypes.byref(nseg)))
+            res = out[: count.value] if isinstance(out, np.ndarray) else out
+            return res, count.value, npaths.value, nseg.value
         _check(lib().pm_emit_photons(self.ctx.handle, self.handle, lights.ctypes.data, len(lights), casted, max_depth,
                                      1 if caustics else 0, seed, rng_mode, first_photon, photon_stride, _ptr(out),
                                      capacity, ctypes.byref(count), ctypes.byref(npaths), ctypes.byref(nseg)))

@@ -147,6 +147,20 @@ template <class R> __device__ __forceinline__ vec3 randomUnitVector(R& rng) {
 template <class R> __device__ __forceinline__ vec3 cosineSampleHemisphere(vec3 n, R& rng) {
   return normalize(n + randomPointInUnitSphere(rng) * (1 - PMD_EPS));
 }
+/* square emitter (LightSource::normal / side_length, common/src/world.h:17-20 — declared by the reference, never
+ * read by it; semantics are ours): a point uniform on the square of side `side` centred at `pos` in the plane
+ * orthogonal to `nrm`, direction cosine-distributed about `nrm` with the reference's diffuse sampler. Draw order:
+ * u, v (position), then the two draws of cosineSampleHemisphere. */
+template <class R> __device__ __forceinline__ void sampleSquareLight(vec3 pos, vec3 nrm, float side, R& rng, vec3* org, vec3* dir) {
+  const vec3 n = normalize(nrm);
+  const vec3 a = fabsf(n.x) > 0.9f ? v3(0.f, 1.f, 0.f) : v3(1.f, 0.f, 0.f);
+  const vec3 t = normalize(cross(a, n));
+  const vec3 b = cross(n, t);
+  const float u = rng.next();
+  const float v = rng.next();
+  *org = pos + ((u - 0.5f) * side) * t + ((v - 0.5f) * side) * b;
+  *dir = cosineSampleHemisphere(n, rng);
+}
 /* helpers.h:49-51 */
 __device__ __forceinline__ vec3 reflect(vec3 in, vec3 n) { return in - (2.f * dot(in, n)) * n; }
 /* helpers.h:57-74 */

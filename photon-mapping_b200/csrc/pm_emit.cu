@@ -31,6 +31,7 @@ struct EmitParams {
   int64_t light_first[kMaxLights + 1]; /* prefix of this rank's path counts per light */
   float light_pos[kMaxLights][3];
   float light_rgb[kMaxLights][3];
+  float light_shape[kMaxLights][4]; /* normal, side length; side <= 0: point light */
   int max_depth, caustics, rng_mode;
   uint64_t seed;
   int64_t first_photon, photon_stride;
@@ -84,7 +85,8 @@ k_walk(const EmitParams P, unsigned long long* __restrict__ next_path, pm_photon
           else rng.init_counter(P.seed, ((uint64_t)((P.caustics ? P.n_lights : 0) + l) << 32) | (uint64_t)idx);
           color = v3(P.light_rgb[l]);
           org = v3(P.light_pos[l]);
-          dir = randomPointInUnitSphere(rng); /* deviceCode.cu:64 */
+          if (P.light_shape[l][3] > 0.f) sampleSquareLight(org, v3(P.light_shape[l]), P.light_shape[l][3], rng, &org, &dir);
+          else dir = randomPointInUnitSphere(rng); /* deviceCode.cu:64 */
           depth = 0; stored = 0;
           active = P.max_depth > 0;
           if (!active) counts[local] = 0;
@@ -196,7 +198,7 @@ __global__ void k_conv44(int64_t n, const pm_photon40* __restrict__ in, float po
 
 extern "C" {
 
-static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_lights, int64_t casted,
+static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, const pm_light_shape* shapes, int n_lights, int64_t casted,
                      int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
                      int64_t photon_stride, pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
                      int64_t* n_paths, int64_t* n_segments) {
@@ -228,6 +230,13 @@ static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights,
     const int64_t mine = n > first_photon ? (n - first_photon + photon_stride - 1) / photon_stride : 0;
     P.light_first[l + 1] = P.light_first[l] + mine;
     for (int d = 0; d < 3; d++) { P.light_pos[l][d] = lights[l].pos[d]; P.light_rgb[l][d] = lights[l].rgb[d]; }
+    if (shapes && shapes[l].type == PM_LIGHT_SQUARE) {
+      PM_REQUIRE(shapes[l].side_length > 0.f, "square light needs side_length > 0");
+      for (int d = 0; d < 3; d++) P.light_shape[l][d] = shapes[l].normal[d];
+      P.light_shape[l][3] = shapes[l].side_length;
+    } else {
+      PM_REQUIRE(!shapes || shapes[l].type == PM_LIGHT_POINT, "unknown light type");
+    }
   }
   const int64_t total_paths = P.light_first[n_lights];
   P.max_depth = max_depth; P.caustics = caustics_mode ? 1 : 0; P.rng_mode = rng_mode; P.seed = seed;
@@ -334,7 +343,7 @@ int pm_emit_photons(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, 
                     int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
                     int64_t photon_stride, pm_photon40* out, int64_t capacity, int64_t* count, int64_t* n_paths,
                     int64_t* n_segments) {
-  return emit_impl(ctx, scene, lights, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
+  return emit_impl(ctx, scene, lights, nullptr, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
                    photon_stride, out, nullptr, capacity, count, n_paths, n_segments);
 }
 
@@ -343,7 +352,15 @@ int pm_emit_photons_keyed(pm_ctx* ctx, const pm_scene* scene, const pm_light* li
                           int64_t photon_stride, pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
                           int64_t* n_paths, int64_t* n_segments) {
   PM_REQUIRE(out_keys || capacity == 0, "out_keys is NULL");
-  return emit_impl(ctx, scene, lights, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
+  return emit_impl(ctx, scene, lights, nullptr, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
+                   photon_stride, out, out_keys, capacity, count, n_paths, n_segments);
+}
+
+int pm_emit_photons_shaped(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, const pm_light_shape* shapes, int n_lights,
+                           int64_t casted, int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
+                           int64_t photon_stride, pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
+                           int64_t* n_paths, int64_t* n_segments) {
+  return emit_impl(ctx, scene, lights, shapes, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
                    photon_stride, out, out_keys, capacity, count, n_paths, n_segments);
 }
 

@@ -72,8 +72,9 @@ int main(int argc, char** argv) {
       std::vector<pm_photon40> photons((size_t)std::max<long long>(p.casted, 0) * (size_t)std::max(max_depth, 1));
       int64_t count = 0, paths = 0, segments = 0;
       const auto t0 = std::chrono::steady_clock::now();
-      check(pm_emit_photons(ctx, scene, world.light_sources.data(), (int)world.light_sources.size(), p.casted, max_depth, p.caustics,
-                            seed, rng_mode, 0, 1, photons.data(), (int64_t)photons.size(), &count, &paths, &segments));
+      check(pm_emit_photons_shaped(ctx, scene, world.light_sources.data(), world.light_shapes.data(), (int)world.light_sources.size(),
+                                   p.casted, max_depth, p.caustics, seed, rng_mode, 0, 1, photons.data(), nullptr,
+                                   (int64_t)photons.size(), &count, &paths, &segments));
       const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
       LOG_OK(p.what << " pass: " << paths << " paths, " << segments << " segments, " << count << " photons stored in " << ms
                     << " ms (device " << pm_ctx_last_kernel_ms(ctx) << " ms)");

@@ -5,7 +5,8 @@
 //     by exact equality in first-seen order over the face stream (:54-78) — done with a hash map
 //     instead of the reference's O(V^2) std::find, same output;
 //   * mesh name = material name (:88-92), used to look the material up in <model>.mtl (:139-214);
-//   * lights.txt beside the model, "posx posy posz r g b power" (:98-137); missing file throws.
+//   * lights.txt beside the model, "posx posy posz r g b power" (:98-137); missing file throws. Four more values
+//     on a line ("nx ny nz side") make the light a square emitter (not in the reference).
 // Paths are used as given (the reference rewrites '/' to '\\', which only works on Windows).
 #pragma once
 #include <array>
@@ -34,6 +35,7 @@ struct Mesh {
 struct World {
   std::vector<Mesh> meshes;
   std::vector<pm_light> light_sources;
+  std::vector<pm_light_shape> light_shapes;  // one per light; lights.txt lines with 4 extra values are square emitters
   // flattened for pm_scene_create
   std::vector<float> verts;
   std::vector<int32_t> tris, tri_mesh;
@@ -209,7 +211,7 @@ inline std::vector<Mesh> extract_objects(const GlbFile& glb) {
   return meshes;
 }
 
-inline std::vector<pm_light> extract_lights(const std::string& model_path) {
+inline std::vector<pm_light> extract_lights(const std::string& model_path, std::vector<pm_light_shape>* shapes = nullptr) {
   const size_t slash = model_path.find_last_of("/\\");
   const std::string file = (slash == std::string::npos ? std::string(".") : model_path.substr(0, slash)) + "/lights.txt";
   std::ifstream f(file);
@@ -224,6 +226,11 @@ inline std::vector<pm_light> extract_lights(const std::string& model_path) {
     for (double& d : v) if (!(iss >> d)) throw std::runtime_error("Invalid light source data format");  // :124-128
     pm_light l{{(float)v[0], (float)v[1], (float)v[2]}, {(float)v[3], (float)v[4], (float)v[5]}, v[6]};
     out.push_back(l);
+    // extension (world.h:17-20 fields the reference never fills): "... power nx ny nz side" = square emitter
+    pm_light_shape sh{PM_LIGHT_POINT, {0.f, 0.f, 0.f}, 0.f};
+    double e[4];
+    if (iss >> e[0] >> e[1] >> e[2] >> e[3]) sh = pm_light_shape{PM_LIGHT_SQUARE, {(float)e[0], (float)e[1], (float)e[2]}, (float)e[3]};
+    if (shapes) shapes->push_back(sh);
   }
   return out;
 }
@@ -260,7 +267,7 @@ inline World import_scene(const std::string& path) {
   World w;
   GlbFile glb(path);
   w.meshes = extract_objects(glb);
-  w.light_sources = extract_lights(path);
+  w.light_sources = extract_lights(path, &w.light_shapes);
   assign_materials(w.meshes, path);
   w.flatten();
   return w;

@@ -24,6 +24,7 @@ MATERIAL = np.dtype(
     [("albedo", "<f4", 3), ("diffuse", "<f4"), ("specular", "<f4"), ("transmission", "<f4"), ("refraction_idx", "<f4")]
 )
 LIGHT = np.dtype([("pos", "<f4", 3), ("rgb", "<f4", 3), ("power", "<f8")])
+LIGHT_SHAPE = np.dtype([("type", "<i4"), ("normal", "<f4", 3), ("side_length", "<f4")])
 
 _COMP = {5120: "i1", 5121: "u1", 5122: "<i2", 5123: "<u2", 5125: "<u4", 5126: "<f4"}
 _NCOMP = {"SCALAR": 1, "VEC2": 2, "VEC3": 3, "VEC4": 4, "MAT4": 16}
@@ -119,6 +120,16 @@ def load_glb_meshes(path: str):
     return meshes
 
 
+def read_light_shapes(path: str) -> np.ndarray:
+    """Emitter shapes of lights.txt: lines with four extra values "nx ny nz side" are square emitters (type 1)."""
+    rows = [ln.split() for ln in open(path) if ln.strip() and ln[0] != "#"]
+    shapes = np.zeros(len(rows), LIGHT_SHAPE)
+    for i, tok in enumerate(rows):
+        if len(tok) >= 11:
+            shapes[i] = (1, tuple(float(t) for t in tok[7:10]), float(tok[10]))
+    return shapes
+
+
 def read_lights(path: str) -> np.ndarray:
     if not os.path.exists(path):
         raise RuntimeError("Unable to open file: " + path)
@@ -188,5 +199,6 @@ def import_scene(model_path: str):
         tri_mesh=np.concatenate(tri_mesh) if tri_mesh else np.zeros(0, np.int32),
         mats=mats,
         lights=lights,
+        light_shapes=read_light_shapes(os.path.join(os.path.dirname(model_path), "lights.txt")),
         names=names,
     )

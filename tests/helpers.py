@@ -174,11 +174,25 @@ def oracle_occluded(orc, sc, rays):
     return occ
 
 
-def oracle_emit(orc, sc, casted, max_depth, caustics, seed=0, rng_mode=0, first=0, stride=1, lights=None):
+LIGHT_SHAPE = np.dtype([("type", "<i4"), ("normal", "<f4", 3), ("side_length", "<f4")])
+
+
+def oracle_emit(orc, sc, casted, max_depth, caustics, seed=0, rng_mode=0, first=0, stride=1, lights=None, shapes=None):
     lights = sc["lights"] if lights is None else lights
     cap = max(1, int(casted) * max(1, max_depth))
     out = np.zeros(cap, PHOTON40)
     npaths, nseg = c_int64(0), c_int64(0)
+    if shapes is not None:
+        orc.orc_emit_photons_shaped.restype = c_int64
+        orc.orc_emit_photons_shaped.argtypes = [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                                c_int, c_int64, c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p,
+                                                c_int64, POINTER(c_int64), POINTER(c_int64)]
+        shapes = np.ascontiguousarray(shapes, LIGHT_SHAPE)
+        n = orc.orc_emit_photons_shaped(vp(sc["verts"]), len(sc["verts"]), vp(sc["tris"]), len(sc["tris"]), vp(sc["tri_mesh"]),
+                                        vp(sc["mats"]), len(sc["mats"]), vp(lights), vp(shapes), len(lights), casted, max_depth,
+                                        1 if caustics else 0, seed, rng_mode, first, stride, vp(out), cap,
+                                        ctypes.byref(npaths), ctypes.byref(nseg))
+        return out[:n].copy(), npaths.value, nseg.value
     n = orc.orc_emit_photons(vp(sc["verts"]), len(sc["verts"]), vp(sc["tris"]), len(sc["tris"]), vp(sc["tri_mesh"]),
                              vp(sc["mats"]), len(sc["mats"]), vp(lights), len(lights), casted, max_depth,
                              1 if caustics else 0, seed, rng_mode, first, stride, vp(out), cap, ctypes.byref(npaths),

