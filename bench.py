@@ -149,11 +149,14 @@ def peaks():
 
 
 def traffic_per_launch():
-    """dram bytes per launch of the kNN kernel (k_grid_query) from the committed ncu capture, or None."""
+    """dram bytes per 1M-query launch of the kNN kernels (descriptor pass + streaming kernel) from the committed
+    ncu capture, or None."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("k_grid_query_k64_dram_bytes_per_launch")
+            j = json.load(open(p))
+            a, b = j.get("k_grid_fast_k64_dram_bytes_per_launch"), j.get("k_fast_prep_k64_dram_bytes_per_launch")
+            return a + b if a is not None and b is not None else None
         except Exception:
             return None
     return None
@@ -378,7 +381,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic_per_launch(),
-                         "kernel": "k_grid_query<false> (+ k_kd<64> on the queries it hands over)", "kernel_ms": k_ms,
+                         "kernel": "k_fast_prep + k_grid_fast<false> (+ k_grid_query<false> / k_kd<64> on the queries handed over)", "kernel_ms": k_ms,
                          "kd_tree_fallback_queries": int(fallbacks), "general_grid_kernel_queries": int(handovers),
                          "algorithmic_bytes_per_launch": BYTES_PER_QUERY * N_QUERIES, "peak_source": peak_src},
             "cpu_baseline": cpu,

@@ -49,30 +49,37 @@ with open(os.path.join(out, f"{tag}_launches.csv"), "w") as f:
 
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 R = list(csv.reader(raw.splitlines()))
-Hh, U, V = R[0], R[1], R[2]
+Hh, U = R[0], R[1]
 want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
         "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate.pct", "l1tex__t_bytes.sum",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
         "smsp__inst_executed.sum", "sm__inst_executed.avg.per_cycle_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
         "smsp__thread_inst_executed_per_inst_executed.ratio", "sm__cycles_elapsed.avg", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
         "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed"]
-kname = V[Hh.index("Kernel Name")] if "Kernel Name" in Hh else "kernel"
-short = kname.split("(")[0].split("::")[-1].split("<")[0]
-vals = {}
-with open(os.path.join(out, f"{tag}_{short}_ncu.txt"), "w") as f:
-    f.write(f"# ncu --set full --clock-control none, one launch of {kname}\n")
-    for w in want:
-        if w in Hh:
-            i = Hh.index(w)
-            vals[w] = (V[i], U[i])
-            f.write(f"{w:70s} {V[i]:>18s} {U[i]}\n")
-    for i, hname in enumerate(Hh):
-        if hname.startswith("smsp__average_warps_issue_stalled") and hname.endswith("per_issue_active.ratio"):
-            try:
-                if float(V[i].replace(",", "")) >= 0.15:
-                    f.write(f"{hname:70s} {V[i]:>18s} {U[i]}\n")
-            except ValueError:
-                pass
+captured = {}  # short kernel name -> metric values of its first captured launch
+for V in R[2:]:
+    if len(V) != len(Hh):
+        continue
+    kname = V[Hh.index("Kernel Name")] if "Kernel Name" in Hh else "kernel"
+    short = kname.split("(")[0].split("::")[-1].split("<")[0]
+    if short in captured:
+        continue
+    vals = {}
+    with open(os.path.join(out, f"{tag}_{short}_ncu.txt"), "w") as f:
+        f.write(f"# ncu --set full --clock-control none, one launch of {kname}\n")
+        for w in want:
+            if w in Hh:
+                i = Hh.index(w)
+                vals[w] = (V[i], U[i])
+                f.write(f"{w:70s} {V[i]:>18s} {U[i]}\n")
+        for i, hname in enumerate(Hh):
+            if hname.startswith("smsp__average_warps_issue_stalled") and hname.endswith("per_issue_active.ratio"):
+                try:
+                    if float(V[i].replace(",", "")) >= 0.15:
+                        f.write(f"{hname:70s} {V[i]:>18s} {U[i]}\n")
+                except ValueError:
+                    pass
+    captured[short] = vals
 
 
 def to_bytes(v, u):
@@ -82,9 +89,11 @@ def to_bytes(v, u):
 
 tr = os.path.join(out, "roofline_traffic.json")
 j = json.load(open(tr)) if os.path.exists(tr) else {}
-if "dram__bytes_read.sum" in vals:
-    j[f"{short}_k64_dram_bytes_per_launch"] = int(to_bytes(*vals["dram__bytes_read.sum"]) + to_bytes(*vals["dram__bytes_write.sum"]))
-    j[f"{short}_source"] = f"profiles/{tag}_{short}_ncu.txt"
+for short, vals in captured.items():
+    if "dram__bytes_read.sum" in vals:
+        j[f"{short}_k64_dram_bytes_per_launch"] = int(to_bytes(*vals["dram__bytes_read.sum"]) + to_bytes(*vals["dram__bytes_write.sum"]))
+        j[f"{short}_source"] = f"profiles/{tag}_{short}_ncu.txt"
 json.dump(j, open(tr, "w"), indent=1)
 print(open(os.path.join(out, f"{tag}_step_launches.csv")).read())
-print(open(os.path.join(out, f"{tag}_{short}_ncu.txt")).read())
+for short in captured:
+    print(open(os.path.join(out, f"{tag}_{short}_ncu.txt")).read())
