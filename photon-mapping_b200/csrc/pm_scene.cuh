@@ -52,7 +52,12 @@ __device__ __forceinline__ bool tri_test(const float4 a4, const float4 e14, cons
   return true;
 }
 
-/* closest hit (ANY = false) or occlusion (ANY = true: returns at the first accepted triangle) */
+/* closest hit (ANY = false) or occlusion (ANY = true: returns at the first accepted triangle).
+ * "While-while" traversal: the inner loop descends through inner nodes only; a lane that reaches a leaf waits there
+ * until the other lanes of its warp have one too (leaves are ordinary stack entries, encoded negative), then the
+ * warp runs the triangle tests together. With the two kinds of work interleaved in one loop body a warp of
+ * incoherent photon rays kept ~6 of 32 lanes busy (ncu, Cornell box); the visiting order does not affect the
+ * result (closest t, ties -> lowest id; the slab test keeps boxes at exactly best.t). */
 template <bool ANY>
 __device__ __forceinline__ Hit trace(const SceneView& sc, vec3 org, vec3 dir, float tmin, float tmax) {
   Hit best{-1, tmax, -1};
@@ -60,29 +65,42 @@ __device__ __forceinline__ Hit trace(const SceneView& sc, vec3 org, vec3 dir, fl
   const float ix = __fdiv_rn(1.f, dir.x), iy = __fdiv_rn(1.f, dir.y), iz = __fdiv_rn(1.f, dir.z);
   int stack[kStackDepth];
   int sp = 0;
-  int node = 0;
-  while (true) {
-    const float4 q0 = __ldg(sc.nodes + 4 * (size_t)node + 0);
-    const float4 q1 = __ldg(sc.nodes + 4 * (size_t)node + 1);
-    const float4 q2 = __ldg(sc.nodes + 4 * (size_t)node + 2);
-    const float4 q3 = __ldg(sc.nodes + 4 * (size_t)node + 3);
-    const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
-    /* slabs; fminf/fmaxf drop the NaN of 0 * inf */
-    const float a0x = (q0.x - org.x) * ix, b0x = (q0.y - org.x) * ix;
-    const float a0y = (q0.z - org.y) * iy, b0y = (q0.w - org.y) * iy;
-    const float a0z = (q2.x - org.z) * iz, b0z = (q2.y - org.z) * iz;
-    const float a1x = (q1.x - org.x) * ix, b1x = (q1.y - org.x) * ix;
-    const float a1y = (q1.z - org.y) * iy, b1y = (q1.w - org.y) * iy;
-    const float a1z = (q2.z - org.z) * iz, b1z = (q2.w - org.z) * iz;
-    const float n0 = fmaxf(fmaxf(fminf(a0x, b0x), fminf(a0y, b0y)), fmaxf(fminf(a0z, b0z), tmin));
-    const float f0 = fminf(fminf(fmaxf(a0x, b0x), fmaxf(a0y, b0y)), fminf(fmaxf(a0z, b0z), best.t));
-    const float n1 = fmaxf(fmaxf(fminf(a1x, b1x), fminf(a1y, b1y)), fmaxf(fminf(a1z, b1z), tmin));
-    const float f1 = fminf(fminf(fmaxf(a1x, b1x), fmaxf(a1y, b1y)), fminf(fmaxf(a1z, b1z), best.t));
-    /* conservative: a couple of ulps of slack on the far side */
-    bool h0 = n0 <= f0 * 1.0000004f;
-    bool h1 = (n1 <= f1 * 1.0000004f) && c1 != kNoChild;
-    if (h0 && c0 < 0) {
-      const int slot = ~c0;
+  int node = 0; /* the root is an inner node; kNoChild = traversal finished */
+  while (node != kNoChild) {
+    while (node >= 0 && node != kNoChild) {
+      const float4 q0 = __ldg(sc.nodes + 4 * (size_t)node + 0);
+      const float4 q1 = __ldg(sc.nodes + 4 * (size_t)node + 1);
+      const float4 q2 = __ldg(sc.nodes + 4 * (size_t)node + 2);
+      const float4 q3 = __ldg(sc.nodes + 4 * (size_t)node + 3);
+      const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+      /* slabs; fminf/fmaxf drop the NaN of 0 * inf */
+      const float a0x = (q0.x - org.x) * ix, b0x = (q0.y - org.x) * ix;
+      const float a0y = (q0.z - org.y) * iy, b0y = (q0.w - org.y) * iy;
+      const float a0z = (q2.x - org.z) * iz, b0z = (q2.y - org.z) * iz;
+      const float a1x = (q1.x - org.x) * ix, b1x = (q1.y - org.x) * ix;
+      const float a1y = (q1.z - org.y) * iy, b1y = (q1.w - org.y) * iy;
+      const float a1z = (q2.z - org.z) * iz, b1z = (q2.w - org.z) * iz;
+      const float n0 = fmaxf(fmaxf(fminf(a0x, b0x), fminf(a0y, b0y)), fmaxf(fminf(a0z, b0z), tmin));
+      const float f0 = fminf(fminf(fmaxf(a0x, b0x), fmaxf(a0y, b0y)), fminf(fmaxf(a0z, b0z), best.t));
+      const float n1 = fmaxf(fmaxf(fminf(a1x, b1x), fminf(a1y, b1y)), fmaxf(fminf(a1z, b1z), tmin));
+      const float f1 = fminf(fminf(fmaxf(a1x, b1x), fmaxf(a1y, b1y)), fminf(fmaxf(a1z, b1z), best.t));
+      /* conservative: a couple of ulps of slack on the far side */
+      const bool h0 = n0 <= f0 * 1.0000004f;
+      const bool h1 = (n1 <= f1 * 1.0000004f) && c1 != kNoChild;
+      if (h0 && h1) {
+        const bool first0 = n0 <= n1;
+        if (sp < kStackDepth) stack[sp++] = first0 ? c1 : c0;
+        node = first0 ? c0 : c1;
+      } else if (h0) {
+        node = c0;
+      } else if (h1) {
+        node = c1;
+      } else {
+        node = sp ? stack[--sp] : kNoChild;
+      }
+    }
+    while (node < 0) {
+      const int slot = ~node;
       const float4 a4 = __ldg(sc.tris + 3 * (size_t)slot), e14 = __ldg(sc.tris + 3 * (size_t)slot + 1),
                    e24 = __ldg(sc.tris + 3 * (size_t)slot + 2);
       float t;
@@ -91,31 +109,7 @@ __device__ __forceinline__ Hit trace(const SceneView& sc, vec3 org, vec3 dir, fl
         if (best.prim < 0 || t < best.t || (t == best.t && id < best.prim)) { best.prim = id; best.t = t; best.slot = slot; }
         if (ANY) return best;
       }
-      h0 = false;
-    }
-    if (h1 && c1 < 0) {
-      const int slot = ~c1;
-      const float4 a4 = __ldg(sc.tris + 3 * (size_t)slot), e14 = __ldg(sc.tris + 3 * (size_t)slot + 1),
-                   e24 = __ldg(sc.tris + 3 * (size_t)slot + 2);
-      float t;
-      if (tri_test(a4, e14, e24, org, dir, tmin, tmax, &t)) {
-        const int id = __float_as_int(a4.w);
-        if (best.prim < 0 || t < best.t || (t == best.t && id < best.prim)) { best.prim = id; best.t = t; best.slot = slot; }
-        if (ANY) return best;
-      }
-      h1 = false;
-    }
-    if (h0 && h1) {
-      const bool first0 = n0 <= n1;
-      if (sp < kStackDepth) stack[sp++] = first0 ? c1 : c0;
-      node = first0 ? c0 : c1;
-    } else if (h0) {
-      node = c0;
-    } else if (h1) {
-      node = c1;
-    } else {
-      if (sp == 0) break;
-      node = stack[--sp];
+      node = sp ? stack[--sp] : kNoChild;
     }
   }
   return best;
