@@ -37,6 +37,7 @@ struct EmitParams {
   int64_t first_photon, photon_stride;
   int64_t batch_begin, batch_count; /* global path numbers [batch_begin, batch_begin + batch_count) */
   int slots_per_path;               /* max_depth - 1 */
+  int min_lanes;
 };
 
 enum { EV_MISS = 0, EV_ABSORBED = 1, EV_DIFFUSE = 2, EV_SPECULAR = 4, EV_REFRACT = 8 };
@@ -51,20 +52,66 @@ __device__ __forceinline__ void store40(pm_photon40* dst, vec3 pos, vec3 dir, ve
   reinterpret_cast<float2*>(w)[4] = make_float2(color.y, color.z);
 }
 
+/* fewer traversing lanes than this: leave the traversal loop so that finished lanes can shade and pick up their
+ * next segment (or a new path) instead of idling until the slowest ray of the warp is done */
+constexpr int kMinTraceLanes = 28; /* swept 0..31 on B200: 24-31 within 1 %, 0 (never leave) 8-25 % slower */
+
 __global__ void __launch_bounds__(128)
 k_walk(const EmitParams P, unsigned long long* __restrict__ next_path, pm_photon40* __restrict__ slots,
        int* __restrict__ counts, unsigned long long* __restrict__ segments) {
   const unsigned lane = threadIdx.x & 31u;
-  bool active = false;
-  int64_t local = 0; /* index inside the batch */
+  bool active = false; /* this lane owns a live path; its current segment is traced in `st` */
+  int64_t local = 0;   /* index inside the batch */
   int depth = 0, stored = 0;
   vec3 org = v3(0, 0, 0), dir = v3(0, 0, 1), color = v3(0, 0, 0);
   Rng rng;
   rng.mode = P.rng_mode; rng.lcg.state = 0; rng.cr.key = 0; rng.cr.ctr = 0;
   unsigned long long my_segments = 0;
   bool exhausted = false;
+  TraceState st;
+  st.node = kNoChild; st.sp = 0;
   while (true) {
-    /* refill: lanes without a path claim consecutive ids */
+    /* 1. lanes whose traversal has finished: optixTrace returned -> triangleMeshClosestHit / miss
+     *    (deviceCode.cu:74-136), then shootPhoton / shootCausticsPhoton (deviceCode.cu:25-52) */
+    if (active && st.node == kNoChild) {
+      const Hit h = st.best;
+      int ev = EV_MISS;
+      vec3 s_org = org, s_dir = dir, s_col = color;
+      if (h.prim >= 0) {
+        const pm_material m = P.sc.mats[slot_mesh(P.sc, h.slot)];
+        const float diffuseProb = m.diffuse;
+        const float specularProb = m.specular + diffuseProb;
+        const float transmissionProb = m.transmission + specularProb;
+        const float r = rng.next();
+        if (r < diffuseProb) ev = EV_DIFFUSE;
+        else if (r < specularProb) ev = EV_SPECULAR;
+        else if (r < transmissionProb) ev = EV_REFRACT;
+        else ev = EV_ABSORBED;
+        if (ev != EV_ABSORBED) {
+          s_org = org + h.t * dir;
+          const vec3 n = slot_normal(P.sc, h.slot);
+          if (ev == EV_DIFFUSE) s_dir = cosineSampleHemisphere(n, rng);
+          else if (ev == EV_SPECULAR) s_dir = reflect(dir, n);
+          else s_dir = refract3(dir, n, m.refraction_idx);
+          s_col = v3(m.albedo) * color;
+        }
+      }
+      if (ev == EV_DIFFUSE && depth > 0) {
+        store40(slots + (size_t)local * P.slots_per_path + stored, s_org, s_dir, color);
+        stored++;
+      }
+      const bool cont = P.caustics ? ((ev & (EV_SPECULAR | EV_REFRACT)) != 0) : (ev == EV_DIFFUSE);
+      depth++;
+      if (!cont || depth >= P.max_depth) {
+        counts[local] = stored;
+        active = false;
+      } else {
+        org = s_org; dir = s_dir; color = s_col;
+        my_segments++;
+        trace_begin(P.sc, st, dir, 1e30f);
+      }
+    }
+    /* 2. refill: lanes without a path claim consecutive ids */
     const unsigned need = __ballot_sync(0xffffffffu, !active && !exhausted);
     if (need) {
       unsigned long long base = 0;
@@ -90,49 +137,13 @@ k_walk(const EmitParams P, unsigned long long* __restrict__ next_path, pm_photon
           depth = 0; stored = 0;
           active = P.max_depth > 0;
           if (!active) counts[local] = 0;
+          else { my_segments++; trace_begin(P.sc, st, dir, 1e30f); }
         }
       }
     }
     if (!__any_sync(0xffffffffu, active)) break;
-    if (active) {
-      /* one segment: optixTrace + triangleMeshClosestHit / miss (deviceCode.cu:74-136) */
-      my_segments++;
-      const Hit h = trace<false>(P.sc, org, dir, PMD_EPS, 1e30f);
-      int ev = EV_MISS;
-      vec3 s_org = org, s_dir = dir, s_col = color;
-      if (h.prim >= 0) {
-        const pm_material m = P.sc.mats[slot_mesh(P.sc, h.slot)];
-        const float diffuseProb = m.diffuse;
-        const float specularProb = m.specular + diffuseProb;
-        const float transmissionProb = m.transmission + specularProb;
-        const float r = rng.next();
-        if (r < diffuseProb) ev = EV_DIFFUSE;
-        else if (r < specularProb) ev = EV_SPECULAR;
-        else if (r < transmissionProb) ev = EV_REFRACT;
-        else ev = EV_ABSORBED;
-        if (ev != EV_ABSORBED) {
-          s_org = org + h.t * dir;
-          const vec3 n = slot_normal(P.sc, h.slot);
-          if (ev == EV_DIFFUSE) s_dir = cosineSampleHemisphere(n, rng);
-          else if (ev == EV_SPECULAR) s_dir = reflect(dir, n);
-          else s_dir = refract3(dir, n, m.refraction_idx);
-          s_col = v3(m.albedo) * color;
-        }
-      }
-      /* shootPhoton / shootCausticsPhoton (deviceCode.cu:25-52) */
-      if (ev == EV_DIFFUSE && depth > 0) {
-        store40(slots + (size_t)local * P.slots_per_path + stored, s_org, s_dir, color);
-        stored++;
-      }
-      const bool cont = P.caustics ? ((ev & (EV_SPECULAR | EV_REFRACT)) != 0) : (ev == EV_DIFFUSE);
-      depth++;
-      if (!cont || depth >= P.max_depth) {
-        counts[local] = stored;
-        active = false;
-      } else {
-        org = s_org; dir = s_dir; color = s_col;
-      }
-    }
+    /* 3. traversal of the segments in flight (lanes without one have st.node == kNoChild and pass through) */
+    if (active) trace_advance<false>(P.sc, st, org, dir, PMD_EPS, 1e30f, P.min_lanes);
   }
   /* one atomic per warp */
   for (int o = 16; o > 0; o >>= 1) my_segments += __shfl_xor_sync(0xffffffffu, my_segments, o);
@@ -242,6 +253,7 @@ static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights,
   P.max_depth = max_depth; P.caustics = caustics_mode ? 1 : 0; P.rng_mode = rng_mode; P.seed = seed;
   P.first_photon = first_photon; P.photon_stride = photon_stride;
   P.slots_per_path = max_depth > 1 ? max_depth - 1 : 1;
+  P.min_lanes = getenv("PM_WALK_MIN_LANES") ? atoi(getenv("PM_WALK_MIN_LANES")) : kMinTraceLanes;
   if (n_paths) *n_paths = total_paths;
   if (total_paths == 0) return PM_OK;
   PM_REQUIRE(scene->nt == 0 || scene->mats, "scene has triangles but no materials");

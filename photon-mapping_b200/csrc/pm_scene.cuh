@@ -22,7 +22,6 @@ namespace pmd {
 
 constexpr int kNoChild = 0x7fffffff;
 constexpr int kStackDepth = 64;
-
 struct SceneView {
   const float4* nodes;
   const float4* tris;
@@ -52,20 +51,37 @@ __device__ __forceinline__ bool tri_test(const float4 a4, const float4 e14, cons
   return true;
 }
 
-/* closest hit (ANY = false) or occlusion (ANY = true: returns at the first accepted triangle).
+/* Traversal state of one ray, resumable: k_walk leaves the loop when too few lanes of the warp are still
+ * traversing, lets the finished lanes shade and start their next segment, and comes back. */
+struct TraceState {
+  int node; /* current inner node (>= 0), leaf (~slot, < 0) or kNoChild: finished / idle */
+  int sp;
+  Hit best;
+  float ix, iy, iz;
+  int stack[kStackDepth];
+};
+
+__device__ __forceinline__ void trace_begin(const SceneView& sc, TraceState& st, vec3 dir, float tmax) {
+  st.best = Hit{-1, tmax, -1};
+  st.sp = 0;
+  st.node = sc.nt > 0 ? 0 : kNoChild; /* the root is an inner node */
+  st.ix = __fdiv_rn(1.f, dir.x); st.iy = __fdiv_rn(1.f, dir.y); st.iz = __fdiv_rn(1.f, dir.z);
+}
+
+/* closest hit (ANY = false) or occlusion (ANY = true: stops at the first accepted triangle).
  * "While-while" traversal: the inner loop descends through inner nodes only; a lane that reaches a leaf waits there
  * until the other lanes of its warp have one too (leaves are ordinary stack entries, encoded negative), then the
  * warp runs the triangle tests together. With the two kinds of work interleaved in one loop body a warp of
  * incoherent photon rays kept ~6 of 32 lanes busy (ncu, Cornell box); the visiting order does not affect the
- * result (closest t, ties -> lowest id; the slab test keeps boxes at exactly best.t). */
+ * result (closest t, ties -> lowest id; the slab test keeps boxes at exactly best.t).
+ * Returns when st.node == kNoChild (result in st.best) or, if min_lanes > 0, as soon as fewer than min_lanes
+ * lanes are still inside the loop (call again to continue). */
 template <bool ANY>
-__device__ __forceinline__ Hit trace(const SceneView& sc, vec3 org, vec3 dir, float tmin, float tmax) {
-  Hit best{-1, tmax, -1};
-  if (sc.nt <= 0) return best;
-  const float ix = __fdiv_rn(1.f, dir.x), iy = __fdiv_rn(1.f, dir.y), iz = __fdiv_rn(1.f, dir.z);
-  int stack[kStackDepth];
-  int sp = 0;
-  int node = 0; /* the root is an inner node; kNoChild = traversal finished */
+__device__ __forceinline__ void trace_advance(const SceneView& sc, TraceState& st, vec3 org, vec3 dir, float tmin, float tmax,
+                                              int min_lanes) {
+  int node = st.node, sp = st.sp;
+  Hit best = st.best;
+  const float ix = st.ix, iy = st.iy, iz = st.iz;
   while (node != kNoChild) {
     while (node >= 0 && node != kNoChild) {
       const float4 q0 = __ldg(sc.nodes + 4 * (size_t)node + 0);
@@ -89,14 +105,14 @@ __device__ __forceinline__ Hit trace(const SceneView& sc, vec3 org, vec3 dir, fl
       const bool h1 = (n1 <= f1 * 1.0000004f) && c1 != kNoChild;
       if (h0 && h1) {
         const bool first0 = n0 <= n1;
-        if (sp < kStackDepth) stack[sp++] = first0 ? c1 : c0;
+        if (sp < kStackDepth) st.stack[sp++] = first0 ? c1 : c0;
         node = first0 ? c0 : c1;
       } else if (h0) {
         node = c0;
       } else if (h1) {
         node = c1;
       } else {
-        node = sp ? stack[--sp] : kNoChild;
+        node = sp ? st.stack[--sp] : kNoChild;
       }
     }
     while (node < 0) {
@@ -104,15 +120,24 @@ __device__ __forceinline__ Hit trace(const SceneView& sc, vec3 org, vec3 dir, fl
       const float4 a4 = __ldg(sc.tris + 3 * (size_t)slot), e14 = __ldg(sc.tris + 3 * (size_t)slot + 1),
                    e24 = __ldg(sc.tris + 3 * (size_t)slot + 2);
       float t;
+      node = sp ? st.stack[--sp] : kNoChild;
       if (tri_test(a4, e14, e24, org, dir, tmin, tmax, &t)) {
         const int id = __float_as_int(a4.w);
         if (best.prim < 0 || t < best.t || (t == best.t && id < best.prim)) { best.prim = id; best.t = t; best.slot = slot; }
-        if (ANY) return best;
+        if (ANY) { node = kNoChild; sp = 0; }
       }
-      node = sp ? stack[--sp] : kNoChild;
     }
+    if (min_lanes > 0 && __popc(__activemask()) < min_lanes) break;
   }
-  return best;
+  st.node = node; st.sp = sp; st.best = best;
+}
+
+template <bool ANY>
+__device__ __forceinline__ Hit trace(const SceneView& sc, vec3 org, vec3 dir, float tmin, float tmax) {
+  TraceState st;
+  trace_begin(sc, st, dir, tmax);
+  trace_advance<ANY>(sc, st, org, dir, tmin, tmax, 0);
+  return st.best;
 }
 
 /* getPrimitiveNormal (common/cuda/helpers.h:76-85): normalize(cross(B-A, C-A)), never flipped */
