@@ -22,6 +22,7 @@ namespace pmd {
 
 constexpr int kNoChild = 0x7fffffff;
 constexpr int kStackDepth = 64;
+
 struct SceneView {
   const float4* nodes;
   const float4* tris;
