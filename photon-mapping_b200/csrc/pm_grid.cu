@@ -45,7 +45,11 @@ constexpr int kMaxAttempts = 12;
 constexpr int kTuneK = 64;         /* the cell size is tuned for the largest supported k */
 constexpr int kTuneSamples = 2048;
 constexpr int64_t kMinGridNodes = 4096;
-constexpr int64_t kMaxCells = (int64_t)1 << 24;
+/* cells of the offset table (4 bytes each): at least 2^24, up to 32 per photon, never more than 2^30 (4 GB).
+ * Photons on surfaces occupy a vanishing share of a 3-D grid, so a dense table at the wanted resolution can be out
+ * of reach (C3: 92 M photons on the Cornell walls want 4e10 cells); the cap then coarsens the cells and the
+ * ball-trimmed rows keep the candidate count in check. */
+constexpr int64_t kMinCellCap = (int64_t)1 << 24, kMaxCellCap = (int64_t)1 << 30;
 
 struct GridView {
   const float4* pts;
@@ -1006,6 +1010,7 @@ int grid_build(pm_ctx* ctx, pm_map* m) {
     maxabs = std::max(maxabs, std::max(std::fabs(m->bounds[d]), std::fabs(m->bounds[3 + d])));
   }
   int dim[3];
+  const int64_t cell_cap = std::min(kMaxCellCap, std::max(kMinCellCap, (int64_t)32 * n));
   while (true) {
     const float inv = 1.f / cell;
     int64_t cells = 1;
@@ -1014,7 +1019,7 @@ int grid_build(pm_ctx* ctx, pm_map* m) {
       if (dim[d] < 1) dim[d] = 1;
       cells *= dim[d];
     }
-    if (cells <= kMaxCells && dim[0] < 32768 && dim[1] < 32768 && dim[2] < 32768) break;
+    if (cells <= cell_cap && dim[0] < 32768 && dim[1] < 32768 && dim[2] < 32768) break;
     cell *= 1.26f;
   }
   m->cell = cell; m->inv_cell = 1.f / cell; m->tuned_rk = rk;
