@@ -362,6 +362,10 @@ int knn_pipelined(pm_ctx* ctx, const pm_map* map, const float* q_dev, int64_t nq
 namespace pm {
 
 int kd_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gather, const int* list, const int* list_count) {
+  /* the warp-cooperative kernel answers everything; the per-thread restatement of cukd's traversal stays
+   * selectable (PM_KD_KERNEL=thread) as the literal reference order */
+  static const bool per_thread = getenv("PM_KD_KERNEL") && !strcmp(getenv("PM_KD_KERNEL"), "thread");
+  if (!per_thread) return kdw_query(ctx, map, io, gather, list, list_count);
   return gather ? dispatch_kd<true>(ctx, map, io, list, list_count) : dispatch_kd<false>(ctx, map, io, list, list_count);
 }
 
