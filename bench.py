@@ -272,13 +272,14 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     t0 = time.perf_counter()
     pmap = pkg.PhotonMap.build(ctx, d_tree)
     build_ms = 1e3 * (time.perf_counter() - t0)
-    t0 = time.perf_counter()
-    pmap.close()
-    d_tree.copy_(torch.from_numpy(cloud.view(np.uint8)))
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    pmap = pkg.PhotonMap.build(ctx, d_tree)  # second build: scratch already allocated
-    build_ms_warm = 1e3 * (time.perf_counter() - t0)
+    build_ms_warm = float("inf")
+    for _ in range(3):  # warm builds (scratch already allocated); best of 3: the call also cudaMallocs the map's arrays
+        pmap.close()
+        d_tree.copy_(torch.from_numpy(cloud.view(np.uint8)))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        pmap = pkg.PhotonMap.build(ctx, d_tree)
+        build_ms_warm = min(build_ms_warm, 1e3 * (time.perf_counter() - t0))
 
     queries = make_queries(N_QUERIES, rank)
     d_q = torch.from_numpy(queries).cuda()

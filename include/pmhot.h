@@ -201,7 +201,8 @@ int64_t pm_map_size(const pm_map* map);
  * for each query the k smallest (dist² bits, node id) among nodes with dist² < cutoff².
  * out_ids: nq*k int32, slots not filled are -1; out_dist2 (nq*k, may be NULL) holds the matching
  * squared distances (cutoff² in unfilled slots); out_r2 (nq, may be NULL) is the return value of
- * knn(): the largest dist² if k were found, else cutoff². Slots are sorted ascending.
+ * knn(): the largest dist² if k were found, else cutoff². The order of the slots within a row is unspecified (the
+ * reference returns heap order); unfilled slots come last.
  * k must be one of 8, 16, 32, 50, 64. All pointers host or device. */
 int  pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int k,
             float cutoff_radius, int32_t* out_ids, float* out_dist2, float* out_r2);

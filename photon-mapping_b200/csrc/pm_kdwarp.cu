@@ -193,7 +193,7 @@ __device__ __noinline__ uint64_t select_k(KdwScratch& ws, int cnt, int k, int la
 
 /* one warp per query of list[0 .. *list_count) (or order[t] / t when list == NULL) */
 template <bool GATHER>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 3)
 k_kdw(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n, int first_bucket_node, pmk::QueryIO io,
       const int* __restrict__ list, const int* __restrict__ list_count) {
   __shared__ KdwScratch scratch[kWarpsPerCta];
