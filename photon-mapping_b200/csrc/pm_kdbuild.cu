@@ -139,21 +139,42 @@ __global__ void k_mark(int n, int level_first, const int* __restrict__ seg_of_po
   else { side[e] = 2; seg_next[i] = kDead; }
 }
 
-/* packed (lefts | rights << 32) indicator of the element at position i of one list */
+/* side of the element at position i of each of the three lists, 2 bits per list (0 left, 1 right, 2 pivot, 3 dead
+ * slot): gathered ONCE per level (the split-axis list needs no gather: there the side is positional); the three
+ * scans and the partition read this byte stream instead of chasing side[ord[i]] six times */
+__global__ void k_flags(int n, int level_first, const int* __restrict__ seg_of_pos, const int* __restrict__ seg_pivot,
+                        const uint8_t* __restrict__ seg_dim, const int* __restrict__ ord0, const int* __restrict__ ord1,
+                        const int* __restrict__ ord2, const uint8_t* __restrict__ side, uint8_t* __restrict__ flags) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int s = seg_of_pos[i];
+  if (s == kDead) { flags[i] = 0x3f; return; }
+  const int j = s - level_first;
+  const int pivot = seg_pivot[j];
+  const int dim = seg_dim[j];
+  const uint32_t pos = i < pivot ? 0u : (i > pivot ? 1u : 2u);
+  const uint32_t f0 = dim == 0 ? pos : side[ord0[i]];
+  const uint32_t f1 = dim == 1 ? pos : side[ord1[i]];
+  const uint32_t f2 = dim == 2 ? pos : side[ord2[i]];
+  flags[i] = (uint8_t)(f0 | (f1 << 2) | (f2 << 4));
+}
+
+/* packed (lefts | rights << 32) indicator of position i of list `shift / 2` */
 struct SideFlagOp {
-  const int* ord; const uint8_t* side; const int* seg;
+  const uint8_t* flags; int shift;
   __device__ unsigned long long operator()(int i) const {
-    if (seg[i] == kDead) return 0ull;
-    const uint8_t sd = side[ord[i]];
+    const uint32_t sd = (flags[i] >> shift) & 3u;
     return sd == 0 ? 1ull : (sd == 1 ? (1ull << 32) : 0ull);
   }
 };
 
-/* stable partition of one list inside every subtree range, using the exclusive scan of the flags */
-__global__ void k_partition(int n, int level_first, const int* __restrict__ seg_of_pos,
-                            const int* __restrict__ seg_pivot, const int* __restrict__ begin_cur,
-                            const int* __restrict__ ord_in, const uint8_t* __restrict__ side,
-                            const unsigned long long* __restrict__ scan, int* __restrict__ ord_out) {
+/* stable partition of the three lists inside every subtree range, using the exclusive scans of the flags */
+__global__ void k_partition3(int n, int level_first, const int* __restrict__ seg_of_pos, const int* __restrict__ seg_pivot,
+                             const int* __restrict__ begin_cur, const uint8_t* __restrict__ flags,
+                             const int* __restrict__ in0, const int* __restrict__ in1, const int* __restrict__ in2,
+                             const unsigned long long* __restrict__ sc0, const unsigned long long* __restrict__ sc1,
+                             const unsigned long long* __restrict__ sc2, int* __restrict__ out0, int* __restrict__ out1,
+                             int* __restrict__ out2) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int s = seg_of_pos[i];
@@ -161,14 +182,20 @@ __global__ void k_partition(int n, int level_first, const int* __restrict__ seg_
   const int j = s - level_first;
   const int begin = begin_cur[j];
   const int pivot = seg_pivot[j];
-  const int e = ord_in[i];
-  const uint8_t sd = side[e];
-  const unsigned long long here = scan[i], base = scan[begin];
-  int dst;
-  if (sd == 0) dst = begin + (int)((uint32_t)here - (uint32_t)base);
-  else if (sd == 1) dst = pivot + 1 + (int)((uint32_t)(here >> 32) - (uint32_t)(base >> 32));
-  else dst = pivot;
-  ord_out[dst] = e;
+  const uint32_t f = flags[i];
+  const int* in[3] = {in0, in1, in2};
+  const unsigned long long* sc[3] = {sc0, sc1, sc2};
+  int* out[3] = {out0, out1, out2};
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    const uint32_t sd = (f >> (2 * d)) & 3u;
+    const unsigned long long here = sc[d][i], base = sc[d][begin];
+    int dst;
+    if (sd == 0) dst = begin + (int)((uint32_t)here - (uint32_t)base);
+    else if (sd == 1) dst = pivot + 1 + (int)((uint32_t)(here >> 32) - (uint32_t)(base >> 32));
+    else dst = pivot;
+    out[d][dst] = in[d][i];
+  }
 }
 
 /* ---- the last kLocalLevels levels: one CTA per subtree, everything in shared memory ----------
@@ -413,7 +440,7 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   size_t cub_bytes = 0, scan_bytes = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys_in, keys_out, iota, ord[0][0], n, 0, 32, st);
   {
-    SideFlagOp op{nullptr, nullptr, nullptr};
+    SideFlagOp op{nullptr, 0};
     cub::TransformInputIterator<unsigned long long, SideFlagOp, cub::CountingInputIterator<int>> it(cub::CountingInputIterator<int>(0), op);
     cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, it, (unsigned long long*)nullptr, n, st);
   }
@@ -430,7 +457,7 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   const int num_levels = 32 - __builtin_clz((unsigned)n);  /* floor(log2 n) + 1 */
   const int max_width = (n + 1) / 2 + 1;
   float* box[2]; int* begin[2]; int *seg_pivot, *seg[2], *elem_of_node; uint8_t *seg_dim, *side, *dim_of_node;
-  unsigned long long* scan;
+  unsigned long long* scan; uint8_t* flags;
   PM_B(ctx->get_scratch(pm::S_BUILD6, (size_t)max_width * 6, &box[0]));
   PM_B(ctx->get_scratch(pm::S_BUILD7, (size_t)max_width * 6, &box[1]));
   PM_B(ctx->get_scratch(pm::S_BUILD8, (size_t)max_width, &begin[0]));
@@ -441,7 +468,8 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   PM_B(ctx->get_scratch(pm::S_BUILD12, (size_t)n, &elem_of_node));
   PM_B(ctx->get_scratch(pm::S_BUILD13, (size_t)max_width + 2 * (size_t)n, &seg_dim));
   side = seg_dim + max_width; dim_of_node = side + n;
-  PM_B(ctx->get_scratch(pm::S_BUILD14, (size_t)n, &scan));
+  PM_B(ctx->get_scratch(pm::S_BUILD14, (size_t)n * 3, &scan));
+  PM_B(ctx->get_scratch(pm::S_MISC1, (size_t)n, &flags));
   float* bounds_dev = nullptr;
   PM_B(ctx->get_scratch(pm::S_BUILD15, (size_t)8, &bounds_dev));
 
@@ -470,15 +498,17 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
     k_mark<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, seg_dim, ord[cur][0], ord[cur][1], ord[cur][2],
                                   side, seg[(L + 1) & 1]);
     ctx->launches++;
+    k_flags<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, seg_dim, ord[cur][0], ord[cur][1], ord[cur][2], side, flags);
     for (int d = 0; d < 3; d++) {
-      SideFlagOp op{ord[cur][d], side, seg[L & 1]};
+      SideFlagOp op{flags, 2 * d};
       cub::TransformInputIterator<unsigned long long, SideFlagOp, cub::CountingInputIterator<int>> it(cub::CountingInputIterator<int>(0), op);
       size_t tb = cub_cap;
-      PM_BC(cub::DeviceScan::ExclusiveSum(cub_tmp, tb, it, scan, n, st));
-      k_partition<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, begin[L & 1], ord[cur][d], side, scan,
-                                         ord[cur ^ 1][d]);
-      ctx->launches += 3;
+      PM_BC(cub::DeviceScan::ExclusiveSum(cub_tmp, tb, it, scan + (size_t)d * n, n, st));
     }
+    k_partition3<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, begin[L & 1], flags, ord[cur][0], ord[cur][1],
+                                        ord[cur][2], scan, scan + (size_t)n, scan + 2 * (size_t)n, ord[cur ^ 1][0],
+                                        ord[cur ^ 1][1], ord[cur ^ 1][2]);
+    ctx->launches += 8;
     cur ^= 1;
   }
 
