@@ -34,12 +34,14 @@ constexpr int kBucketLevels = 8;     /* a bucket = the last 8 levels below its r
 constexpr int kBucketNodes = (1 << kBucketLevels) - 1;
 constexpr int kStack = 40;
 
+struct Box6f { float lo[3], hi[3]; };
+
 struct __align__(16) KdwScratch {
   uint64_t keys[kCap];
   uint64_t win[kCap];      /* window members during a selection */
   int hist[32];
   int stack_node[kStack];
-  float stack_d2[kStack];
+  float4 stack_box[kStack]; /* per-axis distance from the query to the subtree's domain box, and its dist² bound */
 };
 
 __device__ __forceinline__ uint64_t warp_max_u64(uint64_t v) {
@@ -194,8 +196,8 @@ __device__ __noinline__ uint64_t select_k(KdwScratch& ws, int cnt, int k, int la
 /* one warp per query of list[0 .. *list_count) (or order[t] / t when list == NULL) */
 template <bool GATHER>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 3)
-k_kdw(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n, int first_bucket_node, pmk::QueryIO io,
-      const int* __restrict__ list, const int* __restrict__ list_count) {
+k_kdw(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n, int first_bucket_node, const Box6f box,
+      pmk::QueryIO io, const int* __restrict__ list, const int* __restrict__ list_count) {
   __shared__ KdwScratch scratch[kWarpsPerCta];
   KdwScratch& ws = scratch[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
@@ -215,6 +217,12 @@ k_kdw(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n
     const float qx = io.q[(size_t)qi * 3 + 0], qy = io.q[(size_t)qi * 3 + 1], qz = io.q[(size_t)qi * 3 + 2];
     uint64_t bound = encode(io.cutoff2, 0); /* candidates must have key < bound */
     int cnt = 0, sp = 0, curr = 0;
+    /* per-axis distance from the query to the domain box of `curr` (root: the map's bounds). Culling by the box
+     * distance instead of the reference's single plane distance is what keeps far-away queries (a caustic map seen
+     * from the other side of the room) from visiting most of the tree; the factor below absorbs the different
+     * rounding of this sum of squares and pmk::dist2, so the bound stays conservative */
+    float ox = fmaxf(fmaxf(box.lo[0] - qx, qx - box.hi[0]), 0.f), oy = fmaxf(fmaxf(box.lo[1] - qy, qy - box.hi[1]), 0.f),
+          oz = fmaxf(fmaxf(box.lo[2] - qz, qz - box.hi[2]), 0.f);
     while (true) {
       while (curr < n) {
         if (curr >= first_bucket_node) {
@@ -257,10 +265,12 @@ k_kdw(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n
         const float dp = dim == 0 ? qx - nd.x : (dim == 1 ? qy - nd.y : qz - nd.z);
         const int l = 2 * curr + 1;
         const int far_child = dp < 0.f ? l + 1 : l;
-        const float pd2 = __fmul_rn(dp, dp);
-        /* a far subtree can only hold keys >= encode(pd2, 0) */
-        if (far_child < n && encode(pd2, 0) < bound && sp < kStack) {
-          if (lane == 0) { ws.stack_node[sp] = far_child; ws.stack_d2[sp] = pd2; }
+        const float ad = fabsf(dp);
+        const float fx = dim == 0 ? fmaxf(ox, ad) : ox, fy = dim == 1 ? fmaxf(oy, ad) : oy, fz = dim == 2 ? fmaxf(oz, ad) : oz;
+        const float fd2 = (fx * fx + fy * fy + fz * fz) * 0.999999f;
+        /* the far subtree can only hold keys >= encode(fd2, 0) */
+        if (far_child < n && encode(fd2, 0) < bound && sp < kStack) {
+          if (lane == 0) { ws.stack_node[sp] = far_child; ws.stack_box[sp] = make_float4(fx, fy, fz, fd2); }
           sp++;
         }
         curr = dp < 0.f ? l : l + 1;
@@ -269,7 +279,8 @@ k_kdw(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n
       bool found = false;
       while (sp > 0) {
         --sp;
-        if (encode(ws.stack_d2[sp], 0) < bound) { curr = ws.stack_node[sp]; found = true; break; }
+        const float4 b4 = ws.stack_box[sp];
+        if (encode(b4.w, 0) < bound) { curr = ws.stack_node[sp]; ox = b4.x; oy = b4.y; oz = b4.z; found = true; break; }
       }
       __syncwarp();
       if (!found) break;
@@ -342,8 +353,10 @@ int kdw_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gathe
   const int64_t cap = (int64_t)ctx->sm_count * (list ? 16 : 64);
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
-  if (gather) k_kdw<true><<<(unsigned)grid, kWarpsPerCta * 32, 0, ctx->stream>>>(map->nodes4, map->color4, n, first_bucket_node, io, list, list_count);
-  else k_kdw<false><<<(unsigned)grid, kWarpsPerCta * 32, 0, ctx->stream>>>(map->nodes4, map->color4, n, first_bucket_node, io, list, list_count);
+  Box6f box;
+  for (int d = 0; d < 3; d++) { box.lo[d] = map->bounds[d]; box.hi[d] = map->bounds[3 + d]; }
+  if (gather) k_kdw<true><<<(unsigned)grid, kWarpsPerCta * 32, 0, ctx->stream>>>(map->nodes4, map->color4, n, first_bucket_node, box, io, list, list_count);
+  else k_kdw<false><<<(unsigned)grid, kWarpsPerCta * 32, 0, ctx->stream>>>(map->nodes4, map->color4, n, first_bucket_node, box, io, list, list_count);
   ctx->launches++;
   PM_CUDA(cudaGetLastError());
   return PM_OK;

@@ -287,7 +287,8 @@ int run_queries(pm_ctx* ctx, const pm_map* map, pmk::QueryIO io, bool gather, bo
   ctx->fb_count_dev = nullptr;
   ctx->ho_count_dev = nullptr;
   if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
-  if (map->grid_pts) {
+  static const bool kd_only = getenv("PM_KD_ONLY") != nullptr; /* measurement knob: every query through the kd-tree kernel */
+  if (map->grid_pts && !kd_only) {
     int *fb_list = nullptr, *fb_count = nullptr;
     PM_CHECK(ctx->get_scratch(pm::S_MISC1, (size_t)io.nq, &fb_list));
     PM_CHECK(ctx->get_scratch(pm::S_MISC2, (size_t)4, &fb_count));
