@@ -30,7 +30,7 @@ using pmk::encode;
 constexpr int kWarpsPerCta = 8;
 constexpr int kCap = 256;            /* candidate buffer per warp */
 constexpr int kSlotsW = kCap / 32;   /* keys per lane during a selection */
-constexpr int kBucketLevels = 8;     /* a bucket = the last 8 levels below its root: <= 255 nodes */
+constexpr int kBucketLevels = 7;     /* a bucket = the last 8 levels below its root: <= 255 nodes */
 constexpr int kBucketNodes = (1 << kBucketLevels) - 1;
 constexpr int kStack = 40;
 
