@@ -83,7 +83,8 @@ __global__ void k_split(int level_first, int level_count, int n, const int* __re
                         const float* __restrict__ c1, const float* __restrict__ c2,
                         const float* __restrict__ box_cur, const int* __restrict__ begin_cur,
                         float* __restrict__ box_next, int* __restrict__ begin_next, int* __restrict__ seg_pivot,
-                        uint8_t* __restrict__ seg_dim, int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
+                        uint8_t* __restrict__ seg_dim, uint2* __restrict__ seg_pkey, int* __restrict__ elem_of_node,
+                        uint8_t* __restrict__ dim_of_node) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= level_count) return;
   const int s = level_first + j;
@@ -103,6 +104,7 @@ __global__ void k_split(int level_first, int level_count, int n, const int* __re
   dim_of_node[s] = (uint8_t)dim;
   seg_pivot[j] = pivot;
   seg_dim[j] = (uint8_t)dim;
+  seg_pkey[j] = make_uint2(ordered_key(split), (uint32_t)e); /* the list order is (ordered key, input index) */
   /* children (index in the next level's arrays = 2j, 2j+1) */
   const int next_first = 2 * level_first + 1;
   if (lchild < n) {
@@ -121,42 +123,40 @@ __global__ void k_split(int level_first, int level_count, int n, const int* __re
   }
 }
 
-/* one thread per in-order position: classify the element found there in the split-axis list */
-__global__ void k_mark(int n, int level_first, const int* __restrict__ seg_of_pos, const int* __restrict__ seg_pivot,
-                       const uint8_t* __restrict__ seg_dim, const int* __restrict__ ord0, const int* __restrict__ ord1,
-                       const int* __restrict__ ord2, uint8_t* __restrict__ side, int* __restrict__ seg_next) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int s = seg_of_pos[i];
-  if (s == kDead) { seg_next[i] = kDead; return; }
-  const int j = s - level_first;
-  const int pivot = seg_pivot[j];
-  const int dim = seg_dim[j];
-  const int* ord = dim == 0 ? ord0 : (dim == 1 ? ord1 : ord2);
-  const int e = ord[i];
-  if (i < pivot) { side[e] = 0; seg_next[i] = 2 * s + 1; }
-  else if (i > pivot) { side[e] = 1; seg_next[i] = 2 * s + 2; }
-  else { side[e] = 2; seg_next[i] = kDead; }
-}
-
-/* side of the element at position i of each of the three lists, 2 bits per list (0 left, 1 right, 2 pivot, 3 dead
- * slot): gathered ONCE per level (the split-axis list needs no gather: there the side is positional); the three
- * scans and the partition read this byte stream instead of chasing side[ord[i]] six times */
+/* Side of the element at position i of each of the three lists, 2 bits per list (0 left, 1 right, 2 pivot, 3 dead
+ * slot), and the subtree every position belongs to on the next level. In the split-axis list the side is
+ * positional; in the other two the element is compared with the pivot by (ordered coordinate key, input index) —
+ * the order the lists were sorted in — which costs one 4-byte gather per list and no scatter. The three scans and
+ * the partition read this byte stream. */
 __global__ void k_flags(int n, int level_first, const int* __restrict__ seg_of_pos, const int* __restrict__ seg_pivot,
-                        const uint8_t* __restrict__ seg_dim, const int* __restrict__ ord0, const int* __restrict__ ord1,
-                        const int* __restrict__ ord2, const uint8_t* __restrict__ side, uint8_t* __restrict__ flags) {
+                        const uint8_t* __restrict__ seg_dim, const uint2* __restrict__ seg_pkey, const int* __restrict__ ord0,
+                        const int* __restrict__ ord1, const int* __restrict__ ord2, const float* __restrict__ c0,
+                        const float* __restrict__ c1, const float* __restrict__ c2, uint8_t* __restrict__ flags,
+                        int* __restrict__ seg_next) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int s = seg_of_pos[i];
-  if (s == kDead) { flags[i] = 0x3f; return; }
+  if (s == kDead) { flags[i] = 0x3f; seg_next[i] = kDead; return; }
   const int j = s - level_first;
   const int pivot = seg_pivot[j];
   const int dim = seg_dim[j];
+  const uint2 pk = seg_pkey[j];
   const uint32_t pos = i < pivot ? 0u : (i > pivot ? 1u : 2u);
-  const uint32_t f0 = dim == 0 ? pos : side[ord0[i]];
-  const uint32_t f1 = dim == 1 ? pos : side[ord1[i]];
-  const uint32_t f2 = dim == 2 ? pos : side[ord2[i]];
-  flags[i] = (uint8_t)(f0 | (f1 << 2) | (f2 << 4));
+  seg_next[i] = pos == 0u ? 2 * s + 1 : (pos == 1u ? 2 * s + 2 : kDead);
+  const float* c = dim == 0 ? c0 : (dim == 1 ? c1 : c2);
+  const int* ord[3] = {ord0, ord1, ord2};
+  uint32_t f = 0;
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    uint32_t fd = pos;
+    if (d != dim) {
+      const uint32_t e = (uint32_t)ord[d][i];
+      const uint32_t k = ordered_key(c[e]);
+      fd = e == pk.y ? 2u : ((k < pk.x || (k == pk.x && e < pk.y)) ? 0u : 1u);
+    }
+    f |= fd << (2 * d);
+  }
+  flags[i] = (uint8_t)f;
 }
 
 /* packed (lefts | rights << 32) indicator of position i of list `shift / 2` */
@@ -456,7 +456,7 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   /* per-level state */
   const int num_levels = 32 - __builtin_clz((unsigned)n);  /* floor(log2 n) + 1 */
   const int max_width = (n + 1) / 2 + 1;
-  float* box[2]; int* begin[2]; int *seg_pivot, *seg[2], *elem_of_node; uint8_t *seg_dim, *side, *dim_of_node;
+  float* box[2]; int* begin[2]; int *seg_pivot, *seg[2], *elem_of_node; uint8_t *seg_dim, *dim_of_node; uint2* seg_pkey;
   unsigned long long* scan; uint8_t* flags;
   PM_B(ctx->get_scratch(pm::S_BUILD6, (size_t)max_width * 6, &box[0]));
   PM_B(ctx->get_scratch(pm::S_BUILD7, (size_t)max_width * 6, &box[1]));
@@ -466,8 +466,9 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   PM_B(ctx->get_scratch(pm::S_BUILD11, (size_t)n * 2, &seg[0]));
   seg[1] = seg[0] + n;
   PM_B(ctx->get_scratch(pm::S_BUILD12, (size_t)n, &elem_of_node));
-  PM_B(ctx->get_scratch(pm::S_BUILD13, (size_t)max_width + 2 * (size_t)n, &seg_dim));
-  side = seg_dim + max_width; dim_of_node = side + n;
+  PM_B(ctx->get_scratch(pm::S_BUILD13, (size_t)max_width + (size_t)n, &seg_dim));
+  dim_of_node = seg_dim + max_width;
+  PM_B(ctx->get_scratch(pm::S_BUILD16, (size_t)max_width, &seg_pkey));
   PM_B(ctx->get_scratch(pm::S_BUILD14, (size_t)n * 3, &scan));
   PM_B(ctx->get_scratch(pm::S_MISC1, (size_t)n, &flags));
   float* bounds_dev = nullptr;
@@ -492,13 +493,11 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
     }
     k_split<<<(unsigned)pm::div_up(level_count, 128), 128, 0, st>>>(
         level_first, level_count, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
-        box[(L + 1) & 1], begin[(L + 1) & 1], seg_pivot, seg_dim, elem_of_node, dim_of_node);
+        box[(L + 1) & 1], begin[(L + 1) & 1], seg_pivot, seg_dim, seg_pkey, elem_of_node, dim_of_node);
     ctx->launches++;
     if (L == num_levels - 1) break;
-    k_mark<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, seg_dim, ord[cur][0], ord[cur][1], ord[cur][2],
-                                  side, seg[(L + 1) & 1]);
-    ctx->launches++;
-    k_flags<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, seg_dim, ord[cur][0], ord[cur][1], ord[cur][2], side, flags);
+    k_flags<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, seg_dim, seg_pkey, ord[cur][0], ord[cur][1], ord[cur][2],
+                                   cx, cy, cz, flags, seg[(L + 1) & 1]);
     for (int d = 0; d < 3; d++) {
       SideFlagOp op{flags, 2 * d};
       cub::TransformInputIterator<unsigned long long, SideFlagOp, cub::CountingInputIterator<int>> it(cub::CountingInputIterator<int>(0), op);
@@ -508,7 +507,7 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
     k_partition3<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, begin[L & 1], flags, ord[cur][0], ord[cur][1],
                                         ord[cur][2], scan, scan + (size_t)n, scan + 2 * (size_t)n, ord[cur ^ 1][0],
                                         ord[cur ^ 1][1], ord[cur ^ 1][2]);
-    ctx->launches += 8;
+    ctx->launches += 7;
     cur ^= 1;
   }
 
