@@ -213,11 +213,12 @@ constexpr uint16_t kDead16 = 0xffffu;
 struct LocalSmem {
   float c[3][kLocalCap + 1];
   int gid[kLocalCap + 1];
-  uint32_t scanv[kLocalCap + 1];
+  uint64_t scanv[kLocalCap + 1];
   uint16_t lst[2][3][kLocalCap + 1];
-  uint16_t segid[2][kLocalCap + 1];
-  uint8_t side[kLocalCap + 1];
-  float box[2][kLocalSegs][6];
+  uint16_t segid[kLocalCap + 1];
+  float box_even[kLocalSegs / 2][6]; /* boxes of even local levels (<= 256 nodes at level 8) */
+  float box_odd[kLocalSegs / 4][6];  /* odd local levels (<= 128 at level 7); level 9 keeps only its split axis */
+  uint8_t last_dim[kLocalSegs];
   uint16_t seg_begin[2][kLocalSegs];
   uint16_t seg_pivot[kLocalSegs];
   uint8_t seg_dim[kLocalSegs];
@@ -230,7 +231,7 @@ k_finish_subtrees(int level_first, int level_count, int n, const int* __restrict
                   int* __restrict__ local_of, int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   LocalSmem& sm = *reinterpret_cast<LocalSmem*>(smem_raw);
-  using Scan = cub::BlockScan<uint32_t, kLocalThreads>;
+  using Scan = cub::BlockScan<uint64_t, kLocalThreads>;
   __shared__ typename Scan::TempStorage scan_tmp;
   const int j = blockIdx.x;
   if (j >= level_count) return;
@@ -244,10 +245,10 @@ k_finish_subtrees(int level_first, int level_count, int n, const int* __restrict
     sm.gid[i] = e;
     sm.c[0][i] = cx[e]; sm.c[1][i] = cy[e]; sm.c[2][i] = cz[e];
     sm.lst[0][0][i] = (uint16_t)i;
-    sm.segid[0][i] = 0;
+    sm.segid[i] = 0;
     local_of[e] = i;
   }
-  if (tid < 6) sm.box[0][0][tid] = box_cur[(size_t)j * 6 + tid];
+  if (tid < 6) sm.box_even[0][tid] = box_cur[(size_t)j * 6 + tid];
   if (tid == 0) sm.seg_begin[0][0] = 0;
   __threadfence_block();
   __syncthreads();
@@ -266,10 +267,16 @@ k_finish_subtrees(int level_first, int level_count, int n, const int* __restrict
     /* split: one thread per node of the level */
     for (int q = tid; q < nseg; q += kLocalThreads) {
       const int s = (int)first + q;
+      const bool last = t + 1 == kLocalLevels;
       float box[6];
+      int dim;
+      if (last) dim = sm.last_dim[q];
+      else {
+        const float* src = tb ? sm.box_odd[q] : sm.box_even[q];
 #pragma unroll
-      for (int d = 0; d < 6; d++) box[d] = sm.box[tb][q][d];
-      const int dim = widest_dim(box);
+        for (int d = 0; d < 6; d++) box[d] = src[d];
+        dim = widest_dim(box);
+      }
       const int begin = sm.seg_begin[tb][q];
       const int64_t lchild = 2 * (int64_t)s + 1;
       const int left = lchild < n ? (int)subtree_size(lchild, n) : 0;
@@ -280,70 +287,85 @@ k_finish_subtrees(int level_first, int level_count, int n, const int* __restrict
       dim_of_node[s] = (uint8_t)dim;
       sm.seg_pivot[q] = (uint16_t)pivot;
       sm.seg_dim[q] = (uint8_t)dim;
-      if (t + 1 < kLocalLevels) {
-        if (lchild < n) {
+      if (!last) {
 #pragma unroll
-          for (int d = 0; d < 6; d++) sm.box[tb ^ 1][2 * q][d] = box[d];
-          sm.box[tb ^ 1][2 * q][3 + dim] = fminf(split, box[3 + dim]);
-          sm.seg_begin[tb ^ 1][2 * q] = (uint16_t)begin;
-        }
-        if (lchild + 1 < n) {
+        for (int c = 0; c < 2; c++) {
+          if (lchild + c >= n) continue;
+          float cb[6];
 #pragma unroll
-          for (int d = 0; d < 6; d++) sm.box[tb ^ 1][2 * q + 1][d] = box[d];
-          sm.box[tb ^ 1][2 * q + 1][dim] = fmaxf(split, box[dim]);
-          sm.seg_begin[tb ^ 1][2 * q + 1] = (uint16_t)(pivot + 1);
+          for (int d = 0; d < 6; d++) cb[d] = box[d];
+          if (c == 0) cb[3 + dim] = fminf(split, box[3 + dim]);
+          else cb[dim] = fmaxf(split, box[dim]);
+          if (t + 2 == kLocalLevels) sm.last_dim[2 * q + c] = (uint8_t)widest_dim(cb);
+          else {
+            float* dst = tb ? sm.box_even[2 * q + c] : sm.box_odd[2 * q + c];
+#pragma unroll
+            for (int d = 0; d < 6; d++) dst[d] = cb[d];
+          }
+          sm.seg_begin[tb ^ 1][2 * q + c] = (uint16_t)(c == 0 ? begin : pivot + 1);
         }
       }
     }
     __syncthreads();
     if (2 * first + 1 >= n || t + 1 >= kLocalLevels) break; /* no level below */
-    /* mark: the element found at position i of its segment's split-axis list goes left / right / is the pivot */
-    for (int i = tid; i < m; i += kLocalThreads) {
-      const uint16_t sg = sm.segid[tb][i];
-      if (sg == kDead16) { sm.segid[tb ^ 1][i] = kDead16; continue; }
-      const int piv = sm.seg_pivot[sg];
-      const int el = sm.lst[cur][sm.seg_dim[sg]][i];
-      sm.side[el] = i < piv ? 0 : (i > piv ? 1 : 2);
-      sm.segid[tb ^ 1][i] = i < piv ? (uint16_t)(2 * sg) : (i > piv ? (uint16_t)(2 * sg + 1) : kDead16);
+    /* stable partition of the three lists inside every segment, one packed scan for all of them: list d keeps
+     * its left count in bits [20d, 20d+10) and its right count in bits [20d+10, 20d+20) (totals <= 1023).
+     * Position i of the split-axis list goes by position; in the other two lists an element goes by the list
+     * order (ordered key, input index) against the pivot, which is the same decision */
+    uint64_t f[kLocalItems], ex[kLocalItems];
+    uint32_t sides[kLocalItems]; /* 2 bits per list, and the segment id above them */
+#pragma unroll
+    for (int it = 0; it < kLocalItems; it++) {
+      const int i = tid * kLocalItems + it;
+      f[it] = 0ull; sides[it] = 0x3fu;
+      if (i >= m) continue;
+      const uint16_t sg = sm.segid[i]; /* position i is only ever touched by this thread */
+      if (sg == kDead16) continue;
+      const int piv = sm.seg_pivot[sg], dim = sm.seg_dim[sg];
+      const int pe = sm.lst[cur][dim][piv];
+      const uint32_t pk = ordered_key(sm.c[dim][pe]);
+      const int pg = sm.gid[pe];
+      sm.segid[i] = i < piv ? (uint16_t)(2 * sg) : (i > piv ? (uint16_t)(2 * sg + 1) : kDead16);
+      uint32_t pack = (uint32_t)sg << 8;
+#pragma unroll
+      for (int d = 0; d < 3; d++) {
+        uint32_t sd;
+        if (d == dim) sd = i < piv ? 0u : (i > piv ? 1u : 2u);
+        else {
+          const int el = sm.lst[cur][d][i];
+          const uint32_t k = ordered_key(sm.c[dim][el]);
+          sd = el == pe ? 2u : ((k < pk || (k == pk && sm.gid[el] < pg)) ? 0u : 1u);
+        }
+        pack |= sd << (2 * d);
+        if (sd < 2u) f[it] += 1ull << (20 * d + 10 * (int)sd);
+      }
+      sides[it] = pack;
+    }
+    Scan(scan_tmp).ExclusiveSum(f, ex);
+#pragma unroll
+    for (int it = 0; it < kLocalItems; it++) {
+      const int i = tid * kLocalItems + it;
+      if (i < m) sm.scanv[i] = ex[it];
     }
     __syncthreads();
-    /* stable partition of the three lists inside every segment */
-    for (int d = 0; d < 3; d++) {
-      uint32_t f[kLocalItems], ex[kLocalItems];
 #pragma unroll
-      for (int it = 0; it < kLocalItems; it++) {
-        const int i = tid * kLocalItems + it;
-        f[it] = 0u;
-        if (i < m && sm.segid[tb][i] != kDead16) {
-          const uint8_t sd = sm.side[sm.lst[cur][d][i]];
-          f[it] = sd == 0 ? 1u : (sd == 1 ? 1u << 16 : 0u);
-        }
-      }
-      Scan(scan_tmp).ExclusiveSum(f, ex);
+    for (int it = 0; it < kLocalItems; it++) {
+      const int i = tid * kLocalItems + it;
+      if (sides[it] == 0x3fu) continue;
+      const uint32_t sg = sides[it] >> 8;
+      const int begin = sm.seg_begin[tb][sg], pivot = sm.seg_pivot[sg];
+      const uint64_t rel = ex[it] - sm.scanv[begin]; /* field-wise: every field of ex >= that of the base */
 #pragma unroll
-      for (int it = 0; it < kLocalItems; it++) {
-        const int i = tid * kLocalItems + it;
-        if (i < m) sm.scanv[i] = ex[it];
-      }
-      __syncthreads();
-#pragma unroll
-      for (int it = 0; it < kLocalItems; it++) {
-        const int i = tid * kLocalItems + it;
-        if (i >= m) continue;
-        const uint16_t sg = sm.segid[tb][i];
-        if (sg == kDead16) continue;
-        const int begin = sm.seg_begin[tb][sg], pivot = sm.seg_pivot[sg];
-        const uint16_t el = sm.lst[cur][d][i];
-        const uint8_t sd = sm.side[el];
-        const uint32_t here = ex[it], base = sm.scanv[begin];
+      for (int d = 0; d < 3; d++) {
+        const uint32_t sd = (sides[it] >> (2 * d)) & 3u;
         int dst;
-        if (sd == 0) dst = begin + (int)((here & 0xffffu) - (base & 0xffffu));
-        else if (sd == 1) dst = pivot + 1 + (int)((here >> 16) - (base >> 16));
+        if (sd == 0) dst = begin + (int)((rel >> (20 * d)) & 0x3ffu);
+        else if (sd == 1) dst = pivot + 1 + (int)((rel >> (20 * d + 10)) & 0x3ffu);
         else dst = pivot;
-        sm.lst[cur ^ 1][d][dst] = el;
+        sm.lst[cur ^ 1][d][dst] = sm.lst[cur][d][i];
       }
-      __syncthreads();
     }
+    __syncthreads();
     cur ^= 1;
   }
 }
