@@ -18,6 +18,8 @@
  * range is [begin, begin+size) and its pivot sits at begin + |left subtree|; the slot a pivot
  * leaves behind simply stays dead.
  */
+#include <cstdlib>
+#include <cstring>
 #include <cub/cub.cuh>
 #include "pm_internal.h"
 
@@ -77,14 +79,20 @@ __device__ inline int widest_dim(const float* b) {
   return best;
 }
 
+/* what k_level needs to know about one subtree range of the current level */
+struct SegRec {
+  int pivot_dim; /* pivot position | split axis << 30 */
+  int begin;
+  uint32_t pkey, pelem; /* the pivot in the order the lists were sorted in: (ordered key, input index) */
+};
+
 /* one thread per subtree of the current level: choose dim + pivot, emit the node, derive children */
 __global__ void k_split(int level_first, int level_count, int n, const int* __restrict__ ord0,
                         const int* __restrict__ ord1, const int* __restrict__ ord2, const float* __restrict__ c0,
                         const float* __restrict__ c1, const float* __restrict__ c2,
                         const float* __restrict__ box_cur, const int* __restrict__ begin_cur,
-                        float* __restrict__ box_next, int* __restrict__ begin_next, int* __restrict__ seg_pivot,
-                        uint8_t* __restrict__ seg_dim, uint2* __restrict__ seg_pkey, int* __restrict__ elem_of_node,
-                        uint8_t* __restrict__ dim_of_node) {
+                        float* __restrict__ box_next, int* __restrict__ begin_next, SegRec* __restrict__ seg_rec,
+                        int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= level_count) return;
   const int s = level_first + j;
@@ -102,9 +110,7 @@ __global__ void k_split(int level_first, int level_count, int n, const int* __re
   const float split = c[e];
   elem_of_node[s] = e;
   dim_of_node[s] = (uint8_t)dim;
-  seg_pivot[j] = pivot;
-  seg_dim[j] = (uint8_t)dim;
-  seg_pkey[j] = make_uint2(ordered_key(split), (uint32_t)e); /* the list order is (ordered key, input index) */
+  seg_rec[j] = SegRec{pivot | (dim << 30), begin, ordered_key(split), (uint32_t)e};
   /* children (index in the next level's arrays = 2j, 2j+1) */
   const int next_first = 2 * level_first + 1;
   if (lchild < n) {
@@ -123,79 +129,146 @@ __global__ void k_split(int level_first, int level_count, int n, const int* __re
   }
 }
 
-/* Side of the element at position i of each of the three lists, 2 bits per list (0 left, 1 right, 2 pivot, 3 dead
- * slot), and the subtree every position belongs to on the next level. In the split-axis list the side is
- * positional; in the other two the element is compared with the pivot by (ordered coordinate key, input index) —
- * the order the lists were sorted in — which costs one 4-byte gather per list and no scatter. The three scans and
- * the partition read this byte stream. */
-__global__ void k_flags(int n, int level_first, const int* __restrict__ seg_of_pos, const int* __restrict__ seg_pivot,
-                        const uint8_t* __restrict__ seg_dim, const uint2* __restrict__ seg_pkey, const int* __restrict__ ord0,
-                        const int* __restrict__ ord1, const int* __restrict__ ord2, const float* __restrict__ c0,
-                        const float* __restrict__ c1, const float* __restrict__ c2, uint8_t* __restrict__ flags,
-                        int* __restrict__ seg_next) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int s = seg_of_pos[i];
-  if (s == kDead) { flags[i] = 0x3f; seg_next[i] = kDead; return; }
-  const int j = s - level_first;
-  const int pivot = seg_pivot[j];
-  const int dim = seg_dim[j];
-  const uint2 pk = seg_pkey[j];
-  const uint32_t pos = i < pivot ? 0u : (i > pivot ? 1u : 2u);
-  seg_next[i] = pos == 0u ? 2 * s + 1 : (pos == 1u ? 2 * s + 2 : kDead);
-  const float* c = dim == 0 ? c0 : (dim == 1 ? c1 : c2);
-  const int* ord[3] = {ord0, ord1, ord2};
-  uint32_t f = 0;
-#pragma unroll
-  for (int d = 0; d < 3; d++) {
-    uint32_t fd = pos;
-    if (d != dim) {
-      const uint32_t e = (uint32_t)ord[d][i];
-      const uint32_t k = ordered_key(c[e]);
-      fd = e == pk.y ? 2u : ((k < pk.x || (k == pk.x && e < pk.y)) ? 0u : 1u);
-    }
-    f |= fd << (2 * d);
-  }
-  flags[i] = (uint8_t)f;
+/* ---- one level in one pass --------------------------------------------------------------------
+ * k_level moves every element of the three lists to its place on the next level: a stable partition of each
+ * subtree range around its pivot. In the split-axis list the side of an element is its position; in the other
+ * two it is compared with the pivot by (ordered coordinate key, input index), the order the lists were sorted
+ * in — one 4-byte gather per list. A tile of kTile positions computes the sides, scans them in shared memory
+ * and resolves what its first (spilled-over) subtree range
+ * accumulated in earlier tiles with a decoupled look-back over one 64-bit status word per tile. The scan is
+ * segmented (it restarts at every range begin and at every dead slot), so a tile that holds a range begin
+ * publishes a resolved value without waiting for anybody, and the look-back never walks past the previous
+ * range begin. Only the two lists that are not sorted along the split axis move (slot 0 = axis dim+1, slot 1 =
+ * axis dim+2); per slot the word carries the lefts seen so far in the range (30 bits) and whether the pivot
+ * was seen (1 bit): rights = (i - begin) - lefts - pivot_seen. Tiles take their number from a ticket counter,
+ * so a tile only ever waits for tiles that are already running. */
+constexpr int kTile = 512;
+constexpr uint64_t kStInvalid = 0ull, kStAgg = 1ull << 62, kStPrefix = 2ull << 62, kStMask = 3ull << 62;
+
+__device__ inline uint64_t tile_to_global(uint64_t x) { /* 4 x 11-bit tile-local fields -> L0 | P0<<30 | L1<<31 | P1<<61 */
+  return (x & 0x7ffull) | (((x >> 11) & 0x7ffull) << 30) | (((x >> 22) & 0x7ffull) << 31) | (((x >> 33) & 0x7ffull) << 61);
 }
 
-/* packed (lefts | rights << 32) indicator of position i of list `shift / 2` */
-struct SideFlagOp {
-  const uint8_t* flags; int shift;
-  __device__ unsigned long long operator()(int i) const {
-    const uint32_t sd = (flags[i] >> shift) & 3u;
-    return sd == 0 ? 1ull : (sd == 1 ? (1ull << 32) : 0ull);
-  }
-};
+__global__ void __launch_bounds__(kTile, 4)
+k_level(int n, int level_first, const int* __restrict__ seg_of_pos, const SegRec* __restrict__ seg_rec,
+        const int* __restrict__ in0, const int* __restrict__ in1, const int* __restrict__ in2,
+        const float* __restrict__ c0, const float* __restrict__ c1, const float* __restrict__ c2,
+        int* __restrict__ out0, int* __restrict__ out1, int* __restrict__ out2, int* __restrict__ seg_next,
+        unsigned long long* __restrict__ status, unsigned int* __restrict__ ticket) {
+  __shared__ uint64_t scanv[kTile];
+  __shared__ uint64_t warp_tot[kTile / 32];
+  __shared__ uint64_t carry_sh;
+  __shared__ int tile_sh, last_head_sh, first_is_head_sh;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) { tile_sh = (int)atomicAdd(ticket, 1u); last_head_sh = -1; }
+  __syncthreads();
+  const int tile = tile_sh;
+  const int tile_base = tile * kTile;
+  const int i = tile_base + tid;
 
-/* stable partition of the three lists inside every subtree range, using the exclusive scans of the flags */
-__global__ void k_partition3(int n, int level_first, const int* __restrict__ seg_of_pos, const int* __restrict__ seg_pivot,
-                             const int* __restrict__ begin_cur, const uint8_t* __restrict__ flags,
-                             const int* __restrict__ in0, const int* __restrict__ in1, const int* __restrict__ in2,
-                             const unsigned long long* __restrict__ sc0, const unsigned long long* __restrict__ sc1,
-                             const unsigned long long* __restrict__ sc2, int* __restrict__ out0, int* __restrict__ out1,
-                             int* __restrict__ out2) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int s = seg_of_pos[i];
-  if (s == kDead) return;
-  const int j = s - level_first;
-  const int begin = begin_cur[j];
-  const int pivot = seg_pivot[j];
-  const uint32_t f = flags[i];
-  const int* in[3] = {in0, in1, in2};
-  const unsigned long long* sc[3] = {sc0, sc1, sc2};
-  int* out[3] = {out0, out1, out2};
-#pragma unroll
-  for (int d = 0; d < 3; d++) {
-    const uint32_t sd = (f >> (2 * d)) & 3u;
-    const unsigned long long here = sc[d][i], base = sc[d][begin];
-    int dst;
-    if (sd == 0) dst = begin + (int)((uint32_t)here - (uint32_t)base);
-    else if (sd == 1) dst = pivot + 1 + (int)((uint32_t)(here >> 32) - (uint32_t)(base >> 32));
-    else dst = pivot;
-    out[d][dst] = in[d][i];
+  int s = kDead, begin = 0, pivot = 0, dim = 0;
+  int e0 = 0, e1 = 0, e2 = 0;
+  uint32_t sd_a = 2u, sd_b = 2u, pos = 2u; /* sides of the element in slot 0 / slot 1 / the split-axis list */
+  if (i < n) { s = seg_of_pos[i]; e0 = in0[i]; e1 = in1[i]; e2 = in2[i]; }
+  const bool live = s != kDead;
+  uint64_t f = 0ull;
+  if (live) {
+    const int4 rec = *reinterpret_cast<const int4*>(seg_rec + (s - level_first));
+    pivot = rec.x & 0x3fffffff; dim = (int)((uint32_t)rec.x >> 30); begin = rec.y;
+    const uint2 pk = make_uint2((uint32_t)rec.z, (uint32_t)rec.w);
+    const float* c = dim == 0 ? c0 : (dim == 1 ? c1 : c2);
+    const uint32_t ea = (uint32_t)(dim == 0 ? e1 : (dim == 1 ? e2 : e0));
+    const uint32_t eb = (uint32_t)(dim == 0 ? e2 : (dim == 1 ? e0 : e1));
+    const uint32_t ka = ordered_key(c[ea]), kb = ordered_key(c[eb]);
+    sd_a = ea == pk.y ? 2u : ((ka < pk.x || (ka == pk.x && ea < pk.y)) ? 0u : 1u);
+    sd_b = eb == pk.y ? 2u : ((kb < pk.x || (kb == pk.x && eb < pk.y)) ? 0u : 1u);
+    pos = i < pivot ? 0u : (i > pivot ? 1u : 2u);
+    seg_next[i] = pos == 0u ? 2 * s + 1 : (pos == 1u ? 2 * s + 2 : kDead);
+    f = (sd_a == 0u ? 1ull : (sd_a == 2u ? 1ull << 11 : 0ull)) + (sd_b == 0u ? 1ull << 22 : (sd_b == 2u ? 1ull << 33 : 0ull));
+  } else if (i < n) {
+    seg_next[i] = kDead;
   }
+  const bool head = !live || i == begin;
+  if (head) atomicMax(&last_head_sh, tid);
+  if (tid == 0) first_is_head_sh = head ? 1 : 0;
+
+  /* exclusive scan of f over the tile */
+  uint64_t inc = f;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint64_t v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  if (lane == 31) warp_tot[wid] = inc;
+  __syncthreads();
+  if (wid == 0) {
+    uint64_t w = lane < kTile / 32 ? warp_tot[lane] : 0ull;
+#pragma unroll
+    for (int o = 1; o < kTile / 32; o <<= 1) {
+      const uint64_t v = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += v;
+    }
+    if (lane < kTile / 32) warp_tot[lane] = w; /* inclusive over warps */
+  }
+  __syncthreads();
+  const uint64_t ex = inc - f + (wid ? warp_tot[wid - 1] : 0ull);
+  scanv[tid] = ex;
+  const uint64_t total = warp_tot[kTile / 32 - 1];
+  const int last_head = last_head_sh;
+  const bool need_carry = !first_is_head_sh;
+  __syncthreads();
+
+  /* publish, and look back if the tile starts inside a range */
+  if (wid == 0) {
+    unsigned long long* mine = status + tile;
+    if (last_head >= 0) {
+      if (lane == 0) atomicExch(mine, kStPrefix | tile_to_global(total - scanv[last_head]));
+    } else {
+      if (lane == 0) atomicExch(mine, kStAgg | tile_to_global(total));
+    }
+    if (need_carry) {
+      uint64_t carry = 0ull;
+      int look = tile - 1;
+      while (true) {
+        const int t = look - lane;
+        uint64_t w = kStPrefix;
+        if (t >= 0) {
+          do { w = *reinterpret_cast<volatile unsigned long long*>(status + t); } while ((w & kStMask) == kStInvalid);
+        }
+        const unsigned resolved = __ballot_sync(0xffffffffu, (w & kStMask) == kStPrefix);
+        const int stop = resolved ? __ffs(resolved) - 1 : 32; /* nearest resolved tile */
+        uint64_t v = lane <= stop ? (w & ~kStMask) : 0ull;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        carry += v;
+        if (resolved) break;
+        look -= 32;
+      }
+      if (lane == 0) {
+        carry_sh = carry;
+        if (last_head < 0) atomicExch(mine, kStPrefix | (carry + tile_to_global(total)));
+      }
+    }
+  }
+  if (need_carry) __syncthreads();
+  if (!live) return;
+
+  uint32_t La, Pa, Lb, Pb;
+  if (begin >= tile_base) {
+    const uint64_t rel = ex - scanv[begin - tile_base]; /* field-wise, no borrows: the fields are monotone */
+    La = (uint32_t)(rel & 0x7ffu); Pa = (uint32_t)((rel >> 11) & 0x7ffu);
+    Lb = (uint32_t)((rel >> 22) & 0x7ffu); Pb = (uint32_t)((rel >> 33) & 0x7ffu);
+  } else {
+    const uint64_t g = carry_sh + tile_to_global(ex);
+    La = (uint32_t)(g & 0x3fffffffu); Pa = (uint32_t)((g >> 30) & 1u);
+    Lb = (uint32_t)((g >> 31) & 0x3fffffffu); Pb = (uint32_t)((g >> 61) & 1u);
+  }
+  const int off = i - begin;
+  const int dst_a = sd_a == 0u ? begin + (int)La : (sd_a == 1u ? pivot + 1 + (off - (int)La - (int)Pa) : pivot);
+  const int dst_b = sd_b == 0u ? begin + (int)Lb : (sd_b == 1u ? pivot + 1 + (off - (int)Lb - (int)Pb) : pivot);
+  if (dim == 0) { out0[i] = e0; out1[dst_a] = e1; out2[dst_b] = e2; }
+  else if (dim == 1) { out1[i] = e1; out2[dst_a] = e2; out0[dst_b] = e0; }
+  else { out2[i] = e2; out0[dst_a] = e0; out1[dst_b] = e1; }
 }
 
 /* ---- the last kLocalLevels levels: one CTA per subtree, everything in shared memory ----------
@@ -459,16 +532,11 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   ctx->launches++;
 
   /* three stable LSD radix sorts: ties keep ascending element index */
-  size_t cub_bytes = 0, scan_bytes = 0;
+  size_t cub_bytes = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys_in, keys_out, iota, ord[0][0], n, 0, 32, st);
-  {
-    SideFlagOp op{nullptr, 0};
-    cub::TransformInputIterator<unsigned long long, SideFlagOp, cub::CountingInputIterator<int>> it(cub::CountingInputIterator<int>(0), op);
-    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, it, (unsigned long long*)nullptr, n, st);
-  }
   void* cub_tmp = nullptr;
-  PM_B(ctx->get_scratch(pm::S_CUB, cub_bytes > scan_bytes ? cub_bytes : scan_bytes, &cub_tmp));
-  size_t cub_cap = cub_bytes > scan_bytes ? cub_bytes : scan_bytes;
+  PM_B(ctx->get_scratch(pm::S_CUB, cub_bytes, &cub_tmp));
+  const size_t cub_cap = cub_bytes;
   for (int d = 0; d < 3; d++) {
     size_t tb = cub_cap;
     PM_BC(cub::DeviceRadixSort::SortPairs(cub_tmp, tb, keys_in + (size_t)d * n, keys_out, iota, ord[0][d], n, 0, 32, st));
@@ -478,27 +546,30 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   /* per-level state */
   const int num_levels = 32 - __builtin_clz((unsigned)n);  /* floor(log2 n) + 1 */
   const int max_width = (n + 1) / 2 + 1;
-  float* box[2]; int* begin[2]; int *seg_pivot, *seg[2], *elem_of_node; uint8_t *seg_dim, *dim_of_node; uint2* seg_pkey;
-  unsigned long long* scan; uint8_t* flags;
+  const unsigned ntiles = (unsigned)pm::div_up(n, kTile);
+  const size_t status_words = (size_t)num_levels * ntiles + 64; /* per-level tile status words, then the tickets */
+  float* box[2]; int* begin[2]; int *seg[2], *elem_of_node, *local_of; uint8_t* dim_of_node; SegRec* seg_rec;
+  unsigned long long* status;
   PM_B(ctx->get_scratch(pm::S_BUILD6, (size_t)max_width * 6, &box[0]));
   PM_B(ctx->get_scratch(pm::S_BUILD7, (size_t)max_width * 6, &box[1]));
   PM_B(ctx->get_scratch(pm::S_BUILD8, (size_t)max_width, &begin[0]));
   PM_B(ctx->get_scratch(pm::S_BUILD9, (size_t)max_width, &begin[1]));
-  PM_B(ctx->get_scratch(pm::S_BUILD10, (size_t)max_width, &seg_pivot));
+  PM_B(ctx->get_scratch(pm::S_BUILD10, (size_t)n, &local_of));
   PM_B(ctx->get_scratch(pm::S_BUILD11, (size_t)n * 2, &seg[0]));
   seg[1] = seg[0] + n;
   PM_B(ctx->get_scratch(pm::S_BUILD12, (size_t)n, &elem_of_node));
-  PM_B(ctx->get_scratch(pm::S_BUILD13, (size_t)max_width + (size_t)n, &seg_dim));
-  dim_of_node = seg_dim + max_width;
-  PM_B(ctx->get_scratch(pm::S_BUILD16, (size_t)max_width, &seg_pkey));
-  PM_B(ctx->get_scratch(pm::S_BUILD14, (size_t)n * 3, &scan));
-  PM_B(ctx->get_scratch(pm::S_MISC1, (size_t)n, &flags));
+  PM_B(ctx->get_scratch(pm::S_BUILD13, (size_t)n, &dim_of_node));
+  PM_B(ctx->get_scratch(pm::S_BUILD16, (size_t)max_width, &seg_rec));
+  PM_B(ctx->get_scratch(pm::S_BUILD14, status_words, &status));
   float* bounds_dev = nullptr;
   PM_B(ctx->get_scratch(pm::S_BUILD15, (size_t)8, &bounds_dev));
 
   k_root<<<1, 32, 0, st>>>(ord[0][0], ord[0][1], ord[0][2], cx, cy, cz, n, box[0], begin[0], bounds_dev);
   ctx->launches++;
   PM_BC(cudaMemsetAsync(seg[0], 0, sizeof(int) * (size_t)n, st)); /* everything starts in subtree 0 */
+
+  unsigned int* tickets = reinterpret_cast<unsigned int*>(status + (size_t)num_levels * ntiles);
+  PM_BC(cudaMemsetAsync(status, 0, sizeof(unsigned long long) * status_words, st));
 
   int cur = 0;
   const int local_from = num_levels > kLocalLevels ? num_levels - kLocalLevels : 0; /* first level finished per CTA */
@@ -509,27 +580,19 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
       PM_BC(cudaFuncSetAttribute(k_finish_subtrees, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSmem)));
       k_finish_subtrees<<<(unsigned)level_count, kLocalThreads, sizeof(LocalSmem), st>>>(
           level_first, level_count, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
-          reinterpret_cast<int*>(scan), elem_of_node, dim_of_node);
+          local_of, elem_of_node, dim_of_node);
       ctx->launches++;
       break;
     }
     k_split<<<(unsigned)pm::div_up(level_count, 128), 128, 0, st>>>(
         level_first, level_count, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
-        box[(L + 1) & 1], begin[(L + 1) & 1], seg_pivot, seg_dim, seg_pkey, elem_of_node, dim_of_node);
+        box[(L + 1) & 1], begin[(L + 1) & 1], seg_rec, elem_of_node, dim_of_node);
     ctx->launches++;
     if (L == num_levels - 1) break;
-    k_flags<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, seg_dim, seg_pkey, ord[cur][0], ord[cur][1], ord[cur][2],
-                                   cx, cy, cz, flags, seg[(L + 1) & 1]);
-    for (int d = 0; d < 3; d++) {
-      SideFlagOp op{flags, 2 * d};
-      cub::TransformInputIterator<unsigned long long, SideFlagOp, cub::CountingInputIterator<int>> it(cub::CountingInputIterator<int>(0), op);
-      size_t tb = cub_cap;
-      PM_BC(cub::DeviceScan::ExclusiveSum(cub_tmp, tb, it, scan + (size_t)d * n, n, st));
-    }
-    k_partition3<<<nb256, 256, 0, st>>>(n, level_first, seg[L & 1], seg_pivot, begin[L & 1], flags, ord[cur][0], ord[cur][1],
-                                        ord[cur][2], scan, scan + (size_t)n, scan + 2 * (size_t)n, ord[cur ^ 1][0],
-                                        ord[cur ^ 1][1], ord[cur ^ 1][2]);
-    ctx->launches += 7;
+    k_level<<<ntiles, kTile, 0, st>>>(n, level_first, seg[L & 1], seg_rec, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz,
+                                      ord[cur ^ 1][0], ord[cur ^ 1][1], ord[cur ^ 1][2], seg[(L + 1) & 1],
+                                      status + (size_t)L * ntiles, tickets + L);
+    ctx->launches++;
     cur ^= 1;
   }
 
