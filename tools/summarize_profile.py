@@ -34,6 +34,8 @@ starts = [i for i, (nm, _) in enumerate(seq) if nm.endswith("k_morton")]
 # (the longest one: bench.py's later end-to-end steps run the same kernels on 131 072-query chunks)
 groups = [seq[a:b] for a, b in zip(starts, starts[1:])]
 groups = [g for g in groups if not any("k_split" in nm or "k_partition" in nm for nm, _ in g)]  # not a map build
+fast = [g for g in groups if any("k_grid_fast" in nm for nm, _ in g)]  # the C2 steps, not the C1 render's gathers
+groups = fast or groups
 step = max(groups, key=lambda g: sum(t for _, t in g)) if groups else []
 with open(os.path.join(out, f"{tag}_step_launches.csv"), "w") as f:
     f.write("# launches of ONE pm_knn step (k_morton .. last query kernel), in launch order; same ncu pass as the full list\n")
