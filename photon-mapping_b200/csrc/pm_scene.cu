@@ -8,9 +8,16 @@
  *   3. k_hierarchy   Karras 2012: one thread per inner node finds its key range and split
  *   4. k_refit       leaves walk up; the second arrival at a node merges the child boxes
  *   5. k_pack        inner node -> 64-byte record holding both (padded) child boxes
+ * Scenes of at most kSahMaxTris triangles (the reference's Cornell box has 58) get a full-sweep SAH hierarchy built
+ * on the host instead of steps 1-4 of the Morton build: same node records, same one-triangle leaves, fewer box and
+ * triangle tests per ray. The hierarchy only decides which triangles are skipped, never the hit that is returned.
  */
 #include <cub/cub.cuh>
+#include <algorithm>
 #include <cfloat>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
 #include "pm_scene.cuh"
 
 namespace {
@@ -161,6 +168,72 @@ __global__ void k_trace_occluded(SceneView sc, const pm_ray* __restrict__ rays, 
   occ[i] = trace<true>(sc, v3(r.org), v3(r.dir), r.tmin, r.tmax).prim >= 0 ? 1 : 0;
 }
 
+/* ---- host-side SAH build for small scenes ---- */
+constexpr int kSahMaxTris = 4096;
+constexpr int kSahMaxDepth = 44; /* below this depth: median splits (<= 12 more levels), so the 64-entry ray stack holds */
+
+struct SahBuilder {
+  const float* tb;            /* 6 floats per triangle: lo, hi */
+  std::vector<int> order;     /* leaf slot -> triangle */
+  std::vector<int> c0, c1;    /* inner node -> child (inner index or ~slot) */
+  std::vector<float> cbox;    /* inner node -> the two child boxes, 12 floats */
+  std::vector<float> lcost;   /* sweep scratch */
+
+  static float half_area(const float* b) {
+    const float dx = b[3] - b[0], dy = b[4] - b[1], dz = b[5] - b[2];
+    return dx * dy + dy * dz + dz * dx;
+  }
+  static void grow(float* b, const float* t) {
+    for (int d = 0; d < 3; d++) { b[d] = std::min(b[d], t[d]); b[3 + d] = std::max(b[3 + d], t[3 + d]); }
+  }
+  static void empty(float* b) { for (int d = 0; d < 3; d++) { b[d] = FLT_MAX; b[3 + d] = -FLT_MAX; } }
+
+  void sort_axis(int* ids, int cnt, int axis) const {
+    const float* t = tb;
+    std::sort(ids, ids + cnt, [t, axis](int a, int b) {
+      const float ca = t[6 * (size_t)a + axis] + t[6 * (size_t)a + 3 + axis], cb = t[6 * (size_t)b + axis] + t[6 * (size_t)b + 3 + axis];
+      return ca < cb || (ca == cb && a < b);
+    });
+  }
+
+  /* builds the subtree over ids[0, cnt); returns its encoded reference and its box */
+  int build(int* ids, int cnt, int depth, float* box) {
+    if (cnt == 1) {
+      const int slot = (int)order.size();
+      order.push_back(ids[0]);
+      for (int d = 0; d < 6; d++) box[d] = tb[6 * (size_t)ids[0] + d];
+      return ~slot;
+    }
+    const int me = (int)c0.size();
+    c0.push_back(0); c1.push_back(0); cbox.resize(cbox.size() + 12);
+    int best_axis = 0, best_i = cnt / 2;
+    if (depth < kSahMaxDepth) {
+      float best = FLT_MAX;
+      lcost.resize((size_t)cnt);
+      for (int axis = 0; axis < 3; axis++) {
+        sort_axis(ids, cnt, axis);
+        float b[6];
+        empty(b);
+        for (int i = 0; i < cnt - 1; i++) { grow(b, tb + 6 * (size_t)ids[i]); lcost[i + 1] = half_area(b) * (float)(i + 1); }
+        empty(b);
+        for (int i = cnt - 1; i >= 1; i--) {
+          grow(b, tb + 6 * (size_t)ids[i]);
+          const float cost = lcost[i] + half_area(b) * (float)(cnt - i);
+          if (cost < best) { best = cost; best_axis = axis; best_i = i; }
+        }
+      }
+    }
+    sort_axis(ids, cnt, best_axis);
+    float b0[6], b1[6];
+    const int r0 = build(ids, best_i, depth + 1, b0);
+    const int r1 = build(ids + best_i, cnt - best_i, depth + 1, b1);
+    c0[me] = r0; c1[me] = r1;
+    for (int d = 0; d < 6; d++) { cbox[12 * (size_t)me + d] = b0[d]; cbox[12 * (size_t)me + 6 + d] = b1[d]; }
+    for (int d = 0; d < 3; d++) { box[d] = std::min(b0[d], b1[d]); box[3 + d] = std::max(b0[3 + d], b1[3 + d]); }
+    return me;
+  }
+};
+
 }  // namespace
 
 extern "C" {
@@ -230,6 +303,40 @@ int pm_scene_create(pm_ctx* ctx, const float* verts_host, int nv, const int32_t*
     PM_SC(cudaMemcpyAsync(s->tris, rec, sizeof(float4) * 3, cudaMemcpyDeviceToDevice, st));
     k_single<<<1, 1, 0, st>>>(tri_box, pad, s->nodes);
     ctx->launches++;
+  } else if (nt <= kSahMaxTris && !getenv("PM_SCENE_LBVH")) {
+    std::vector<float> tbox((size_t)nt * 6);
+    for (int i = 0; i < nt; i++)
+      for (int d = 0; d < 3; d++) {
+        const float a = verts_host[3 * (size_t)tris_host[3 * i] + d], b = verts_host[3 * (size_t)tris_host[3 * i + 1] + d],
+                    c = verts_host[3 * (size_t)tris_host[3 * i + 2] + d];
+        tbox[6 * (size_t)i + d] = fminf(a, fminf(b, c));
+        tbox[6 * (size_t)i + 3 + d] = fmaxf(a, fmaxf(b, c));
+      }
+    SahBuilder sah;
+    sah.tb = tbox.data();
+    std::vector<int> ids((size_t)nt);
+    for (int i = 0; i < nt; i++) ids[i] = i;
+    float root_box[6];
+    sah.build(ids.data(), nt, 0, root_box);
+    std::vector<float4> hnodes((size_t)(nt - 1) * 4);
+    for (int i = 0; i < nt - 1; i++) {
+      const float* b0 = &sah.cbox[12 * (size_t)i];
+      const float* b1 = b0 + 6;
+      hnodes[4 * (size_t)i + 0] = make_float4(b0[0] - pad, b0[3] + pad, b0[1] - pad, b0[4] + pad);
+      hnodes[4 * (size_t)i + 1] = make_float4(b1[0] - pad, b1[3] + pad, b1[1] - pad, b1[4] + pad);
+      hnodes[4 * (size_t)i + 2] = make_float4(b0[2] - pad, b0[5] + pad, b1[2] - pad, b1[5] + pad);
+      int c0 = sah.c0[i], c1 = sah.c1[i];
+      float4 q;
+      memcpy(&q.x, &c0, 4); memcpy(&q.y, &c1, 4); q.z = q.w = 0.f;
+      hnodes[4 * (size_t)i + 3] = q;
+    }
+    std::vector<uint64_t> hkeys((size_t)nt);
+    for (int j = 0; j < nt; j++) hkeys[j] = (uint64_t)(uint32_t)sah.order[j];
+    PM_SC(cudaMemcpyAsync(s->nodes, hnodes.data(), sizeof(float4) * hnodes.size(), cudaMemcpyHostToDevice, st));
+    PM_SC(cudaMemcpyAsync(keys_out, hkeys.data(), sizeof(uint64_t) * hkeys.size(), cudaMemcpyHostToDevice, st));
+    k_permute_tris<<<(unsigned)pm::div_up(3 * (int64_t)nt, 256), 256, 0, st>>>(nt, keys_out, rec, s->tris);
+    ctx->launches++;
+    PM_SC(cudaStreamSynchronize(st)); /* the host vectors go out of scope */
   } else {
     size_t tb = 0;
     cub::DeviceRadixSort::SortKeys(nullptr, tb, keys_in, keys_out, nt, 0, 62, st);

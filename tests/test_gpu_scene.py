@@ -35,7 +35,7 @@ def test_trace_closest_matches_bruteforce_on_reference_assets(pkg, ctx, orc, nam
     assert np.array_equal(occ, oracle_occluded(orc, sc, rays))
 
 
-@pytest.mark.parametrize("nt", [1, 2, 3, 17, 1000, 20000])
+@pytest.mark.parametrize("nt", [1, 2, 3, 17, 1000, 4096, 4097, 20000])  # <= 4096: host SAH hierarchy, above: LBVH
 def test_trace_closest_soup(pkg, ctx, orc, nt):
     sc = soup_scene(nt, nt)
     s = make_scene(pkg, ctx, sc)
@@ -45,6 +45,23 @@ def test_trace_closest_soup(pkg, ctx, orc, nt):
     want = oracle_trace(orc, sc, rays)
     assert np.array_equal(got["prim"], want["prim"])
     assert got["t"].tobytes() == want["t"].tobytes()
+    assert np.array_equal(s.trace_occluded(rays), oracle_occluded(orc, sc, rays))
+
+
+def test_trace_nested_triangles_deep_sah_chain(pkg, ctx, orc):
+    """Concentric coplanar-ish triangles of growing size: the SAH sweep peels one triangle per level, so the
+    builder's depth guard (median splits below level 44) has to keep the ray stack within its 64 entries."""
+    n = 300
+    k = np.arange(1, n + 1, dtype=np.float32)
+    ang = np.array([0.0, 2.1, 4.2], np.float32)
+    verts = np.stack([np.stack([k * np.cos(a), k * np.sin(a), 0.01 * k], 1) for a in ang], 1).reshape(-1, 3).astype(np.float32)
+    sc = {"verts": verts, "tris": np.arange(3 * n, dtype=np.int32).reshape(n, 3), "tri_mesh": np.zeros(n, np.int32),
+          "mats": np.zeros(1, pkg.MATERIAL)}
+    s = make_scene(pkg, ctx, sc)
+    rays = random_rays(20000, 77, [-50, -50, -20], [50, 50, 20])
+    got, want = s.trace_closest(rays), oracle_trace(orc, sc, rays)
+    assert (want["prim"] >= 0).sum() > 1000
+    assert np.array_equal(got["prim"], want["prim"]) and got["t"].tobytes() == want["t"].tobytes()
     assert np.array_equal(s.trace_occluded(rays), oracle_occluded(orc, sc, rays))
 
 

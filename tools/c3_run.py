@@ -38,8 +38,9 @@ depth = 8
 cap_g, cap_c = casted * 3, max(casted // 10, 1) * 2
 d_g = torch.empty(cap_g * 40, dtype=torch.uint8, device="cuda")
 d_c = torch.empty(cap_c * 40, dtype=torch.uint8, device="cuda")
+(_, ng, paths, segs), ms_first = timed(lambda: scene.emit_photons(lights, casted, depth, False, seed=1, rng_mode=pkg.RNG_COUNTER, out=d_g, capacity=cap_g))
 (_, ng, paths, segs), ms = timed(lambda: scene.emit_photons(lights, casted, depth, False, seed=1, rng_mode=pkg.RNG_COUNTER, out=d_g, capacity=cap_g))
-res["emit_global"] = {"ms": ms, "paths": paths, "segments": segs, "stored": ng, "walk_kernel_ms": ctx.last_kernel_ms}
+res["emit_global"] = {"ms": ms, "ms_first": ms_first, "paths": paths, "segments": segs, "stored": ng, "walk_kernel_ms": ctx.last_kernel_ms}
 (_, nc, paths_c, segs_c), ms = timed(lambda: scene.emit_photons(lights, casted // 10, depth, True, seed=1, rng_mode=pkg.RNG_COUNTER, out=d_c, capacity=cap_c))
 res["emit_caustic"] = {"ms": ms, "paths": paths_c, "segments": segs_c, "stored": nc}
 g44 = torch.empty((ng + nc) * 44, dtype=torch.uint8, device="cuda")
