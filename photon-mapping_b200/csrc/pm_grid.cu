@@ -752,8 +752,12 @@ k_grid_fast(const GridView g, const float4* __restrict__ color4, const pmk::Quer
 /* ---- fixed-radius gather (progressive photon mapping pass; SURVEY appendix B — no reference code) ------
  * Per hit point: flux = brdf * sum(power * colour) over the nodes with dist² < radius², count = their number.
  * Same candidate enumeration as k_grid_query (ball-trimmed rows of the smallest block that covers the ball),
- * no selection. Hit points whose ball no block of up to (2 kMaxH + 1)^3 cells covers, or whose rows are too
- * dense for the flat index space, go to the kd-tree range kernel below. */
+ * no selection. Rows are taken 32 at a time (one per lane); a chunk of rows with at most kMaxScan candidates is
+ * flattened into one index space so that short rows still fill the warp, a denser chunk is streamed row by row
+ * (its rows are long: every step is a coalesced 512-byte read). Early passes of a progressive render hold
+ * thousands of photons per ball on blocks of 15..20 cells a side: both used to fall to the per-thread kd-tree
+ * range kernel below, which now only sees balls that no block of (2 kMaxHRadius + 1)^3 cells covers. */
+constexpr int kMaxHRadius = 48;
 __global__ void __launch_bounds__(kWarps * 32)
 k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
               const float* __restrict__ radius2, const int* __restrict__ order, int nq, float* __restrict__ out_flux,
@@ -775,10 +779,10 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
     const int cx = min(max(__float2int_rd(fx), 0), g.nx - 1), cy = min(max(__float2int_rd(fy), 0), g.ny - 1),
               cz = min(max(__float2int_rd(fz), 0), g.nz - 1);
     /* smallest block whose guaranteed radius covers the ball */
-    int h = min(max(__float2int_ru(sqrtf(R2) * g.inv_cell), 1), kMaxH);
+    int h = min(max(__float2int_ru(sqrtf(R2) * g.inv_cell), 1), kMaxHRadius);
     int x0, x1, y0, y1, z0, z1;
     bool covered = false;
-    for (; h <= kMaxH; h++) {
+    for (; h <= kMaxHRadius; h++) {
       x0 = max(cx - h, 0); x1 = min(cx + h, g.nx - 1);
       y0 = max(cy - h, 0); y1 = min(cy + h, g.ny - 1);
       z0 = max(cz - h, 0); z1 = min(cz + h, g.nz - 1);
@@ -801,7 +805,7 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
         const int row = r0 + lane;
         int len = 0, st = 0;
         if (row < nrows) {
-          const int rzo = div_small(row, ny_r);
+          const int rzo = row / ny_r;
           const int ry = y0 + row - rzo * ny_r, rz = z0 + rzo;
           const float ylo = g.lo[1] + (float)ry * g.cell, zlo = g.lo[2] + (float)rz * g.cell;
           const float dy = fmaxf(fmaxf(ylo - qy, qy - (ylo + g.cell)) - g.margin, 0.f);
@@ -827,7 +831,26 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
         }
         const int mc = __shfl_sync(0xffffffffu, incl, 31);
         if (mc == 0) continue;
-        if (mc > kMaxScan) { give_up = true; break; }
+        if (mc > kMaxScan) { /* dense chunk: row by row */
+          unsigned rows_left = __ballot_sync(0xffffffffu, len > 0);
+          while (rows_left) {
+            const int r = __ffs(rows_left) - 1;
+            rows_left &= rows_left - 1;
+            const int rs = __shfl_sync(0xffffffffu, st, r), rl = __shfl_sync(0xffffffffu, len, r);
+            for (int j = lane; j < rl; j += 32) {
+              const float4 p = __ldg(g.pts + (rs + j));
+              const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+              if (d2 < R2) {
+                const float4 c = __ldg(color4 + __float_as_int(p.w));
+                sr = __fadd_rn(sr, __fmul_rn(c.w, c.x));
+                sg = __fadd_rn(sg, __fmul_rn(c.w, c.y));
+                sb = __fadd_rn(sb, __fmul_rn(c.w, c.z));
+                cnt++;
+              }
+            }
+          }
+          continue;
+        }
         const int P = incl - len;
         __syncwarp();
         ws.words[lane] = make_uint2(0u, 0u);

@@ -55,3 +55,22 @@ def test_progressive_passes_match_oracle_loop(pkg, ctx, orc):
     assert np.allclose(got["tau"], tau, rtol=2e-4, atol=1e-6)
     assert got["emitted"] == passes * per_pass and np.isfinite(got["radiance"]).all() and got["radiance"].max() > 0
     assert (r2 < np.float32(r0) ** 2).any()
+
+
+@pytest.mark.gpu
+def test_device_resident_loop_equals_host_loop(pkg, ctx):
+    """progressive_render_device keeps photons, maps and per-pixel state in HBM; on one GPU its N, r² and tau equal
+    the host loop's bit for bit (same C-ABI calls, the update restated in torch float32)."""
+    ppm = graft.load_package_module("ppm")
+    sc = load_scene("cornell_box")
+    scene = pkg.Scene(ctx, sc["verts"], sc["tris"], sc["tri_mesh"], sc["mats"])
+    W, H, passes, per_pass, r0, alpha, depth = 64, 40, 4, 30000, 2.5, 0.7, 6
+    cam = pkg.make_camera((80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87, W, H)
+    host = ppm.progressive_render(pkg, ctx, scene, sc["tri_mesh"], sc["mats"], sc["lights"], cam, W, H, passes, per_pass, r0, alpha,
+                                  depth, seed=9)
+    stats = []
+    dev = ppm.progressive_render_device(pkg, ctx, scene, sc["tri_mesh"], sc["mats"], sc["lights"], cam, W, H, passes, per_pass, r0,
+                                        alpha, depth, seed=9, stats=stats)
+    assert np.array_equal(dev["N"], host["N"]) and np.array_equal(dev["r2"], host["r2"])
+    assert np.array_equal(dev["tau"], host["tau"]) and np.array_equal(dev["radiance"], host["radiance"])
+    assert len(stats) == passes and all(s["stored"] > 0 for s in stats) and dev["emitted"] == passes * per_pass
