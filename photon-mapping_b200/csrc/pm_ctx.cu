@@ -99,6 +99,16 @@ int pm_ctx_create(int device, pm_ctx** out) {
   PM_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   PM_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  {
+    /* photon-map buffers come from the stream-ordered pool (pm_internal.h: map_alloc); keep up to 8 GB cached */
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      uint64_t keep = 8ull << 30, cur = 0;
+      cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &cur);
+      if (cur < keep) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    cudaGetLastError();
+  }
   PM_CUDA(cudaEventCreate(&c->ev0));
   PM_CUDA(cudaEventCreate(&c->ev1));
   *out = c;

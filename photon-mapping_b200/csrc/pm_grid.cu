@@ -1057,10 +1057,10 @@ int grid_build(pm_ctx* ctx, pm_map* m) {
   PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)n, &keys_out));
   PM_CHECK(ctx->get_scratch(pm::S_VALS0, (size_t)n, &vals_in));
   PM_CHECK(ctx->get_scratch(pm::S_VALS1, (size_t)n, &vals_out));
-  if (cudaMalloc(&m->grid_pts, sizeof(float4) * ((size_t)n + 32)) != cudaSuccess ||
-      cudaMalloc(&m->cell_start, sizeof(uint32_t) * (size_t)(n_cells + 1)) != cudaSuccess) {
+  if (pm::map_alloc(&m->grid_pts, sizeof(float4) * ((size_t)n + 32), st) != cudaSuccess ||
+      pm::map_alloc(&m->cell_start, sizeof(uint32_t) * (size_t)(n_cells + 1), st) != cudaSuccess) {
     cudaGetLastError();
-    if (m->grid_pts) cudaFree(m->grid_pts);
+    pm::map_free(m->grid_pts);
     m->grid_pts = nullptr; m->cell_start = nullptr; /* no grid: the kd-tree kernels answer everything */
     return PM_OK;
   }

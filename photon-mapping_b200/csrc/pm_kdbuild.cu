@@ -471,8 +471,8 @@ __global__ void k_make_soa(int n, const pm_photon44* __restrict__ ph, float4* __
 
 int make_soa(pm_ctx* ctx, pm_map* m) {
   const int n = (int)m->n;
-  PM_CUDA(cudaMalloc(&m->nodes4, sizeof(float4) * (size_t)n));
-  PM_CUDA(cudaMalloc(&m->color4, sizeof(float4) * (size_t)n));
+  PM_CUDA(pm::map_alloc(&m->nodes4, sizeof(float4) * (size_t)n, ctx->stream));
+  PM_CUDA(pm::map_alloc(&m->color4, sizeof(float4) * (size_t)n, ctx->stream));
   k_make_soa<<<(unsigned)pm::div_up(n, 256), 256, 0, ctx->stream>>>(n, m->photons_dev, m->nodes4, m->color4);
   ctx->launches++;
   PM_CUDA(cudaGetLastError());
@@ -500,7 +500,7 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   if (dev_in) {
     tree = photons;
   } else {
-    if (cudaMalloc(&m->owned_photons, sizeof(pm_photon44) * (size_t)n) != cudaSuccess) {
+    if (pm::map_alloc(&m->owned_photons, sizeof(pm_photon44) * (size_t)n, ctx->stream) != cudaSuccess) {
       cudaGetLastError(); delete m; pm::set_error("pm_map_build: out of device memory"); return PM_ERR_NOMEM;
     }
     tree = m->owned_photons;
@@ -625,7 +625,7 @@ int pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map*
   if (pm::is_device_ptr(photons)) {
     m->photons_dev = photons;
   } else {
-    if (cudaMalloc(&m->owned_photons, sizeof(pm_photon44) * (size_t)n) != cudaSuccess) {
+    if (pm::map_alloc(&m->owned_photons, sizeof(pm_photon44) * (size_t)n, ctx->stream) != cudaSuccess) {
       cudaGetLastError(); delete m; pm::set_error("pm_map_from_tree: out of device memory"); return PM_ERR_NOMEM;
     }
     cudaMemcpyAsync(m->owned_photons, photons, sizeof(pm_photon44) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
@@ -644,11 +644,12 @@ void pm_map_destroy(pm_map* m) {
   if (!m) return;
   cudaSetDevice(m->device);
   cudaDeviceSynchronize();
-  if (m->owned_photons) cudaFree(m->owned_photons);
-  if (m->nodes4) cudaFree(m->nodes4);
-  if (m->color4) cudaFree(m->color4);
-  if (m->grid_pts) cudaFree(m->grid_pts);
-  if (m->cell_start) cudaFree(m->cell_start);
+  pm::map_free(m->owned_photons);
+  pm::map_free(m->nodes4);
+  pm::map_free(m->color4);
+  pm::map_free(m->grid_pts);
+  pm::map_free(m->cell_start);
+  cudaStreamSynchronize((cudaStream_t)0); /* the frees have happened: the next build may take the memory on its own stream */
   delete m;
 }
 
