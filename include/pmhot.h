@@ -193,6 +193,12 @@ int  pm_photons_to_maps(pm_ctx* ctx, const pm_photon40* global_in, int64_t n_glo
 int  pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n, float* bounds_host, pm_map** out);
 /* Wrap an array that is ALREADY in tree order (e.g. built by the reference builder). */
 int  pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map** out);
+/* Cells-only map for fixed-radius gathers (progressive mode, BASELINE configs[4]; no reference counterpart): the
+ * photons stay in input order, no kd-tree is built — only the query-side copies and the uniform-grid copy with the
+ * cell size the caller names (about half the gather radius works well). pm_gather_radius answers every ball from the
+ * cells (blocks grow to the whole grid if they must); pm_knn / pm_gather / pm_render reject such a map
+ * (PM_ERR_INVALID). Builds in a fraction of pm_map_build's time: a progressive pass needs a new map per pass. */
+int  pm_map_build_cells(pm_ctx* ctx, const pm_photon44* photons, int64_t n, float cell_size, pm_map** out);
 void pm_map_destroy(pm_map* map);
 int64_t pm_map_size(const pm_map* map);
 

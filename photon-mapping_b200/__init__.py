@@ -76,6 +76,7 @@ _SIGNATURES = {
     "pm_photons_to_maps": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "pm_map_build": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, POINTER(c_void_p)]),
     "pm_map_from_tree": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_void_p)]),
+    "pm_map_build_cells": (c_int, [c_void_p, c_void_p, c_int64, c_float, POINTER(c_void_p)]),
     "pm_map_destroy": (None, [c_void_p]),
     "pm_map_size": (c_int64, [c_void_p]),
     "pm_knn": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p, c_void_p, c_void_p]),
@@ -214,6 +215,14 @@ class PhotonMap:
         n = _count(photons, 44)
         h = c_void_p()
         _check(lib().pm_map_from_tree(ctx.handle, _ptr(photons), n, ctypes.byref(h)))
+        return cls(ctx, h, n, None, photons)
+
+    @classmethod
+    def build_cells(cls, ctx: Context, photons, cell_size: float) -> "PhotonMap":
+        """pm_map_build_cells: cells-only map (input order, no kd-tree) for `gather_radius`; kNN calls reject it."""
+        n = _count(photons, 44)
+        h = c_void_p()
+        _check(lib().pm_map_build_cells(ctx.handle, _ptr(photons), n, cell_size, ctypes.byref(h)))
         return cls(ctx, h, n, None, photons)
 
     def close(self) -> None:

@@ -760,7 +760,7 @@ k_grid_fast(const GridView g, const float4* __restrict__ color4, const pmk::Quer
 constexpr int kMaxHRadius = 48;
 __global__ void __launch_bounds__(kWarps * 32)
 k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
-              const float* __restrict__ radius2, const int* __restrict__ order, int nq, float* __restrict__ out_flux,
+              const float* __restrict__ radius2, const int* __restrict__ order, int nq, int max_h, float* __restrict__ out_flux,
               int32_t* __restrict__ out_count, int* __restrict__ fb_list, int* __restrict__ fb_count) {
   __shared__ WarpScratch scratch[kWarps];
   const int lane = threadIdx.x & 31;
@@ -779,10 +779,10 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
     const int cx = min(max(__float2int_rd(fx), 0), g.nx - 1), cy = min(max(__float2int_rd(fy), 0), g.ny - 1),
               cz = min(max(__float2int_rd(fz), 0), g.nz - 1);
     /* smallest block whose guaranteed radius covers the ball */
-    int h = min(max(__float2int_ru(sqrtf(R2) * g.inv_cell), 1), kMaxHRadius);
+    int h = min(max(__float2int_ru(sqrtf(R2) * g.inv_cell), 1), max_h);
     int x0, x1, y0, y1, z0, z1;
     bool covered = false;
-    for (; h <= kMaxHRadius; h++) {
+    for (; h <= max_h; h++) {
       x0 = max(cx - h, 0); x1 = min(cx + h, g.nx - 1);
       y0 = max(cy - h, 0); y1 = min(cy + h, g.ny - 1);
       z0 = max(cz - h, 0); z1 = min(cz + h, g.nz - 1);
@@ -1001,39 +1001,70 @@ int host_cell_of(float v, float lo, float inv_cell) {
 
 namespace pm {
 
-int grid_build(pm_ctx* ctx, pm_map* m) {
-  if (m->n < kMinGridNodes) return PM_OK;
+/* cells-only maps: colours follow the cell order of grid_pts and the id a record carries becomes its own position,
+ * so the colour of a candidate sits next to its position (input order is the order photons were traced in: every
+ * colour fetch would be a DRAM sector of its own) */
+__global__ void k_cells_reorder(int n, float4* __restrict__ pts, const float4* __restrict__ color_in, float4* __restrict__ color_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float4 p = pts[i];
+  color_out[i] = __ldg(color_in + __float_as_int(p.w));
+  p.w = __int_as_float(i);
+  pts[i] = p;
+}
+
+int cells_reorder(pm_ctx* ctx, pm_map* m) {
+  if (!m->grid_pts) return PM_OK;
+  const int n = (int)m->n;
+  float4* sorted = nullptr;
+  PM_CUDA(pm::map_alloc(&sorted, sizeof(float4) * (size_t)n, ctx->stream));
+  k_cells_reorder<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(n, m->grid_pts, m->color4, sorted);
+  ctx->launches++;
+  PM_CUDA(cudaGetLastError());
+  PM_CUDA(cudaFreeAsync(m->color4, ctx->stream));
+  m->color4 = sorted;
+  return PM_OK;
+}
+
+int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
+  const bool given = cell_size > 0.f; /* cells-only map: the caller names the cell, nothing is sampled (there is no tree) */
+  if (!given && m->n < kMinGridNodes) return PM_OK;
   const int n = (int)m->n;
   cudaStream_t st = ctx->stream;
-
-  /* 1. sample of exact k-th-neighbour distances (kd-tree kernel on kTuneSamples node positions) */
-  const int ns = kTuneSamples;
-  float *sq = nullptr, *sr2 = nullptr;
-  PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)ns * 3, &sq));
-  PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)ns, &sr2));
-  k_sample_queries<<<(unsigned)div_up(ns, 256), 256, 0, st>>>(m->nodes4, n, ns, sq);
-  ctx->launches++;
-  pmk::QueryIO io;
-  io.q = sq; io.nq = ns; io.k = kTuneK; io.cutoff2 = INFINITY; io.r2 = sr2;
-  PM_CHECK(kd_query(ctx, m, io, false, nullptr, nullptr));
-  std::vector<float> r2(ns);
-  PM_CUDA(cudaMemcpyAsync(r2.data(), sr2, sizeof(float) * ns, cudaMemcpyDeviceToHost, st));
-  PM_CUDA(cudaStreamSynchronize(st));
-  std::sort(r2.begin(), r2.end());
-  const float r50 = std::sqrt(r2[ns / 2]), r98 = std::sqrt(r2[(size_t)(ns * 0.98)]);
-  if (!(r98 > 0.f) || !std::isfinite(r98)) return PM_OK; /* degenerate cloud: kd-tree kernels only */
-  /* G >= 2 cells: two cells must cover the k-th-neighbour distance of nearly every query. Tight
-   * distributions (uniform clouds) take the 98th percentile plus a little; broad ones would pay
-   * for their tail in every dense neighbourhood, so they take the 90th and leave the rest to the
-   * kd-tree kernel. */
-  const float rk = r98 < 1.25f * r50 ? r98 * 1.03f : std::sqrt(r2[(size_t)(ns * 0.90)]);
-  float cell = 0.5f * rk;
+  float cell = cell_size, rk = 2.f * cell_size;
+  bool uniform_like = false;
+  if (!given) {
+    /* 1. sample of exact k-th-neighbour distances (kd-tree kernel on kTuneSamples node positions) */
+    const int ns = kTuneSamples;
+    float *sq = nullptr, *sr2 = nullptr;
+    PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)ns * 3, &sq));
+    PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)ns, &sr2));
+    k_sample_queries<<<(unsigned)div_up(ns, 256), 256, 0, st>>>(m->nodes4, n, ns, sq);
+    ctx->launches++;
+    pmk::QueryIO io;
+    io.q = sq; io.nq = ns; io.k = kTuneK; io.cutoff2 = INFINITY; io.r2 = sr2;
+    PM_CHECK(kd_query(ctx, m, io, false, nullptr, nullptr));
+    std::vector<float> r2(ns);
+    PM_CUDA(cudaMemcpyAsync(r2.data(), sr2, sizeof(float) * ns, cudaMemcpyDeviceToHost, st));
+    PM_CUDA(cudaStreamSynchronize(st));
+    std::sort(r2.begin(), r2.end());
+    const float r50 = std::sqrt(r2[ns / 2]), r98 = std::sqrt(r2[(size_t)(ns * 0.98)]);
+    if (!(r98 > 0.f) || !std::isfinite(r98)) return PM_OK; /* degenerate cloud: kd-tree kernels only */
+    /* G >= 2 cells: two cells must cover the k-th-neighbour distance of nearly every query. Tight
+     * distributions (uniform clouds) take the 98th percentile plus a little; broad ones would pay
+     * for their tail in every dense neighbourhood, so they take the 90th and leave the rest to the
+     * kd-tree kernel. */
+    rk = r98 < 1.25f * r50 ? r98 * 1.03f : std::sqrt(r2[(size_t)(ns * 0.90)]);
+    cell = 0.5f * rk;
+    uniform_like = r98 < 1.25f * r50;
+  }
   float maxabs = 0.f;
   for (int d = 0; d < 3; d++) {
     maxabs = std::max(maxabs, std::max(std::fabs(m->bounds[d]), std::fabs(m->bounds[3 + d])));
   }
   int dim[3];
-  const int64_t cell_cap = std::min(kMaxCellCap, std::max(kMinCellCap, (int64_t)32 * n));
+  /* a cells-only map is rebuilt every pass: keep its offset table (4 B per cell, cleared and filled per build) small */
+  const int64_t cell_cap = std::min(kMaxCellCap, std::max(kMinCellCap, (int64_t)(given ? 8 : 32) * n));
   while (true) {
     const float inv = 1.f / cell;
     int64_t cells = 1;
@@ -1046,7 +1077,7 @@ int grid_build(pm_ctx* ctx, pm_map* m) {
     cell *= 1.26f;
   }
   m->cell = cell; m->inv_cell = 1.f / cell; m->tuned_rk = rk;
-  m->fast_path = r98 < 1.25f * r50; /* the descriptor pass models the cloud as locally uniform */
+  m->fast_path = uniform_like; /* the descriptor pass models the cloud as locally uniform */
   m->cell_margin = 1e-3f * cell + 16.f * FLT_EPSILON * maxabs;
   m->gdim[0] = dim[0]; m->gdim[1] = dim[1]; m->gdim[2] = dim[2];
   const int64_t n_cells = (int64_t)dim[0] * dim[1] * dim[2];
@@ -1062,6 +1093,7 @@ int grid_build(pm_ctx* ctx, pm_map* m) {
     cudaGetLastError();
     pm::map_free(m->grid_pts);
     m->grid_pts = nullptr; m->cell_start = nullptr; /* no grid: the kd-tree kernels answer everything */
+    if (given) { pm::set_error("pm_map_build_cells: out of device memory for the cell table"); return PM_ERR_NOMEM; }
     return PM_OK;
   }
   PM_CUDA(cudaMemsetAsync(m->grid_pts + n, 0, sizeof(float4) * 32, st)); /* read (and dropped) by lanes past a query's last candidate */
@@ -1128,8 +1160,12 @@ int radius_query(pm_ctx* ctx, const pm_map* map, const float* q, const float* br
     int64_t grid = div_up(nq, kWarps);
     const int64_t cap = (int64_t)ctx->sm_count * 64;
     if (grid > cap) grid = cap;
-    k_grid_radius<<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, out_flux, out_count,
-                                                                  fb_list, fb_count);
+    /* a cells-only map has no tree to fall back on: its blocks may grow to the whole grid (then every side is
+     * clipped and the block covers any ball), so nothing is ever handed over */
+    const int max_h = map->cells_only ? std::max(map->gdim[0], std::max(map->gdim[1], map->gdim[2])) : kMaxHRadius;
+    k_grid_radius<<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, max_h, out_flux,
+                                                                  out_count, fb_list, fb_count);
+    if (map->cells_only) { ctx->launches++; PM_CUDA(cudaGetLastError()); return PM_OK; }
     if (kd_grid > ctx->sm_count * 2) kd_grid = ctx->sm_count * 2;
     k_kd_radius<<<(unsigned)kd_grid, 128, 0, ctx->stream>>>(map->nodes4, map->color4, (int)map->n, q, brdf, radius2, nq, fb_list,
                                                            fb_count, out_flux, out_count);

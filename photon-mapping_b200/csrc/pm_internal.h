@@ -126,12 +126,15 @@ struct pm_map {
   int gdim[3] = {0, 0, 0};
   float tuned_rk = 0.f;                      /* sampled k-th neighbour distance the cell size came from */
   bool fast_path = false;                    /* uniform-like cloud: k_fast_prep + k_grid_fast answer most queries */
+  bool cells_only = false;                   /* pm_map_build_cells: input order, no kd-tree; fixed-radius gathers only */
 };
 
 namespace pm {
 /* pm_grid.cu: builds the uniform-grid copy of a map whose nodes4 and bounds are valid; maps it
  * leaves without a grid are answered by the kd-tree kernels alone. */
-int grid_build(pm_ctx* ctx, pm_map* m);
+int grid_build(pm_ctx* ctx, pm_map* m, float cell_size = 0.f);
+/* pm_grid.cu: cells-only maps — colours into cell order, record ids = positions */
+int cells_reorder(pm_ctx* ctx, pm_map* m);
 /* pm_knn.cu: axis-aligned bounds of nodes4 into m->bounds (maps wrapped with pm_map_from_tree) */
 int map_bounds(pm_ctx* ctx, pm_map* m);
 /* pm_knn.cu: fused kNN + radiance estimate on device pointers (used by pm_gather and pm_render).

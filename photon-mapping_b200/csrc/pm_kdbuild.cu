@@ -640,6 +640,35 @@ int pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map*
   return PM_OK;
 }
 
+int pm_map_build_cells(pm_ctx* ctx, const pm_photon44* photons, int64_t n, float cell_size, pm_map** out) {
+  PM_REQUIRE(ctx && out, "ctx/out is NULL");
+  *out = nullptr;
+  if (n < 1) return PM_OK;
+  PM_REQUIRE(photons, "photons is NULL");
+  PM_REQUIRE(n < (int64_t)1 << 30, "at most 2^30 photons per map");
+  PM_REQUIRE(cell_size > 0.f && cell_size < INFINITY, "cell_size must be positive and finite");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  pm_map* m = new pm_map();
+  m->ctx = ctx; m->device = ctx->device; m->n = n; m->cells_only = true;
+  if (pm::is_device_ptr(photons)) {
+    m->photons_dev = photons;
+  } else {
+    if (pm::map_alloc(&m->owned_photons, sizeof(pm_photon44) * (size_t)n, ctx->stream) != cudaSuccess) {
+      cudaGetLastError(); delete m; pm::set_error("pm_map_build_cells: out of device memory"); return PM_ERR_NOMEM;
+    }
+    cudaMemcpyAsync(m->owned_photons, photons, sizeof(pm_photon44) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
+    m->photons_dev = m->owned_photons;
+  }
+  int r = make_soa(ctx, m); /* input order: node id = input index; the split_dim byte is not used */
+  if (r == PM_OK) r = pm::map_bounds(ctx, m);
+  if (r == PM_OK) r = pm::grid_build(ctx, m, cell_size);
+  if (r == PM_OK) r = pm::cells_reorder(ctx, m);
+  if (r == PM_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) { pm::set_error("pm_map_build_cells: sync failed"); r = PM_ERR_CUDA; }
+  if (r != PM_OK) { pm_map_destroy(m); return r; }
+  *out = m;
+  return PM_OK;
+}
+
 void pm_map_destroy(pm_map* m) {
   if (!m) return;
   cudaSetDevice(m->device);

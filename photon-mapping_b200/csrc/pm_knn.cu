@@ -411,6 +411,7 @@ extern "C" {
 int pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int k, float cutoff_radius,
            int32_t* out_ids, float* out_dist2, float* out_r2) {
   PM_REQUIRE(ctx, "ctx is NULL");
+  PM_REQUIRE(!map || !map->cells_only, "this map was built by pm_map_build_cells (no kd-tree): fixed-radius gathers only");
   PM_REQUIRE(nq >= 0 && nq < ((int64_t)1 << 31), "nq out of range");
   PM_REQUIRE(k == 8 || k == 16 || k == 32 || k == 50 || k == 64, "k must be one of 8, 16, 32, 50, 64");
   if (nq == 0) return PM_OK;
@@ -449,6 +450,7 @@ int pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int
 int pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, int64_t nq, int k,
               float cutoff_radius, float* out_rgb) {
   PM_REQUIRE(ctx, "ctx is NULL");
+  PM_REQUIRE(!map || !map->cells_only, "this map was built by pm_map_build_cells (no kd-tree): fixed-radius gathers only");
   PM_REQUIRE(nq >= 0 && nq < ((int64_t)1 << 31), "nq out of range");
   PM_REQUIRE(k == 8 || k == 16 || k == 32 || k == 50 || k == 64, "k must be one of 8, 16, 32, 50, 64");
   if (nq == 0) return PM_OK;

@@ -261,6 +261,8 @@ int pm_render(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_
               const pm_map* caustic_map, const pm_camera* camera, int width, int height, int spp, int depth,
               const float sky[3], int64_t pixel_begin, int64_t pixel_end, uint32_t* fb) {
   PM_REQUIRE(ctx && scene && camera && sky && fb, "ctx/scene/camera/sky/fb is NULL");
+  PM_REQUIRE((!global_map || !global_map->cells_only) && (!caustic_map || !caustic_map->cells_only),
+             "maps built by pm_map_build_cells carry no kd-tree: fixed-radius gathers only");
   PM_REQUIRE(width > 0 && height > 0 && (int64_t)width * height < ((int64_t)1 << 31), "bad framebuffer size");
   PM_REQUIRE(spp >= 1 && depth >= 0, "bad spp/depth");
   PM_REQUIRE(n_lights >= 0 && n_lights <= kMaxLights && (n_lights == 0 || lights), "bad lights");

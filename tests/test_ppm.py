@@ -74,3 +74,49 @@ def test_device_resident_loop_equals_host_loop(pkg, ctx):
     assert np.array_equal(dev["N"], host["N"]) and np.array_equal(dev["r2"], host["r2"])
     assert np.array_equal(dev["tau"], host["tau"]) and np.array_equal(dev["radiance"], host["radiance"])
     assert len(stats) == passes and all(s["stored"] > 0 for s in stats) and dev["emitted"] == passes * per_pass
+
+
+@pytest.mark.gpu
+def test_cells_only_map_counts_and_rejects_knn(pkg, ctx, orc):
+    """pm_map_build_cells: fixed-radius gathers from a map without a kd-tree — counts exact and flux within 1e-4 of the
+    brute-force oracle for radii from a fraction of a cell to the whole cloud (blocks grow to the whole grid); kNN
+    entry points refuse the map; the progressive loop on cells-only maps reproduces N and r² of the kd-tree loop."""
+    from helpers import unique_cloud
+
+    n, nq = 30000, 1500
+    cloud = unique_cloud(n, 21)
+    ext = n * 2.0**-8
+    rng = np.random.default_rng(6)
+    q = (rng.random((nq, 3), dtype=np.float32) * np.float32(1.2 * ext) - np.float32(0.1 * ext)).astype(np.float32)
+    brdf = (rng.random(nq, dtype=np.float32) * 0.9 + 0.1).astype(np.float32)
+    brdf[::13] = 0.0
+    gap = ext / n ** (1 / 3)
+    r2 = ((rng.random(nq, dtype=np.float32) * 6.0 + 0.2) * np.float32(gap)) ** 2
+    r2[::97] = np.float32(4 * ext * ext)  # the whole cloud
+    want_f = np.zeros((nq, 3), np.float32)
+    want_c = np.zeros(nq, np.int32)
+    orc.orc_gather_radius.argtypes = [c_void_p, ctypes.c_int, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]
+    orc.orc_gather_radius(vp(cloud), n, vp(q), vp(brdf), vp(r2), nq, vp(want_f), vp(want_c))
+    for cell in (0.7 * gap, 3.0 * gap):
+        m = pkg.PhotonMap.build_cells(ctx, cloud, float(cell))
+        flux, cnt = m.gather_radius(q, brdf, r2)
+        assert np.array_equal(cnt, want_c) and want_c.max() == n
+        assert np.allclose(flux, want_f, rtol=1e-4, atol=1e-6)
+        with pytest.raises(pkg.PmError):
+            m.knn(q, 8)
+        with pytest.raises(pkg.PmError):
+            m.gather(q, brdf, 8)
+        m.close()
+    with pytest.raises(pkg.PmError):
+        pkg.PhotonMap.build_cells(ctx, cloud, 0.0)
+
+    ppm = graft.load_package_module("ppm")
+    sc = load_scene("cornell_box")
+    scene = pkg.Scene(ctx, sc["verts"], sc["tris"], sc["tri_mesh"], sc["mats"])
+    W, H = 64, 40
+    cam = pkg.make_camera((80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87, W, H)
+    a = ppm.progressive_render_device(pkg, ctx, scene, sc["tri_mesh"], sc["mats"], sc["lights"], cam, W, H, 4, 30000, 2.5, 0.7, 6, seed=9)
+    b = ppm.progressive_render_device(pkg, ctx, scene, sc["tri_mesh"], sc["mats"], sc["lights"], cam, W, H, 4, 30000, 2.5, 0.7, 6, seed=9,
+                                      cells=True)
+    assert np.array_equal(a["N"], b["N"]) and np.array_equal(a["r2"], b["r2"])
+    assert np.allclose(a["tau"], b["tau"], rtol=2e-4, atol=1e-6)

@@ -4,7 +4,7 @@
 (ppm.progressive_render_device). One process per GPU: every pass's photons are sharded by launch index, hit points
 are replicated, one NCCL all-reduce of (flux.rgb, count) per pass.
 
-  python tools/c5_run.py [passes] [photons_per_pass] [W] [H] [r0]
+  python tools/c5_run.py [passes] [photons_per_pass] [W] [H] [r0] [cells|tree]
   torchrun --nnodes=1 --nproc-per-node G --master-addr 127.0.0.1 --master-port 29512 tools/c5_run.py ...
 
 No reference implementation exists; the parity tests are tests/test_ppm.py. Checked here:
@@ -31,6 +31,7 @@ per_pass = int(sys.argv[2]) if len(sys.argv) > 2 else 15_625_000
 W = int(sys.argv[3]) if len(sys.argv) > 3 else 3840
 H = int(sys.argv[4]) if len(sys.argv) > 4 else 2160
 r0 = float(sys.argv[5]) if len(sys.argv) > 5 else 0.5
+cells = (sys.argv[6] != "tree") if len(sys.argv) > 6 else True  # per-pass map: cells-only (default) or the kd-tree map
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 group = None
@@ -48,17 +49,18 @@ mats = z["mats"].view(pkg.MATERIAL).reshape(-1)
 scene = pkg.Scene(ctx, z["verts"], z["tris"], z["tri_mesh"], mats)
 lights = z["lights"].view(pkg.LIGHT).reshape(-1)
 alpha, depth = 0.7, 8
-res = {"ranks": world, "fb": [W, H], "passes": passes, "photons_per_pass": per_pass, "r0": r0, "alpha": alpha, "max_depth": depth}
+res = {"ranks": world, "fb": [W, H], "passes": passes, "photons_per_pass": per_pass, "r0": r0, "alpha": alpha, "max_depth": depth,
+       "per_pass_map": "cells-only (pm_map_build_cells)" if cells else "kd-tree (pm_map_build)"}
 
 
 def run(w, h, n_pass, n_photons, radius, sharded, stats=None):
     cam = pkg.make_camera((80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87, w, h)
     if sharded or world == 1:
         return ppm.progressive_render_device(pkg, ctx, scene, z["tri_mesh"], mats, lights, cam, w, h, n_pass, n_photons, radius, alpha,
-                                             depth, seed=1, stats=stats)
+                                             depth, seed=1, stats=stats, cells=cells, cell_fraction=float(os.environ.get('PM_PPM_CELL_FRAC', '0.2')))
     # unsharded on this rank although a process group exists: a one-rank group of our own
     return ppm.progressive_render_device(pkg, ctx, scene, z["tri_mesh"], mats, lights, cam, w, h, n_pass, n_photons, radius, alpha,
-                                         depth, seed=1, stats=stats, group=solo)
+                                         depth, seed=1, stats=stats, group=solo, cells=cells, cell_fraction=float(os.environ.get('PM_PPM_CELL_FRAC', '0.2')))
 
 
 if world > 1:
@@ -110,7 +112,7 @@ res.update({
 })
 if rank == 0:
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    json.dump(res, open(os.path.join(ROOT, "gpurun_out", f"c5_run_{world}gpu.json"), "w"), indent=1)
+    json.dump(res, open(os.path.join(ROOT, "gpurun_out", f"c5_run_{world}gpu{'' if cells else '_tree'}.json"), "w"), indent=1)
     print(json.dumps(res))
 if world > 1:
     dist.barrier()
