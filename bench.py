@@ -209,6 +209,24 @@ def run_stage_extras(pkg, ctx):
     out["c1_render"] = {"photons_global_map": int(len(g44)), "photons_caustic_map": int(len(c44)), "k": 50, "fb": [W, H],
                         "maps_build_ms": build_ms, "render_ms": 1e3 * best[0], "global_gather_kernel_ms": best[1],
                         "gather_queries_issued_upper_bound": queries, "pixels_per_s": W * H / best[0]}
+    # ---- C5-like: fixed-radius progressive passes, device resident (ppm.progressive_render_device), a quarter of the
+    #      C5 frame and of its photons per pass; tools/c5_run.py runs the full configuration ------------------
+    import __graft_entry__ as graft
+
+    ppm = graft.load_package_module("ppm")
+    PW, PH, passes, per_pass = 1920, 1080, 8, 3_906_250
+    pcam = pkg.make_camera((80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87, PW, PH)
+    stats = []
+    res5 = ppm.progressive_render_device(pkg, ctx, scene, z["tri_mesh"], mats, lights, pcam, PW, PH, passes, per_pass, 0.5, 0.7, 8,
+                                         seed=1, stats=stats, cells=True)
+    warm = stats[2:]  # the first passes grow the context's scratch and the allocator pool
+    pass_ms = float(np.mean([s["pass_ms"] for s in warm]))
+    out["c5_progressive_quarter"] = {
+        "fb": [PW, PH], "passes": passes, "cast_photons_per_pass": per_pass, "r0": 0.5, "alpha": 0.7,
+        "stored_photons_per_pass": float(np.mean([s["stored"] for s in warm])), "pass_ms": pass_ms,
+        "emit_ms": float(np.mean([s["emit_ms"] for s in warm])), "cells_map_ms": float(np.mean([s["convert_build_ms"] for s in warm])),
+        "gather_ms": float(np.mean([s["gather_ms"] for s in warm])), "gather_kernels_ms": float(np.mean([s["gather_kernels_ms"] for s in warm])),
+        "cast_photons_per_s": per_pass / (pass_ms * 1e-3), "mean_photons_per_hit_point": float(res5["N"][res5["N"] > 0].mean() / 0.7 / passes)}
     return out
 
 
