@@ -81,6 +81,56 @@ def allgather_photons(local_records, local_keys, group=None, device=None):
     return rec[order], key[order]
 
 
+def exchange_photons(rec, key, group=None, timing: dict | None = None):
+    """The path's one collective for tensors that stay where they are (HBM under NCCL, host memory under gloo): counts,
+    then ONE all_gather_into_tensor each for the padded 40-byte records and the 64-bit keys, then a sort by key — the
+    single-GPU order — with the records permuted as five 8-byte columns. `rec`: uint8 [n, 40], `key`: int64 [n].
+    Returns (records uint8 [N, 40], keys int64 [N], per-rank counts); `timing` receives the collective's device
+    milliseconds (CUDA tensors only) and the padded per-rank capacity."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    dev = rec.device
+    rec, key = rec.reshape(-1, PHOTON40_BYTES), key.reshape(-1)
+    n = torch.tensor([rec.shape[0]], dtype=torch.int64, device=dev)
+    counts = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(counts, n, group=group)
+    counts = counts.tolist()
+    cap = max(max(counts), 1)
+    # records travel as five int64 columns (40 bytes, 8-byte aligned): flat 1-D int64 buffers suit every backend
+    pad_rec = torch.zeros(cap * 5, dtype=torch.int64, device=dev)
+    pad_key = torch.zeros(cap, dtype=torch.int64, device=dev)
+    pad_rec[: rec.shape[0] * 5] = rec.contiguous().view(torch.int64).reshape(-1)
+    pad_key[: key.shape[0]] = key
+    all_rec = torch.empty(world * cap * 5, dtype=torch.int64, device=dev)
+    all_key = torch.empty(world * cap, dtype=torch.int64, device=dev)
+    ev = None
+    if dev.type == "cuda":
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record()
+    dist.all_gather_into_tensor(all_rec, pad_rec, group=group)
+    dist.all_gather_into_tensor(all_key, pad_key, group=group)
+    if ev:
+        ev[1].record()
+    del pad_rec, pad_key
+    all_rec, all_key = all_rec.view(world, cap, 5), all_key.view(world, cap)
+    keys = torch.cat([all_key[r, :c] for r, c in enumerate(counts)])
+    del all_key
+    # keys are < 2^63 (light < 128), so the signed order equals the unsigned one
+    order = torch.sort(keys, stable=True).indices
+    keys = keys[order]
+    recs = torch.cat([all_rec[r, :c] for r, c in enumerate(counts)])
+    del all_rec
+    recs = recs[order].view(torch.uint8).view(-1, PHOTON40_BYTES)
+    if timing is not None:
+        timing["padded_capacity"] = cap
+        if ev:
+            torch.cuda.synchronize()
+            timing["all_gather_ms"] = ev[0].elapsed_time(ev[1])
+    return recs, keys, counts
+
+
 def emit_sharded(pkg, scene, lights, casted: int, max_depth: int, caustics: bool, seed: int = 0, rng_mode: int = 0,
                  group=None, device=None):
     """Stage 1 over all ranks + the exchange. Returns the full PHOTON40 numpy array (replicated, single-GPU order)."""

@@ -72,6 +72,16 @@ def _worker(rank, world, port, sizes, out_dir):
     all_rec, all_keys = mg.allgather_photons(torch.from_numpy(rec.copy()).reshape(-1), torch.from_numpy(keys.view(np.int64).copy()))
     np.save(os.path.join(out_dir, f"rec{rank}.npy"), all_rec.numpy())
     np.save(os.path.join(out_dir, f"key{rank}.npy"), all_keys.numpy())
+    # the tensor-resident exchange (what tools/c4_run.py runs over NCCL) gives the same array
+    x_rec, x_keys, counts = mg.exchange_photons(torch.from_numpy(rec.copy()), torch.from_numpy(keys.view(np.int64).copy()))
+    assert torch.equal(x_rec, all_rec.reshape(-1, 40)) and torch.equal(x_keys, all_keys) and counts[rank] == len(keys)
+    # progressive mode: one sum of (flux.rgb, count) per pass over disjoint photon shards
+    ppm = graft.load_package_module("ppm")
+    rng = np.random.default_rng(100 + rank)
+    flux = rng.random((50, 3), dtype=np.float32)
+    count = rng.integers(0, 2000, 50).astype(np.int32)
+    f_sum, c_sum = ppm._allreduce(flux, count, None, None)
+    np.save(os.path.join(out_dir, f"ppm{rank}.npy"), np.concatenate([f_sum, c_sum[:, None].astype(np.float32)], axis=1))
     # stage 3: disjoint pixel ranges merged by a sum
     W, H = 37, 11
     b, e = mg.shard_range(W * H, rank, world)
@@ -99,3 +109,13 @@ def test_gloo_world2_allgather_and_tiles(tmp_path):
         assert np.array_equal(np.load(tmp_path / f"rec{r}.npy"), full_rec)
         want = (np.arange(37 * 11) * 2654435761) % (2**32)
         assert np.array_equal(np.load(tmp_path / f"fb{r}.npy"), want)
+    parts = [np.random.default_rng(100 + r) for r in range(world)]
+    flux = sum(g.random((50, 3), dtype=np.float32).astype(np.float64) for g in parts)
+    parts = [np.random.default_rng(100 + r) for r in range(world)]
+    count = 0
+    for g in parts:
+        g.random((50, 3), dtype=np.float32)
+        count = count + g.integers(0, 2000, 50)
+    for r in range(world):
+        got = np.load(tmp_path / f"ppm{r}.npy")
+        assert np.array_equal(got[:, 3], count.astype(np.float32)) and np.allclose(got[:, :3], flux, rtol=1e-6)

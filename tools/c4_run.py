@@ -92,34 +92,11 @@ def emit_shard(scene, lights, casted, depth, first, stride, cap):
 
 
 def exchange(rec, key):
-    """The path's one collective: counts, then padded records and keys; key sort = single-GPU order."""
-    n = torch.tensor([rec.shape[0]], dtype=torch.int64, device=dev)
-    counts = torch.empty(world, dtype=torch.int64, device=dev)
-    dist.all_gather_into_tensor(counts, n)
-    counts = counts.tolist()
-    cap = max(max(counts), 1)
-    pad_rec = torch.zeros((cap, 40), dtype=torch.uint8, device=dev)
-    pad_key = torch.zeros(cap, dtype=torch.int64, device=dev)
-    pad_rec[: rec.shape[0]] = rec
-    pad_key[: key.shape[0]] = key
-    all_rec = torch.empty((world, cap, 40), dtype=torch.uint8, device=dev)
-    all_key = torch.empty((world, cap), dtype=torch.int64, device=dev)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    dist.all_gather_into_tensor(all_rec, pad_rec)
-    dist.all_gather_into_tensor(all_key, pad_key)
-    e1.record()
-    del pad_rec, pad_key
-    keys = torch.cat([all_key[r, :c] for r, c in enumerate(counts)])
-    del all_key
-    order = torch.sort(keys, stable=True).indices
-    keys = keys[order]
-    # permute the 40-byte rows as five 8-byte columns (records are 8-byte aligned)
-    recs = torch.cat([all_rec[r, :c] for r, c in enumerate(counts)]).view(torch.int64).view(-1, 5)
-    del all_rec
-    recs = recs[order].view(torch.uint8).view(-1, 40)
+    """multigpu.exchange_photons + its timing: (records, keys, counts, all_gather ms, padded capacity)."""
+    tm = {}
+    recs, keys, counts = mg.exchange_photons(rec, key, timing=tm)
     torch.cuda.synchronize()
-    return recs, keys, counts, e0.elapsed_time(e1), cap
+    return recs, keys, counts, tm["all_gather_ms"], tm["padded_capacity"]
 
 
 def checksum(t: torch.Tensor) -> int:
