@@ -191,6 +191,18 @@ int  pm_photons_to_maps(pm_ctx* ctx, const pm_photon40* global_in, int64_t n_glo
  * (builder_thrust.h:441). photons may be host or device memory. The map keeps a pointer to
  * `photons` only if it is device memory; otherwise it owns a device copy. */
 int  pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n, float* bounds_host, pm_map** out);
+/* Sharded build of the SAME tree over `world` (a power of two) GPUs that all hold the same photons[0..n) (after the
+ * all-gather of SURVEY §8e): the first log2(world) levels are computed by everybody, below them rank r continues only
+ * inside subtree (world - 1) + r. pm_map_build_shard fills node_elem[n] / node_dim[n] (device memory of the caller:
+ * input index and split axis of every tree node) with this rank's part and ZERO elsewhere (the common top levels
+ * are rank 0's part); the caller sums the tables over the ranks (one all-reduce each, viewing node_dim as bytes
+ * padded to int32) and hands them to pm_map_build_finish, which reorders photons in place, fills split_dim and
+ * returns the map — byte-identical to pm_map_build's. photons is not modified by pm_map_build_shard. Trees too small
+ * to shard are built whole on every rank (same calling sequence). world == 1 equals pm_map_build. */
+int  pm_map_build_shard(pm_ctx* ctx, const pm_photon44* photons_dev, int64_t n, int rank, int world,
+                        int32_t* node_elem_dev, uint8_t* node_dim_dev, float* bounds_host);
+int  pm_map_build_finish(pm_ctx* ctx, pm_photon44* photons_dev, int64_t n, const int32_t* node_elem_dev,
+                         const uint8_t* node_dim_dev, const float* bounds_host, pm_map** out);
 /* Wrap an array that is ALREADY in tree order (e.g. built by the reference builder). */
 int  pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map** out);
 /* Cells-only map for fixed-radius gathers (progressive mode, BASELINE configs[4]; no reference counterpart): the

@@ -76,6 +76,8 @@ _SIGNATURES = {
     "pm_photons_to_maps": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "pm_map_build": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, POINTER(c_void_p)]),
     "pm_map_from_tree": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_void_p)]),
+    "pm_map_build_shard": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "pm_map_build_finish": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, POINTER(c_void_p)]),
     "pm_map_build_cells": (c_int, [c_void_p, c_void_p, c_int64, c_float, POINTER(c_void_p)]),
     "pm_map_destroy": (None, [c_void_p]),
     "pm_map_size": (c_int64, [c_void_p]),
@@ -216,6 +218,28 @@ class PhotonMap:
         h = c_void_p()
         _check(lib().pm_map_from_tree(ctx.handle, _ptr(photons), n, ctypes.byref(h)))
         return cls(ctx, h, n, None, photons)
+
+    @classmethod
+    def build_sharded(cls, ctx: Context, photons, rank: int, world: int, reduce_sum) -> "PhotonMap":
+        """pm_map_build_shard + pm_map_build_finish. photons: CUDA torch tensor of n*44 bytes, identical on every rank
+        (reordered in place); `reduce_sum(t)` sums an int32 CUDA tensor over the ranks in place (e.g.
+        ``lambda t: dist.all_reduce(t)``). The map and the array equal PhotonMap.build's byte for byte."""
+        import torch
+
+        n = _count(photons, 44)
+        elem = torch.empty(n, dtype=torch.int32, device=photons.device)
+        dim = torch.zeros((n + 3) // 4 * 4, dtype=torch.uint8, device=photons.device)
+        bounds = np.zeros(6, np.float32)
+        _check(lib().pm_map_build_shard(ctx.handle, _ptr(photons), n, rank, world, elem.data_ptr(), dim.data_ptr(),
+                                        bounds.ctypes.data))
+        if world > 1:
+            reduce_sum(elem)
+            reduce_sum(dim.view(torch.int32))  # one rank contributes each byte: no carries
+            torch.cuda.synchronize(photons.device)
+        h = c_void_p()
+        _check(lib().pm_map_build_finish(ctx.handle, _ptr(photons), n, elem.data_ptr(), dim.data_ptr(), bounds.ctypes.data,
+                                         ctypes.byref(h)))
+        return cls(ctx, h, n, bounds, photons)
 
     @classmethod
     def build_cells(cls, ctx: Context, photons, cell_size: float) -> "PhotonMap":

@@ -87,13 +87,14 @@ struct SegRec {
 };
 
 /* one thread per subtree of the current level: choose dim + pivot, emit the node, derive children */
-__global__ void k_split(int level_first, int level_count, int n, const int* __restrict__ ord0,
+__global__ void k_split(int level_first, int j0, int level_count, int n, const int* __restrict__ ord0,
                         const int* __restrict__ ord1, const int* __restrict__ ord2, const float* __restrict__ c0,
                         const float* __restrict__ c1, const float* __restrict__ c2,
                         const float* __restrict__ box_cur, const int* __restrict__ begin_cur,
                         float* __restrict__ box_next, int* __restrict__ begin_next, SegRec* __restrict__ seg_rec,
                         int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  /* subtrees [j0, level_count) of the level: a rank of a sharded build owns a contiguous range of them */
+  const int j = j0 + blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= level_count) return;
   const int s = level_first + j;
   float box[6];
@@ -150,7 +151,7 @@ __device__ inline uint64_t tile_to_global(uint64_t x) { /* 4 x 11-bit tile-local
 }
 
 __global__ void __launch_bounds__(kTile, 4)
-k_level(int n, int level_first, const int* __restrict__ seg_of_pos, const SegRec* __restrict__ seg_rec,
+k_level(int n, int pos_lo, int pos_hi, int tile0, int level_first, const int* __restrict__ seg_of_pos, const SegRec* __restrict__ seg_rec,
         const int* __restrict__ in0, const int* __restrict__ in1, const int* __restrict__ in2,
         const float* __restrict__ c0, const float* __restrict__ c1, const float* __restrict__ c2,
         int* __restrict__ out0, int* __restrict__ out1, int* __restrict__ out2, int* __restrict__ seg_next,
@@ -162,14 +163,17 @@ k_level(int n, int level_first, const int* __restrict__ seg_of_pos, const SegRec
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   if (tid == 0) { tile_sh = (int)atomicAdd(ticket, 1u); last_head_sh = -1; }
   __syncthreads();
+  /* a sharded build passes only over [pos_lo, pos_hi) — the range of the rank's own subtree, which starts with a
+   * range begin, so its first tile never looks back; positions outside are other ranks' and count as dead */
   const int tile = tile_sh;
-  const int tile_base = tile * kTile;
+  const int tile_base = (tile0 + tile) * kTile;
   const int i = tile_base + tid;
 
   int s = kDead, begin = 0, pivot = 0, dim = 0;
   int e0 = 0, e1 = 0, e2 = 0;
   uint32_t sd_a = 2u, sd_b = 2u, pos = 2u; /* sides of the element in slot 0 / slot 1 / the split-axis list */
-  if (i < n) { s = seg_of_pos[i]; e0 = in0[i]; e1 = in1[i]; e2 = in2[i]; }
+  const bool mine = i >= pos_lo && i < pos_hi;
+  if (mine) { s = seg_of_pos[i]; e0 = in0[i]; e1 = in1[i]; e2 = in2[i]; }
   const bool live = s != kDead;
   uint64_t f = 0ull;
   if (live) {
@@ -185,7 +189,7 @@ k_level(int n, int level_first, const int* __restrict__ seg_of_pos, const SegRec
     pos = i < pivot ? 0u : (i > pivot ? 1u : 2u);
     seg_next[i] = pos == 0u ? 2 * s + 1 : (pos == 1u ? 2 * s + 2 : kDead);
     f = (sd_a == 0u ? 1ull : (sd_a == 2u ? 1ull << 11 : 0ull)) + (sd_b == 0u ? 1ull << 22 : (sd_b == 2u ? 1ull << 33 : 0ull));
-  } else if (i < n) {
+  } else if (mine) {
     seg_next[i] = kDead;
   }
   const bool head = !live || i == begin;
@@ -298,7 +302,7 @@ struct LocalSmem {
 };
 
 __global__ void __launch_bounds__(kLocalThreads)
-k_finish_subtrees(int level_first, int level_count, int n, const int* __restrict__ ord0, const int* __restrict__ ord1,
+k_finish_subtrees(int level_first, int j0, int level_count, int n, const int* __restrict__ ord0, const int* __restrict__ ord1,
                   const int* __restrict__ ord2, const float* __restrict__ cx, const float* __restrict__ cy,
                   const float* __restrict__ cz, const float* __restrict__ box_cur, const int* __restrict__ begin_cur,
                   int* __restrict__ local_of, int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
@@ -306,7 +310,7 @@ k_finish_subtrees(int level_first, int level_count, int n, const int* __restrict
   LocalSmem& sm = *reinterpret_cast<LocalSmem*>(smem_raw);
   using Scan = cub::BlockScan<uint64_t, kLocalThreads>;
   __shared__ typename Scan::TempStorage scan_tmp;
-  const int j = blockIdx.x;
+  const int j = j0 + blockIdx.x;
   if (j >= level_count) return;
   const int s0 = level_first + j;
   const int begin0 = begin_cur[j];
@@ -483,6 +487,133 @@ int make_soa(pm_ctx* ctx, pm_map* m) {
 
 extern "C" {
 
+/* Sorts + level passes: fills the node tables (element and split axis of every node) from the unsorted records in
+ * `src`. world > 1: a sharded build — the first log2(world) levels run on everything (replicated on every rank), below
+ * them this rank continues only inside subtree (2^S - 1) + rank; table entries of other ranks' subtrees stay zero,
+ * and only rank 0 keeps the replicated top levels, so that a SUM over ranks yields the complete tables. */
+static int build_nodes(pm_ctx* ctx, const pm_photon44* src, int n, int rank, int world, int** elem_out, uint8_t** dim_out,
+                       float** bounds_dev_out) {
+  cudaStream_t st = ctx->stream;
+  float *cx, *cy, *cz; uint32_t *keys_in, *keys_out; int *iota;
+  int* ord[2][3];
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD1, (size_t)n, &cx));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD2, (size_t)n, &cy));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD3, (size_t)n, &cz));
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)n * 3, &keys_in));
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)n, &keys_out));
+  PM_CHECK(ctx->get_scratch(pm::S_VALS0, (size_t)n, &iota));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD4, (size_t)n * 3, &ord[0][0]));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD5, (size_t)n * 3, &ord[1][0]));
+  for (int b = 0; b < 2; b++) { ord[b][1] = ord[b][0] + n; ord[b][2] = ord[b][0] + 2 * (size_t)n; }
+
+  const unsigned nb256 = (unsigned)pm::div_up(n, 256);
+  k_extract<<<nb256, 256, 0, st>>>(src, n, cx, cy, cz, keys_in, keys_in + n, keys_in + 2 * (size_t)n, iota);
+  ctx->launches++;
+
+  /* three stable LSD radix sorts: ties keep ascending element index */
+  size_t cub_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys_in, keys_out, iota, ord[0][0], n, 0, 32, st);
+  void* cub_tmp = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_CUB, cub_bytes, &cub_tmp));
+  const size_t cub_cap = cub_bytes;
+  for (int d = 0; d < 3; d++) {
+    size_t tb = cub_cap;
+    PM_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp, tb, keys_in + (size_t)d * n, keys_out, iota, ord[0][d], n, 0, 32, st));
+    ctx->launches += 5;
+  }
+
+  /* per-level state */
+  const int num_levels = 32 - __builtin_clz((unsigned)n);  /* floor(log2 n) + 1 */
+  const int max_width = (n + 1) / 2 + 1;
+  const unsigned ntiles = (unsigned)pm::div_up(n, kTile);
+  const size_t status_words = (size_t)num_levels * ntiles + 64; /* per-level tile status words, then the tickets */
+  float* box[2]; int* begin[2]; int *seg[2], *elem_of_node, *local_of; uint8_t* dim_of_node; SegRec* seg_rec;
+  unsigned long long* status;
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD6, (size_t)max_width * 6, &box[0]));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD7, (size_t)max_width * 6, &box[1]));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD8, (size_t)max_width, &begin[0]));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD9, (size_t)max_width, &begin[1]));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD10, (size_t)n, &local_of));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD11, (size_t)n * 2, &seg[0]));
+  seg[1] = seg[0] + n;
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD12, (size_t)n, &elem_of_node));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD13, (size_t)n + 4, &dim_of_node));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD16, (size_t)max_width, &seg_rec));
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD14, status_words, &status));
+  float* bounds_dev = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_BUILD15, (size_t)8, &bounds_dev));
+
+  k_root<<<1, 32, 0, st>>>(ord[0][0], ord[0][1], ord[0][2], cx, cy, cz, n, box[0], begin[0], bounds_dev);
+  ctx->launches++;
+  PM_CUDA(cudaMemsetAsync(seg[0], 0, sizeof(int) * (size_t)n, st)); /* everything starts in subtree 0 */
+
+  unsigned int* tickets = reinterpret_cast<unsigned int*>(status + (size_t)num_levels * ntiles);
+  PM_CUDA(cudaMemsetAsync(status, 0, sizeof(unsigned long long) * status_words, st));
+
+  const int local_from = num_levels > kLocalLevels ? num_levels - kLocalLevels : 0; /* first level finished per CTA */
+  /* sharding: S replicated levels, then subtree (2^S - 1) + rank. Too small a tree is built whole by everybody. */
+  int S = 0;
+  while ((1 << S) < world) S++;
+  const bool sharded = world > 1 && (1 << S) == world && S < local_from && (int64_t)n >= ((int64_t)2 << S);
+  int pos_lo = 0, pos_hi = n;
+  if (sharded) {
+    PM_CUDA(cudaMemsetAsync(elem_of_node, 0, sizeof(int) * (size_t)n, st));
+    PM_CUDA(cudaMemsetAsync(dim_of_node, 0, (size_t)n + 4, st));
+    int64_t node = 0, b = 0; /* walk down to the rank's subtree: in-order ranges, pivot at begin + |left subtree| */
+    for (int l = 0; l < S; l++) {
+      const int64_t lc = 2 * node + 1;
+      const int64_t left = lc < n ? subtree_size(lc, n) : 0;
+      if ((rank >> (S - 1 - l)) & 1) { b = b + left + 1; node = lc + 1; } else { node = lc; }
+    }
+    pos_lo = (int)b;
+    pos_hi = (int)(b + subtree_size(node, n));
+  }
+  int cur = 0;
+  for (int L = 0; L < num_levels; L++) {
+    const int level_first = (1 << L) - 1;
+    const int level_count = (n - level_first < (1 << L)) ? n - level_first : (1 << L);
+    /* this rank's subtrees of the level: all of them above the split level, a contiguous share below */
+    int j0 = 0, j1 = level_count;
+    if (sharded && L >= S) {
+      j0 = std::min(level_count, rank << (L - S));
+      j1 = std::min(level_count, (rank + 1) << (L - S));
+    }
+    if (L == local_from) {
+      PM_CUDA(cudaFuncSetAttribute(k_finish_subtrees, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSmem)));
+      if (j1 > j0)
+        k_finish_subtrees<<<(unsigned)(j1 - j0), kLocalThreads, sizeof(LocalSmem), st>>>(
+            level_first, j0, j1, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
+            local_of, elem_of_node, dim_of_node);
+      ctx->launches++;
+      break;
+    }
+    if (j1 > j0)
+      k_split<<<(unsigned)pm::div_up(j1 - j0, 128), 128, 0, st>>>(
+          level_first, j0, j1, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
+          box[(L + 1) & 1], begin[(L + 1) & 1], seg_rec, elem_of_node, dim_of_node);
+    ctx->launches++;
+    if (L == num_levels - 1) break;
+    const bool part = sharded && L >= S;
+    const int lo = part ? pos_lo : 0, hi = part ? pos_hi : n;
+    const int tile0 = lo / kTile;
+    const unsigned tiles = (unsigned)(pm::div_up(hi, kTile) - tile0);
+    if (hi > lo)
+      k_level<<<tiles, kTile, 0, st>>>(n, lo, hi, tile0, level_first, seg[L & 1], seg_rec, ord[cur][0], ord[cur][1], ord[cur][2], cx,
+                                      cy, cz, ord[cur ^ 1][0], ord[cur ^ 1][1], ord[cur ^ 1][2], seg[(L + 1) & 1],
+                                      status + (size_t)L * ntiles, tickets + L);
+    ctx->launches++;
+    cur ^= 1;
+  }
+  if (sharded && rank != 0) { /* the replicated top levels are rank 0's contribution to the sum */
+    const size_t top = ((size_t)1 << S) - 1;
+    PM_CUDA(cudaMemsetAsync(elem_of_node, 0, sizeof(int) * top, st));
+    PM_CUDA(cudaMemsetAsync(dim_of_node, 0, top, st));
+  }
+  PM_CUDA(cudaGetLastError());
+  *elem_out = elem_of_node; *dim_out = dim_of_node; *bounds_dev_out = bounds_dev;
+  return PM_OK;
+}
+
 int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_host, pm_map** out) {
   PM_REQUIRE(ctx && out, "ctx/out is NULL");
   *out = nullptr;
@@ -514,87 +645,8 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   pm_photon44* src = nullptr;
   PM_B(ctx->get_scratch(pm::S_BUILD0, (size_t)n, &src));
   PM_BC(cudaMemcpyAsync(src, photons, sizeof(pm_photon44) * (size_t)n, dev_in ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
-
-  float *cx, *cy, *cz; uint32_t *keys_in, *keys_out; int *iota;
-  int* ord[2][3];
-  PM_B(ctx->get_scratch(pm::S_BUILD1, (size_t)n, &cx));
-  PM_B(ctx->get_scratch(pm::S_BUILD2, (size_t)n, &cy));
-  PM_B(ctx->get_scratch(pm::S_BUILD3, (size_t)n, &cz));
-  PM_B(ctx->get_scratch(pm::S_KEYS0, (size_t)n * 3, &keys_in));
-  PM_B(ctx->get_scratch(pm::S_KEYS1, (size_t)n, &keys_out));
-  PM_B(ctx->get_scratch(pm::S_VALS0, (size_t)n, &iota));
-  PM_B(ctx->get_scratch(pm::S_BUILD4, (size_t)n * 3, &ord[0][0]));
-  PM_B(ctx->get_scratch(pm::S_BUILD5, (size_t)n * 3, &ord[1][0]));
-  for (int b = 0; b < 2; b++) { ord[b][1] = ord[b][0] + n; ord[b][2] = ord[b][0] + 2 * (size_t)n; }
-
-  const unsigned nb256 = (unsigned)pm::div_up(n, 256);
-  k_extract<<<nb256, 256, 0, st>>>(src, n, cx, cy, cz, keys_in, keys_in + n, keys_in + 2 * (size_t)n, iota);
-  ctx->launches++;
-
-  /* three stable LSD radix sorts: ties keep ascending element index */
-  size_t cub_bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys_in, keys_out, iota, ord[0][0], n, 0, 32, st);
-  void* cub_tmp = nullptr;
-  PM_B(ctx->get_scratch(pm::S_CUB, cub_bytes, &cub_tmp));
-  const size_t cub_cap = cub_bytes;
-  for (int d = 0; d < 3; d++) {
-    size_t tb = cub_cap;
-    PM_BC(cub::DeviceRadixSort::SortPairs(cub_tmp, tb, keys_in + (size_t)d * n, keys_out, iota, ord[0][d], n, 0, 32, st));
-    ctx->launches += 5;
-  }
-
-  /* per-level state */
-  const int num_levels = 32 - __builtin_clz((unsigned)n);  /* floor(log2 n) + 1 */
-  const int max_width = (n + 1) / 2 + 1;
-  const unsigned ntiles = (unsigned)pm::div_up(n, kTile);
-  const size_t status_words = (size_t)num_levels * ntiles + 64; /* per-level tile status words, then the tickets */
-  float* box[2]; int* begin[2]; int *seg[2], *elem_of_node, *local_of; uint8_t* dim_of_node; SegRec* seg_rec;
-  unsigned long long* status;
-  PM_B(ctx->get_scratch(pm::S_BUILD6, (size_t)max_width * 6, &box[0]));
-  PM_B(ctx->get_scratch(pm::S_BUILD7, (size_t)max_width * 6, &box[1]));
-  PM_B(ctx->get_scratch(pm::S_BUILD8, (size_t)max_width, &begin[0]));
-  PM_B(ctx->get_scratch(pm::S_BUILD9, (size_t)max_width, &begin[1]));
-  PM_B(ctx->get_scratch(pm::S_BUILD10, (size_t)n, &local_of));
-  PM_B(ctx->get_scratch(pm::S_BUILD11, (size_t)n * 2, &seg[0]));
-  seg[1] = seg[0] + n;
-  PM_B(ctx->get_scratch(pm::S_BUILD12, (size_t)n, &elem_of_node));
-  PM_B(ctx->get_scratch(pm::S_BUILD13, (size_t)n, &dim_of_node));
-  PM_B(ctx->get_scratch(pm::S_BUILD16, (size_t)max_width, &seg_rec));
-  PM_B(ctx->get_scratch(pm::S_BUILD14, status_words, &status));
-  float* bounds_dev = nullptr;
-  PM_B(ctx->get_scratch(pm::S_BUILD15, (size_t)8, &bounds_dev));
-
-  k_root<<<1, 32, 0, st>>>(ord[0][0], ord[0][1], ord[0][2], cx, cy, cz, n, box[0], begin[0], bounds_dev);
-  ctx->launches++;
-  PM_BC(cudaMemsetAsync(seg[0], 0, sizeof(int) * (size_t)n, st)); /* everything starts in subtree 0 */
-
-  unsigned int* tickets = reinterpret_cast<unsigned int*>(status + (size_t)num_levels * ntiles);
-  PM_BC(cudaMemsetAsync(status, 0, sizeof(unsigned long long) * status_words, st));
-
-  int cur = 0;
-  const int local_from = num_levels > kLocalLevels ? num_levels - kLocalLevels : 0; /* first level finished per CTA */
-  for (int L = 0; L < num_levels; L++) {
-    const int level_first = (1 << L) - 1;
-    const int level_count = (n - level_first < (1 << L)) ? n - level_first : (1 << L);
-    if (L == local_from) {
-      PM_BC(cudaFuncSetAttribute(k_finish_subtrees, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSmem)));
-      k_finish_subtrees<<<(unsigned)level_count, kLocalThreads, sizeof(LocalSmem), st>>>(
-          level_first, level_count, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
-          local_of, elem_of_node, dim_of_node);
-      ctx->launches++;
-      break;
-    }
-    k_split<<<(unsigned)pm::div_up(level_count, 128), 128, 0, st>>>(
-        level_first, level_count, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
-        box[(L + 1) & 1], begin[(L + 1) & 1], seg_rec, elem_of_node, dim_of_node);
-    ctx->launches++;
-    if (L == num_levels - 1) break;
-    k_level<<<ntiles, kTile, 0, st>>>(n, level_first, seg[L & 1], seg_rec, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz,
-                                      ord[cur ^ 1][0], ord[cur ^ 1][1], ord[cur ^ 1][2], seg[(L + 1) & 1],
-                                      status + (size_t)L * ntiles, tickets + L);
-    ctx->launches++;
-    cur ^= 1;
-  }
+  int* elem_of_node = nullptr; uint8_t* dim_of_node = nullptr; float* bounds_dev = nullptr;
+  PM_B(build_nodes(ctx, src, n, 0, 1, &elem_of_node, &dim_of_node, &bounds_dev));
 
   k_emit_nodes<<<(unsigned)pm::div_up((int64_t)n * 11, 256), 256, 0, st>>>(
       n, elem_of_node, dim_of_node, reinterpret_cast<const uint32_t*>(src), reinterpret_cast<uint32_t*>(tree));
@@ -605,6 +657,68 @@ int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_h
   if (!dev_in) PM_BC(cudaMemcpyAsync(photons, tree, sizeof(pm_photon44) * (size_t)n, cudaMemcpyDeviceToHost, st));
   PM_BC(cudaStreamSynchronize(st));
   if (bounds_host) memcpy(bounds_host, m->bounds, sizeof(float) * 6);
+  PM_B(pm::grid_build(ctx, m));
+  PM_BC(cudaStreamSynchronize(st));
+  *out = m;
+  return PM_OK;
+}
+
+/* ---- sharded build (multi-GPU): node tables per rank, summed by the caller, then the common tail ---- */
+int pm_map_build_shard(pm_ctx* ctx, const pm_photon44* photons, int64_t n64, int rank, int world, int32_t* node_elem,
+                       uint8_t* node_dim, float* bounds_host) {
+  PM_REQUIRE(ctx && photons && node_elem && node_dim, "ctx/photons/node_elem/node_dim is NULL");
+  PM_REQUIRE(n64 >= 1 && n64 < (int64_t)1 << 30, "1 <= n < 2^30 photons per map");
+  PM_REQUIRE(world >= 1 && rank >= 0 && rank < world && (world & (world - 1)) == 0, "world must be a power of two, 0 <= rank < world");
+  PM_REQUIRE(pm::is_device_ptr(photons) && pm::is_device_ptr(node_elem) && pm::is_device_ptr(node_dim),
+             "photons / node_elem / node_dim must be device memory");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  const int n = (int)n64;
+  cudaStream_t st = ctx->stream;
+  int* elem = nullptr; uint8_t* dim = nullptr; float* bounds_dev = nullptr;
+  PM_CHECK(build_nodes(ctx, photons, n, rank, world, &elem, &dim, &bounds_dev));
+  /* a tree too small to shard was built whole: keep rank 0's copy only, so that the sum still is the table */
+  int S = 0;
+  while ((1 << S) < world) S++;
+  const int num_levels = 32 - __builtin_clz((unsigned)n);
+  const int local_from = num_levels > kLocalLevels ? num_levels - kLocalLevels : 0;
+  const bool sharded = world > 1 && S < local_from && n64 >= ((int64_t)2 << S);
+  if (world > 1 && !sharded && rank != 0) {
+    PM_CUDA(cudaMemsetAsync(node_elem, 0, sizeof(int32_t) * (size_t)n, st));
+    PM_CUDA(cudaMemsetAsync(node_dim, 0, (size_t)n, st));
+  } else {
+    PM_CUDA(cudaMemcpyAsync(node_elem, elem, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+    PM_CUDA(cudaMemcpyAsync(node_dim, dim, (size_t)n, cudaMemcpyDeviceToDevice, st));
+  }
+  float b[6];
+  PM_CUDA(cudaMemcpyAsync(b, bounds_dev, sizeof(float) * 6, cudaMemcpyDeviceToHost, st));
+  PM_CUDA(cudaStreamSynchronize(st));
+  if (bounds_host) memcpy(bounds_host, b, sizeof(float) * 6);
+  return PM_OK;
+}
+
+int pm_map_build_finish(pm_ctx* ctx, pm_photon44* photons, int64_t n64, const int32_t* node_elem, const uint8_t* node_dim,
+                        const float* bounds_host, pm_map** out) {
+  PM_REQUIRE(ctx && out, "ctx/out is NULL");
+  *out = nullptr;
+  PM_REQUIRE(photons && node_elem && node_dim && bounds_host, "photons/node_elem/node_dim/bounds is NULL");
+  PM_REQUIRE(n64 >= 1 && n64 < (int64_t)1 << 30, "1 <= n < 2^30 photons per map");
+  PM_REQUIRE(pm::is_device_ptr(photons) && pm::is_device_ptr(node_elem) && pm::is_device_ptr(node_dim),
+             "photons / node_elem / node_dim must be device memory");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  const int n = (int)n64;
+  cudaStream_t st = ctx->stream;
+  pm_map* m = new pm_map();
+  m->ctx = ctx; m->device = ctx->device; m->n = n; m->photons_dev = photons;
+  pm_photon44* src = nullptr;
+  PM_B(ctx->get_scratch(pm::S_BUILD0, (size_t)n, &src));
+  PM_BC(cudaMemcpyAsync(src, photons, sizeof(pm_photon44) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+  k_emit_nodes<<<(unsigned)pm::div_up((int64_t)n * 11, 256), 256, 0, st>>>(
+      n, node_elem, node_dim, reinterpret_cast<const uint32_t*>(src), reinterpret_cast<uint32_t*>(photons));
+  ctx->launches++;
+  PM_BC(cudaGetLastError());
+  PM_B(make_soa(ctx, m));
+  memcpy(m->bounds, bounds_host, sizeof(float) * 6);
+  PM_BC(cudaStreamSynchronize(st));
   PM_B(pm::grid_build(ctx, m));
   PM_BC(cudaStreamSynchronize(st));
 #undef PM_B

@@ -180,13 +180,26 @@ torch.cuda.empty_cache()
 g44, conv_ms = timed(lambda: to_map(m_rec))
 del m_rec
 torch.cuda.empty_cache()  # the library allocates with cudaMalloc: hand torch's cached blocks back first
+def build(t):
+    """sharded build: levels below log2(world) split over the ranks, node tables summed with two NCCL all-reduces"""
+    if os.environ.get("PM_C4_BUILD", "sharded") == "replicated" or world & (world - 1):
+        return pkg.PhotonMap.build(ctx, t)
+    return pkg.PhotonMap.build_sharded(ctx, t, rank, world, lambda x: dist.all_reduce(x))
+
+
 b0 = None
 if g44.shape[0] <= 200_000_000:  # warm build on a copy (grows the context's scratch); skipped when memory is the concern
     g_copy = g44.clone()
-    gmap, b0 = timed(lambda: pkg.PhotonMap.build(ctx, g_copy))
+    gmap, b0 = timed(lambda: build(g_copy))
     del gmap, g_copy
-gmap, build_ms = timed(lambda: pkg.PhotonMap.build(ctx, g44))
-res["stage2_replicated"] = {"photons": int(g44.shape[0]), "to_maps_ms": conv_ms, "build_ms_first": b0, "build_ms": build_ms}
+gmap, build_ms = timed(lambda: build(g44))
+tree_sum = torch.tensor([checksum(g44)], dtype=torch.int64, device=dev)
+tree_sums = torch.empty(world, dtype=torch.int64, device=dev)
+dist.all_gather_into_tensor(tree_sums, tree_sum)
+res["stage2"] = {"photons": int(g44.shape[0]), "to_maps_ms": conv_ms, "build_ms_first": b0, "build_ms": build_ms,
+                 "mode": os.environ.get("PM_C4_BUILD", "sharded"), "tree_checksum": int(tree_sum.item()),
+                 "trees_identical_on_all_ranks": bool((tree_sums == tree_sums[0]).all().item())}
+assert res["stage2"]["trees_identical_on_all_ranks"]
 pb, pe = mg.shard_range(W * H, rank, world)
 for it in range(2):
     _, own_ms = timed(lambda: scene.render(lights, gmap, None, cam, W, H, 1, 1, (1.0, 1.0, 1.0), pb, pe))
