@@ -41,6 +41,19 @@ BYTES_PER_QUERY = 12 + 20 * K  # query 12 B + k*(12 B position re
 METRIC = "knn_gather_queries_per_s_k64"
 UNIT = "queries/s"
 
+
+
+def bench_config(world: int) -> dict:
+    """The `config` object of the JSON line — identical in both arms (the reference arm answers a bounded sample of the
+    same workload per step; its `cpu_baseline.sample` says which)."""
+    return {"workload": "C2: 10M-photon uniform cloud (unique coords), 1M kNN queries per GPU per step, k=64, cutoff 100",
+            "photons": N_PHOTONS, "queries_per_step": N_QUERIES, "k": K, "cutoff": CUTOFF,
+            "parallelism": f"replicated map, queries sharded x{world}",
+            "l2": "256 MiB flush write between steps (untimed); per-step working set 684 MB > 126 MB L2",
+            "outputs": "ids + dist2 + r2 per query (device resident)",
+            "env": {k: v for k, v in sorted(os.environ.items()) if k.startswith("PM_")}}
+
+
 PHOTON44 = np.dtype(
     [("pos", "<f4", 3), ("dir", "<f4", 3), ("color", "<f4", 3), ("power", "<f4"), ("qn", "u1", 3), ("split_dim", "u1")]
 )
@@ -148,18 +161,121 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def traffic_per_launch():
-    """dram bytes per 1M-query launch of the kNN kernels (descriptor pass + streaming kernel) from the committed
-    ncu capture, or None."""
+def traffic(key: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of a kernel from the committed ncu capture
+    (profiles/roofline_traffic.json, written by tools/summarize_profile.py), or None."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         try:
-            j = json.load(open(p))
-            a, b = j.get("k_grid_fast_k64_dram_bytes_per_launch"), j.get("k_fast_prep_k64_dram_bytes_per_launch")
-            return a + b if a is not None and b is not None else None
+            return json.load(open(p)).get(key)
         except Exception:
             return None
     return None
+
+
+def gpu_baseline_cukd(cloud: np.ndarray, queries: np.ndarray):
+    """The like-for-like GPU comparator of SURVEY §8(d): the reference's own cudaKDTree code (cukd::buildTree thrust
+    builder + stackBased::knn<HeapCandidateList<64>>, block 128, one thread per query) compiled for sm_100a from
+    /root/reference/externals/cudaKDTree into oracle/_ref/libcukd_ref.so, on the same B200 and the same C2 arrays.
+    Runs after the timed region; None when oracle/_ref did not travel to the box."""
+    import torch
+
+    path = os.path.join(ROOT, "oracle", "_ref", "libcukd_ref.so")
+    if not os.path.exists(path):
+        return None
+    ref = ctypes.CDLL(path)
+    d_ref = torch.from_numpy(cloud.view(np.uint8)).cuda()
+    d_box = torch.zeros(6, dtype=torch.float32, device="cuda")
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    torch.cuda.synchronize()
+    ev[0].record()
+    rc = ref.ref_build_tree_gpu(ctypes.c_void_p(d_ref.data_ptr()), len(cloud), ctypes.c_void_p(d_box.data_ptr()))
+    ev[1].record()
+    torch.cuda.synchronize()
+    if rc != 0:
+        return {"error": f"ref_build_tree_gpu returned {rc}"}
+    build_ms = ev[0].elapsed_time(ev[1])
+    d_q = torch.from_numpy(queries).cuda()
+    d_out = torch.zeros((len(queries), K), dtype=torch.int64, device="cuda")
+    d_r2 = torch.zeros(len(queries), dtype=torch.float32, device="cuda")
+    ms = []
+    for _ in range(3):
+        torch.cuda.synchronize()
+        ev[0].record()
+        rc = ref.ref_knn_gpu(ctypes.c_void_p(d_ref.data_ptr()), len(cloud), ctypes.c_void_p(d_q.data_ptr()), len(queries), K,
+                             ctypes.c_float(CUTOFF), ctypes.c_void_p(d_out.data_ptr()), ctypes.c_void_p(d_r2.data_ptr()))
+        ev[1].record()
+        torch.cuda.synchronize()
+        if rc != 0:
+            return {"error": f"ref_knn_gpu returned {rc}"}
+        ms.append(ev[0].elapsed_time(ev[1]))
+    return {"kind": "oracle/_ref", "what": "cukd::buildTree (thrust builder) + cukd::stackBased::knn<HeapCandidateList<64>>, "
+            "compiled for sm_100a from the reference tree, same B200, same arrays; first (cold) build, best of 3 query runs",
+            "build_ms": build_ms, "knn_ms": min(ms), "q_per_s": len(queries) / (min(ms) * 1e-3),
+            "r2_checksum": float(d_r2.double().sum().item())}
+
+
+def gpu_numa_node(index: int):
+    """NUMA node of GPU `index` from sysfs (PCI bus id via torch), or None."""
+    try:
+        import torch
+
+        bus = torch.cuda.get_device_properties(index).pci_bus_id
+        dom = torch.cuda.get_device_properties(index).pci_domain_id
+        dev = torch.cuda.get_device_properties(index).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        node = int(open(path).read().strip())
+        return node if node >= 0 else None
+    except Exception:
+        return None
+
+
+class pinned_local_alloc:
+    """Pinned host tensors on the NUMA node of this rank's GPU: the staging buffers of the end-to-end calls otherwise all
+    land on the node the process started on, and eight ranks' 260 MB-per-step result copies share one memory controller
+    (round-1 SCALE: e2e efficiency 0.31 at 8 GPUs). set_mempolicy(MPOL_PREFERRED, node) around the allocation; when the
+    container does not allow it the default placement is kept and `where` says so."""
+
+    def __init__(self, index: int):
+        self.node = gpu_numa_node(index)
+        self.where = "default policy (GPU NUMA node unknown)"
+        self.libc = None
+        if self.node is not None:
+            try:
+                self.libc = ctypes.CDLL(None, use_errno=True)
+                self.where = f"node {self.node} (set_mempolicy MPOL_PREFERRED around cudaHostAlloc)"
+            except Exception:
+                self.libc = None
+
+    def _policy(self, mode: int, node):
+        # long set_mempolicy(int mode, const unsigned long *nodemask, unsigned long maxnode): syscall 238 on x86-64
+        if self.libc is None:
+            return -1
+        if node is None:
+            return self.libc.syscall(238, 0, None, 0)
+        mask = (ctypes.c_ulong * 16)()
+        mask[node // 64] = 1 << (node % 64)
+        return self.libc.syscall(238, mode, mask, 16 * 64)
+
+    def __call__(self, t):
+        ok = self._policy(1, self.node) == 0 if self.node is not None else False
+        try:
+            out = t.pin_memory()
+        finally:
+            if ok:
+                self._policy(0, None)
+        if self.node is not None and not ok and "refused" not in self.where:
+            self.where = f"default policy (set_mempolicy refused for node {self.node})"
+        return out
+
+
+def run_pipelines(pkg, ctx, rank: int, local_rank: int, world: int):
+    """Strong-scaling stages over the `world` ranks (fixed total work): a C4-like pipeline and a C5-like progressive loop.
+    Filled in below (pipelines.py); returns a dict for the JSON line (rank 0) or None."""
+    import __graft_entry__ as graft
+
+    pl = graft.load_package_module("pipelines")
+    return pl.run(pkg, ctx, rank, local_rank, world)
 
 
 def run_stage_extras(pkg, ctx):
@@ -184,10 +300,17 @@ def run_stage_extras(pkg, ctx):
         wall = time.perf_counter() - t0
         res.append((ctx.last_kernel_ms, wall, n, paths, segs))
     k_ms, wall, n, paths, segs = min(res[1:])
+    peak, peak_src = peaks()
+    alg = 96.0 * segs + 40.0 * n  # 2 x 48 B of path state per traced segment + 40 B per stored photon
     out["stage1_cornell"] = {"casted": casted, "max_depth": depth, "paths": paths, "segments": segs, "stored": n,
                              "walk_kernel_ms": k_ms, "call_ms": 1e3 * wall, "paths_per_s": paths / wall,
                              "segments_per_s": segs / wall, "stored_photons_per_s": n / wall,
-                             "algorithmic_GBps": (96.0 * segs + 40.0 * n) / wall / 1e9}
+                             "algorithmic_GBps": alg / wall / 1e9,
+                             "roofline": {"bound": "hbm", "kernel": "k_walk (persistent warps) within pm_emit_photons",
+                                          "achieved": alg / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                          "frac": alg / (k_ms * 1e-3) / 1e9 / peak, "kernel_ms": k_ms,
+                                          "frac_whole_call": alg / wall / 1e9 / peak, "algorithmic_bytes_per_launch": alg,
+                                          "traffic": traffic("k_walk_dram_bytes_per_launch"), "peak_source": peak_src}}
     # ---- C1: 200 k + 100 k cast photons, maps, 512x512 render (spp 1, depth 1) ----------------------
     g40, ng, _, _ = scene.emit_photons(lights, 200_000, 10, False)
     c40, nc, _, _ = scene.emit_photons(lights, 100_000, 10, True)
@@ -259,10 +382,9 @@ def run_reference(args, rank: int):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C2: 10M-photon uniform cloud, kNN k=64, cutoff 100 (CPU arm: bounded sample per step)",
-                   "photons": N_PHOTONS, "queries_per_step": sample, "k": K},
+        "config": bench_config(args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{sample} of {N_QUERIES} queries per step on the 10M-photon tree; oracle port of "
+                         "sample": f"{sample} of the {N_QUERIES} queries per step on the 10M-photon tree; oracle port of "
                                    "cukd stackBased::knn<HeapCandidateList<64>> (the reference has no CPU path); "
                                    f"tree built by the oracle in {build_s:.1f} s (untimed)"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -341,43 +463,66 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     clocks = sampler.stop() if sampler else None
 
     # ---- e2e: same call with HOST (pinned) buffers; H2D + D2H inside the timed region -------------
-    h_q = torch.from_numpy(queries).pin_memory()
-    h_ids = torch.empty((N_QUERIES, K), dtype=torch.int32).pin_memory()
-    h_r2 = torch.empty(N_QUERIES, dtype=torch.float32).pin_memory()
+    pin = pinned_local_alloc(local_rank)
+    h_q = pin(torch.from_numpy(queries))
+    h_ids = pin(torch.empty((N_QUERIES, K), dtype=torch.int32))
+    h_r2 = pin(torch.empty(N_QUERIES, dtype=torch.float32))
 
     def step_host():
         pkg._check(pkg.lib().pm_knn(ctx.handle, pmap.handle, h_q.data_ptr(), N_QUERIES, K, CUTOFF, h_ids.data_ptr(), None,
                                     h_r2.data_ptr()))
 
-    for _ in range(2):
-        step_host()
-    e2e_steps = max(3, min(args.steps, 10))
-    e2e_ms = []
-    with torch.cuda.stream(ext_stream):
-        for _ in range(e2e_steps):
-            flush.zero_()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(ext_stream)
-            step_host()
-            e1.record(ext_stream)
-            e1.synchronize()
-            e2e_ms.append(e0.elapsed_time(e1))
-    e2e_total = float(sum(e2e_ms))
-    assert int(h_ids[0, 0]) >= 0
+    # the call the renderer makes: fused gather, 16 B in + 12 B out per query
+    brdf = np.full(N_QUERIES, 0.3, np.float32)
+    h_b = pin(torch.from_numpy(brdf))
+    h_rgb = pin(torch.empty((N_QUERIES, 3), dtype=torch.float32))
 
-    t = torch.tensor([total_ms, e2e_total], dtype=torch.float64, device="cuda")
+    def step_host_gather():
+        pkg._check(pkg.lib().pm_gather(ctx.handle, pmap.handle, h_q.data_ptr(), h_b.data_ptr(), N_QUERIES, K, CUTOFF,
+                                       h_rgb.data_ptr()))
+
+    def time_host(fn, steps):
+        for _ in range(2):
+            fn()
+        ms = []
+        with torch.cuda.stream(ext_stream):
+            for _ in range(steps):
+                flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(ext_stream)
+                fn()
+                e1.record(ext_stream)
+                e1.synchronize()
+                ms.append(e0.elapsed_time(e1))
+        return float(sum(ms))
+
+    e2e_steps = max(3, min(args.steps, 10))
+    if world > 1:
+        dist.barrier()
+    e2e_total = time_host(step_host, e2e_steps)
+    assert int(h_ids[0, 0]) >= 0
+    if world > 1:
+        dist.barrier()
+    e2e_gather_total = time_host(step_host_gather, e2e_steps)
+    assert float(h_rgb[0, 0]) > 0
+
+    t = torch.tensor([total_ms, e2e_total, e2e_gather_total], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms_max, e2e_total_max = float(t[0]), float(t[1])
+    total_ms_max, e2e_total_max, e2e_gather_max = float(t[0]), float(t[1]), float(t[2])
 
+    line = None
     if rank == 0:
         peak, peak_src = peaks()
         value = world * N_QUERIES * args.steps / (total_ms_max * 1e-3)
         e2e_value = world * N_QUERIES * e2e_steps / (e2e_total_max * 1e-3)
+        e2e_gather_value = world * N_QUERIES * e2e_steps / (e2e_gather_max * 1e-3)
         k_ms = float(np.mean(kern_ms))
-        achieved = BYTES_PER_QUERY * N_QUERIES / (k_ms * 1e-3) / 1e9
+        step_mean = total_ms / args.steps  # this rank's mean step: what the roofline fraction is taken on
+        achieved = BYTES_PER_QUERY * N_QUERIES / (step_mean * 1e-3) / 1e9
         # CPU baseline on this box's host cores (bounded sample), rank 0 at N = 1 only
         cpu = None
+        gpu_ref = None
         if world == 1 and not args.no_cpu_baseline:
             orc = load_oracle()
             tree_h = d_tree.cpu().numpy().view(PHOTON44).reshape(-1)
@@ -385,28 +530,48 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                    "sample": f"first {m} of the {N_QUERIES} queries on the same 10M-photon tree ({dt:.1f} s); oracle port of cukd "
                              "stackBased::knn<HeapCandidateList<64>>, OpenMP over queries (the reference has no CPU path)"}
+            try:
+                gpu_ref = gpu_baseline_cukd(cloud, queries)
+                if gpu_ref and "r2_checksum" in gpu_ref:
+                    gpu_ref["r2_checksum_ours"] = float(d_r2.double().sum().item())
+                    gpu_ref["speedup_knn_step"] = gpu_ref["knn_ms"] / step_mean
+                    gpu_ref["speedup_build"] = gpu_ref["build_ms"] / build_ms
+            except Exception as e:
+                gpu_ref = {"error": repr(e)}
+        build_alg = (88 + 24 * int(np.floor(np.log2(N_PHOTONS)))) * N_PHOTONS  # 640 B/photon at C2
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": total_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C2: 10M-photon uniform cloud (unique coords), 1M kNN queries per GPU, k=64, cutoff 100",
-                       "photons": N_PHOTONS, "queries_per_gpu": N_QUERIES, "k": K,
-                       "parallelism": f"replicated map, queries sharded x{world}",
-                       "l2": "256 MiB flush write between steps (untimed); per-step working set 684 MB > 126 MB L2",
-                       "outputs": "ids + dist2 + r2 per query (device resident)"},
+            "config": bench_config(world),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(N_QUERIES * 12),
                     "d2h_bytes_per_step": int(N_QUERIES * K * 4 + N_QUERIES * 4), "steps": e2e_steps,
-                    "api": "pm_knn with pinned host buffers (queries in, ids + r2 out)"},
+                    "api": "pm_knn with pinned host buffers (queries in, ids + r2 out)",
+                    "d2h_GBps_per_rank": (N_QUERIES * K * 4 + N_QUERIES * 4) * e2e_steps / (e2e_total_max * 1e-3) / 1e9,
+                    "pinned_numa": pin.where},
+            "e2e_gather": {"value": e2e_gather_value, "unit": UNIT, "h2d_bytes_per_step": int(N_QUERIES * 16),
+                           "d2h_bytes_per_step": int(N_QUERIES * 12), "steps": e2e_steps,
+                           "api": "pm_gather with pinned host buffers (hit + brdf in, rgb out): the call the renderer makes"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic_per_launch(),
-                         "kernel": "k_fast_prep + k_grid_fast<false> (+ k_grid_query<false> / k_kd<64> on the queries handed over)", "kernel_ms": k_ms,
+                         "traffic": traffic("knn_step_k64_dram_bytes_per_launch"),
+                         "window": "the whole pm_knn step (CUDA events around the call on the context's stream): query binning "
+                                   "(k_qbin_count/scan/scatter) + k_knn_fast<false> + k_grid_query<false> / k_kdw<false> on the queries handed over",
+                         "kernel": "k_knn_fast<false>", "step_ms": step_mean, "kernel_ms": k_ms,
+                         "kernel_ms_window": "events inside pm_knn around the same kernels (ordering included), without the call's launch and sync latency",
+                         "frac_kernels": BYTES_PER_QUERY * N_QUERIES / (k_ms * 1e-3) / 1e9 / peak,
                          "kd_tree_fallback_queries": int(fallbacks), "general_grid_kernel_queries": int(handovers),
                          "algorithmic_bytes_per_launch": BYTES_PER_QUERY * N_QUERIES, "peak_source": peak_src},
             "cpu_baseline": cpu,
+            "gpu_baseline": gpu_ref,
             "clocks": clocks,
             "stage2_build": {"photons": N_PHOTONS, "ms_first": build_ms, "ms": build_ms_warm,
-                             "photons_per_s": N_PHOTONS / (build_ms_warm * 1e-3)},
+                             "photons_per_s": N_PHOTONS / (build_ms_warm * 1e-3),
+                             "roofline": {"bound": "hbm", "kernel": "pm_map_build (3 axis sorts, k_level x14, k_finish_subtrees, gather, grid copy)",
+                                          "achieved": build_alg / (build_ms_warm * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                          "frac": build_alg / (build_ms_warm * 1e-3) / 1e9 / peak, "kernel_ms": build_ms_warm,
+                                          "algorithmic_bytes_per_launch": build_alg,
+                                          "traffic": traffic("map_build_10M_dram_bytes_per_launch"), "peak_source": peak_src}},
             "wall_ms_timed_region": wall_ms,
         }
         if world == 1 and not args.no_stage_extras:
@@ -414,8 +579,18 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                 line["stages"] = run_stage_extras(pkg, ctx)
             except Exception as e:  # secondary figures must never cost the headline line
                 line["stages"] = {"error": repr(e)}
-        print(json.dumps(line), flush=True)
     pmap.close()
+    del d_tree, d_ids, d_d2, flush
+    torch.cuda.empty_cache()
+    if not args.no_pipelines:
+        try:
+            pipes = run_pipelines(pkg, ctx, rank, local_rank, world)
+        except Exception as e:
+            pipes = {"error": repr(e)}
+        if line is not None:
+            line["pipelines"] = pipes
+    if rank == 0:
+        print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
@@ -429,6 +604,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stage-extras", action="store_true", help="skip the stage-1 / C1-render secondary figures")
+    ap.add_argument("--no-pipelines", action="store_true", help="skip the C4-like / C5-like multi-GPU pipeline stages")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

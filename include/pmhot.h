@@ -124,6 +124,13 @@ void pm_ctx_destroy(pm_ctx* ctx);
 /* cudaStream_t of the context, as an opaque pointer (for event timing by the caller) */
 void* pm_ctx_stream(pm_ctx* ctx);
 int  pm_ctx_sync(pm_ctx* ctx);
+/* Input readiness: the context's stream is created non-blocking, so it is NOT ordered after work the caller queued
+ * on other streams (the legacy default stream included). Device buffers handed to a pm_* call must be complete when
+ * the call is made — or the caller orders the context's stream after the producing stream first:
+ * pm_ctx_wait_stream records an event on `other_stream` (a cudaStream_t; NULL = the legacy default stream) and makes
+ * the context's stream wait for it, without blocking the host. Results need no such step: every pm_* call returns
+ * after its work on the context's stream has completed. */
+int  pm_ctx_wait_stream(pm_ctx* ctx, void* other_stream);
 /* counters: number of kernels launched by this context since creation / last reset */
 int64_t pm_ctx_launch_count(pm_ctx* ctx);
 void pm_ctx_reset_launch_count(pm_ctx* ctx);
@@ -132,8 +139,8 @@ float pm_ctx_last_kernel_ms(pm_ctx* ctx);
 /* queries of the most recent pm_knn / pm_gather that the uniform-grid kernel handed to the kd-tree
  * kernel (sparse or very dense neighbourhoods); -1 if the map has no grid (small maps) */
 int64_t pm_ctx_last_fallback_count(pm_ctx* ctx);
-/* queries of the most recent pm_knn / pm_gather that the descriptor fast path (uniform-like clouds)
- * handed to the general uniform-grid kernel; 0 if the fast path was not used */
+/* queries of the most recent pm_knn / pm_gather that the fast path (uniform-like clouds) handed to the general
+ * uniform-grid kernel; 0 if the fast path was not used */
 int64_t pm_ctx_last_handover_count(pm_ctx* ctx);
 
 /* ---- scene: LBVH build + traversal  (≙ loadGeometry, common/src/world.cpp:3-58) ------- */
@@ -245,6 +252,14 @@ int  pm_render(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host, 
                const pm_map* global_map, const pm_map* caustic_map, const pm_camera* camera,
                int width, int height, int spp, int depth, const float sky[3],
                int64_t pixel_begin, int64_t pixel_end, uint32_t* fb_rgba8);
+
+/* pm_render that also returns the colour BEFORE make_rgba quantises it (rgb_linear: 3*W*H floats indexed by launch
+ * index px + W*py, only the pixels of this call are written; may be NULL): what an image RMSE against the reference
+ * is computed on. Not in the reference (its only output is the 8-bit framebuffer). */
+int  pm_render_rgb(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host, int n_lights,
+                   const pm_map* global_map, const pm_map* caustic_map, const pm_camera* camera,
+                   int width, int height, int spp, int depth, const float sky[3],
+                   int64_t pixel_begin, int64_t pixel_end, uint32_t* fb_rgba8, float* rgb_linear);
 
 /* ---- photon viewer (≙ photonViewer: photon-viewer/src/hostCode.cu:53-75 + photon-viewer/cuda/deviceCode.cu:10-49) --
  * Splats photons into a W*H RGBA8 image: each photon is projected with the reference's glm::lookAt /

@@ -197,11 +197,14 @@ static inline bool refract4(vec3 v, vec3 n, float ni_over_nt, vec3* refracted) {
 /* helpers.h:109-113 — evaluated in double as the reference's literals force; pow(x,5) is
  * defined as x*x*x*x*x here and in the device code. */
 static inline float schlick(float cosv, float ior) {
-  double r0 = (1. - (double)ior) / (1. + (double)ior);
+  /* helpers.h:109-113: `float r0 = (1. - ior) / (1. + ior)` is a double quotient rounded to float, `r0 = r0 * r0` a
+   * float product; the return expression is evaluated in double (the literal 1. promotes it). pow(x, 5) is taken as
+   * the product x*x*x*x*x (stated deviation: CUDA's pow is not available to the host). */
+  float r0 = (float)((1. - (double)ior) / (1. + (double)ior));
   r0 = r0 * r0;
   const double b = 1. - (double)cosv;
   const double b5 = b * b * b * b * b;
-  return (float)(r0 + (1. - r0) * b5);
+  return (float)((double)r0 + (1. - (double)r0) * b5);
 }
 
 /* ---- scene description shared by the stage-1/3 oracles -------------------------------- */

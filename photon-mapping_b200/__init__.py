@@ -49,6 +49,7 @@ _SIGNATURES = {
     "pm_ctx_destroy": (None, [c_void_p]),
     "pm_ctx_stream": (c_void_p, [c_void_p]),
     "pm_ctx_sync": (c_int, [c_void_p]),
+    "pm_ctx_wait_stream": (c_int, [c_void_p, c_void_p]),
     "pm_ctx_launch_count": (c_int64, [c_void_p]),
     "pm_ctx_reset_launch_count": (None, [c_void_p]),
     "pm_ctx_last_kernel_ms": (c_float, [c_void_p]),
@@ -91,6 +92,11 @@ _SIGNATURES = {
         c_int,
         [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
          c_int64, c_int64, c_void_p],
+    ),
+    "pm_render_rgb": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+         c_int64, c_int64, c_void_p, c_void_p],
     ),
     "pm_photons_write_text": (c_int, [c_char_p, c_void_p, c_int64]),
     "pm_photons_read_text": (c_int, [c_char_p, c_void_p, c_int64, POINTER(c_int64)]),
@@ -171,6 +177,18 @@ class Context:
     def sync(self) -> None:
         _check(lib().pm_ctx_sync(self.handle))
 
+    def after_torch(self, *buffers) -> None:
+        """Order the context's (non-blocking) stream after torch's current stream when any of `buffers` is a CUDA
+        tensor: torch ops that produced it may still be queued (pmhot.h: input readiness). No host wait."""
+        for b in buffers:
+            if b is not None and getattr(b, "is_cuda", False):
+                import torch
+
+                s = torch.cuda.current_stream(b.device)
+                if s.cuda_stream != self.stream:
+                    _check(lib().pm_ctx_wait_stream(self.handle, s.cuda_stream))
+                return
+
     @property
     def stream(self) -> int:
         return lib().pm_ctx_stream(self.handle) or 0
@@ -209,6 +227,7 @@ class PhotonMap:
         n = _count(photons, 44)
         h = c_void_p()
         bounds = np.zeros(6, np.float32)
+        ctx.after_torch(photons)
         _check(lib().pm_map_build(ctx.handle, _ptr(photons), n, bounds.ctypes.data, ctypes.byref(h)))
         return cls(ctx, h, n, bounds, photons)
 
@@ -216,6 +235,7 @@ class PhotonMap:
     def from_tree(cls, ctx: Context, photons) -> "PhotonMap":
         n = _count(photons, 44)
         h = c_void_p()
+        ctx.after_torch(photons)
         _check(lib().pm_map_from_tree(ctx.handle, _ptr(photons), n, ctypes.byref(h)))
         return cls(ctx, h, n, None, photons)
 
@@ -230,13 +250,14 @@ class PhotonMap:
         elem = torch.empty(n, dtype=torch.int32, device=photons.device)
         dim = torch.zeros((n + 3) // 4 * 4, dtype=torch.uint8, device=photons.device)
         bounds = np.zeros(6, np.float32)
+        ctx.after_torch(photons)  # also orders the zero fill of `dim` before the library's writes
         _check(lib().pm_map_build_shard(ctx.handle, _ptr(photons), n, rank, world, elem.data_ptr(), dim.data_ptr(),
                                         bounds.ctypes.data))
         if world > 1:
             reduce_sum(elem)
             reduce_sum(dim.view(torch.int32))  # one rank contributes each byte: no carries
-            torch.cuda.synchronize(photons.device)
         h = c_void_p()
+        ctx.after_torch(photons)  # the all-reduces run on torch's stream
         _check(lib().pm_map_build_finish(ctx.handle, _ptr(photons), n, elem.data_ptr(), dim.data_ptr(), bounds.ctypes.data,
                                          ctypes.byref(h)))
         return cls(ctx, h, n, bounds, photons)
@@ -246,6 +267,7 @@ class PhotonMap:
         """pm_map_build_cells: cells-only map (input order, no kd-tree) for `gather_radius`; kNN calls reject it."""
         n = _count(photons, 44)
         h = c_void_p()
+        ctx.after_torch(photons)
         _check(lib().pm_map_build_cells(ctx.handle, _ptr(photons), n, cell_size, ctypes.byref(h)))
         return cls(ctx, h, n, None, photons)
 
@@ -279,6 +301,7 @@ class PhotonMap:
                 out_dist2 = torch.empty((nq, k), dtype=torch.float32, device=dev)
             if want_r2 and out_r2 is None:
                 out_r2 = torch.empty(nq, dtype=torch.float32, device=dev)
+        self.ctx.after_torch(queries, out_ids)
         _check(lib().pm_knn(self.ctx.handle, self.handle, _ptr(queries), nq, k, cutoff, _ptr(out_ids), _ptr(out_dist2),
                             _ptr(out_r2)))
         return out_ids, out_dist2, out_r2
@@ -293,6 +316,7 @@ class PhotonMap:
                 import torch
 
                 out_rgb = torch.empty((nq, 3), dtype=torch.float32, device=hit.device)
+        self.ctx.after_torch(hit, brdf, out_rgb)
         _check(lib().pm_gather(self.ctx.handle, self.handle, _ptr(hit), _ptr(brdf), nq, k, cutoff, _ptr(out_rgb)))
         return out_rgb
 
@@ -308,6 +332,7 @@ def _gather_radius(self, hit, brdf, radius2, out_flux=None, out_count=None):
 
         out_flux = torch.empty((nq, 3), dtype=torch.float32, device=hit.device) if out_flux is None else out_flux
         out_count = torch.empty(nq, dtype=torch.int32, device=hit.device) if out_count is None else out_count
+    self.ctx.after_torch(hit, brdf, radius2, out_flux)
     _check(lib().pm_gather_radius(self.ctx.handle, self.handle, _ptr(hit), _ptr(brdf), _ptr(radius2), nq, _ptr(out_flux),
                                   _ptr(out_count)))
     return out_flux, out_count
@@ -397,6 +422,7 @@ class Scene:
         if out is None:
             out = np.empty(capacity, PHOTON40)
         count, npaths, nseg = c_int64(0), c_int64(0), c_int64(0)
+        self.ctx.after_torch(out)
         if shapes is not None:
             shapes = np.ascontiguousarray(shapes, LIGHT_SHAPE).reshape(-1)
             assert len(shapes) == len(lights)
@@ -414,19 +440,21 @@ class Scene:
 
     def render(self, lights: np.ndarray, global_map: PhotonMap | None, caustic_map: PhotonMap | None, camera: np.ndarray,
                width: int, height: int, spp: int = 1, depth: int = 1, sky=(1.0, 1.0, 1.0), pixel_begin: int = 0,
-               pixel_end: int | None = None) -> np.ndarray:
-        """≙ owlRayGenLaunch2D(simpleRayGen) (ray-tracer/src/hostCode.cu:231-237). Returns uint32[H,W]."""
+               pixel_end: int | None = None, linear: bool = False):
+        """≙ owlRayGenLaunch2D(simpleRayGen) (ray-tracer/src/hostCode.cu:231-237). Returns uint32[H,W]; with
+        ``linear`` also the colours before make_rgba as float32[W*H, 3] by launch index (pm_render_rgb)."""
         lights = np.ascontiguousarray(lights, LIGHT)
         camera = np.ascontiguousarray(camera, CAMERA)
         sky = np.asarray(sky, np.float32)
         fb = np.zeros((height, width), np.uint32)
         if pixel_end is None:
             pixel_end = width * height
-        _check(lib().pm_render(self.ctx.handle, self.handle, lights.ctypes.data, len(lights),
-                               global_map.handle if global_map else None, caustic_map.handle if caustic_map else None,
-                               camera.ctypes.data, width, height, spp, depth, sky.ctypes.data, pixel_begin, pixel_end,
-                               fb.ctypes.data))
-        return fb
+        rgb = np.zeros((width * height, 3), np.float32) if linear else None
+        _check(lib().pm_render_rgb(self.ctx.handle, self.handle, lights.ctypes.data, len(lights),
+                                   global_map.handle if global_map else None, caustic_map.handle if caustic_map else None,
+                                   camera.ctypes.data, width, height, spp, depth, sky.ctypes.data, pixel_begin, pixel_end,
+                                   fb.ctypes.data, rgb.ctypes.data if linear else None))
+        return (fb, rgb) if linear else fb
 
 
 def photons_to_maps(ctx: Context, global40: np.ndarray, caustic40: np.ndarray):

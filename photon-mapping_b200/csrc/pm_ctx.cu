@@ -111,6 +111,8 @@ int pm_ctx_create(int device, pm_ctx** out) {
   }
   PM_CUDA(cudaEventCreate(&c->ev0));
   PM_CUDA(cudaEventCreate(&c->ev1));
+  PM_CUDA(cudaEventCreateWithFlags(&c->ev_order, cudaEventDisableTiming));
+  PM_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&c->host_counts), 4 * sizeof(int), cudaHostAllocDefault));
   *out = c;
   return PM_OK;
 }
@@ -128,6 +130,8 @@ void pm_ctx_destroy(pm_ctx* ctx) {
   }
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
+  cudaEventDestroy(ctx->ev_order);
+  if (ctx->host_counts) cudaFreeHost(ctx->host_counts);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -137,6 +141,14 @@ void* pm_ctx_stream(pm_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 int pm_ctx_sync(pm_ctx* ctx) {
   if (!ctx) return PM_ERR_INVALID;
   PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PM_OK;
+}
+
+int pm_ctx_wait_stream(pm_ctx* ctx, void* other_stream) {
+  if (!ctx) return PM_ERR_INVALID;
+  PM_CUDA(cudaSetDevice(ctx->device));
+  PM_CUDA(cudaEventRecord(ctx->ev_order, (cudaStream_t)other_stream));
+  PM_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_order, 0));
   return PM_OK;
 }
 

@@ -180,13 +180,14 @@ __device__ __forceinline__ bool refract4(vec3 v, vec3 n, float ni_over_nt, vec3*
   if (disc > 0.f) { *refracted = ni_over_nt * (uv - n * dt) - n * __fsqrt_rn(disc); return true; }
   return false;
 }
-/* helpers.h:109-113, evaluated in double like the reference's literals force */
+/* helpers.h:109-113: r0 is a double quotient rounded to float and squared in float; the return expression is
+ * evaluated in double (its literals force that); pow(x, 5) as the product the oracle uses */
 __device__ __forceinline__ float schlick(float cosv, float ior) {
-  double r0 = __ddiv_rn(1. - (double)ior, 1. + (double)ior);
-  r0 = __dmul_rn(r0, r0);
+  float r0 = (float)__ddiv_rn(1. - (double)ior, 1. + (double)ior);
+  r0 = __fmul_rn(r0, r0);
   const double b = 1. - (double)cosv;
   const double b5 = __dmul_rn(__dmul_rn(__dmul_rn(__dmul_rn(b, b), b), b), b);
-  return (float)__dadd_rn(r0, __dmul_rn(1. - r0, b5));
+  return (float)__dadd_rn((double)r0, __dmul_rn(1. - (double)r0, b5));
 }
 
 }  // namespace pmd

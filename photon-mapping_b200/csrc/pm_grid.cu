@@ -439,235 +439,187 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
 }
 
 /* ---- fast path for uniform-like clouds --------------------------------------------------
- * k_grid_query spends about a third of its instructions on per-query scalar work that all 32 lanes
- * repeat (block bounds, radius guess, row trimming, building the flat index space). Here that work is
- * done by k_fast_prep with ONE THREAD per query, which leaves a 224-byte descriptor (search radius,
- * histogram window, the ball-trimmed rows already flattened); k_grid_fast then only streams the
- * candidates (one warp per query), compacts those inside the radius and selects the k smallest with a
- * 31-bin histogram whose shared-memory atomics also hand out the output positions. No retries: a query
- * whose guess does not hold (too few / too many candidates, boundary bin over-full, neighbourhood not
- * covered by its 5x5x5 block) is appended to a list that k_grid_query answers. The result contract is
- * the same: exactly the k smallest (dist² bits, node id) pairs. */
-constexpr int kFastRows = 25;                 /* rows of a 5x5x5 block */
-constexpr int kFastWords = 11;                /* flat index space: 11 * 32 = 352 candidates */
+ * k_grid_query spends a third of its instructions on a density pass (50 offset-table reads per query) and on a
+ * selection that keeps every candidate's bin and position. On a uniform-like cloud neither is needed: the radius
+ * that holds about 1.25 k + 10 photons is a property of the MAP (sampled when the grid is built), and the cells are
+ * sized so that a 5x5x5 block guarantees it. k_knn_fast therefore starts every query at that radius:
+ *   - the lanes own the rows of the block (row = r0 + lane), trim them to the ball in cell units, and a warp scan
+ *     flattens them (same bitmap trick as k_grid_query) — no descriptor, no second kernel;
+ *   - candidates inside the radius are compacted into shared memory as (dist² bits, id);
+ *   - ONE histogram over dist² (window from the count actually found) locates the bin of the k-th candidate, its
+ *     <= 32 members are ranked, and the k-th dist² becomes a threshold tau: every candidate with dist² <= tau is
+ *     written straight to its output row at a ballot-compacted position. A tie on tau that would need the id order
+ *     (the exact (dist², id) contract) is left to k_grid_query;
+ *   - a query whose count falls outside [k, 128] retries with the radius rescaled by the count it saw, on a wider
+ *     block if the exactness bound needs one (balls cut by the cloud's faces take this path); what still fails
+ *     after kFastAttempts goes to the hand-over list that k_grid_query answers.
+ * Queries arrive pre-ordered as float4 (x, y, z, bits(index)) from the binning pass of pm_knn.cu. */
+constexpr int kFastWords = 12;                /* flat index space of one round of rows: 384 candidates */
 constexpr int kFastMaxScan = kFastWords * 32;
-constexpr int kFastChunk = 1 << 21;           /* queries per descriptor buffer (448 MB) */
-constexpr int kPrepBlock = 128;
-enum { FAST_OK = 0, FAST_SKIP = 1, FAST_HANDOVER = 2 };
-
-struct __align__(16) FastDesc {
-  float R2, Ta, scale, qx;      /* search radius², histogram window [Ta, R2) and 30 / (R2 - Ta); the query */
-  float qy, qz;
-  int info, qi;                 /* candidates in the trimmed rows | non-empty rows << 16 | FAST_* << 24; query index */
-  uint2 words[kFastWords];      /* x: bitmap of row starts among elements [32 i, 32 i + 32); y: row holding element 32 i */
-  int rows[kFastRows + 1];      /* per non-empty row: first record - first flat index */
-};
-static_assert(sizeof(FastDesc) == 224, "descriptor layout");
-
-__global__ void __launch_bounds__(kPrepBlock)
-k_fast_prep(const GridView g, const pmk::QueryIO io, int t0, int cnt, FastDesc* __restrict__ desc) {
-  /* descriptors are assembled in shared memory (57-word stride: conflict-free) and leave the block as
-   * fully coalesced stores; per-thread 4- and 8-byte stores at a 224-byte stride cost 5x the sectors */
-  constexpr int kDescWords = (int)sizeof(FastDesc) / 4, kStride = kDescWords + 1;
-  constexpr int kWordsAt = 8, kRowsAt = 8 + 2 * kFastWords;
-  __shared__ uint32_t sd[kPrepBlock * kStride];
-  uint32_t* my = sd + threadIdx.x * kStride;
-  const int u = min(blockIdx.x * kPrepBlock + (int)threadIdx.x, cnt - 1); /* surplus threads repeat the last query */
-  const int qi = io.order ? io.order[t0 + u] : t0 + u;
-  int flags = FAST_OK, mc = 0, nr = 0;
-  float R2 = 0.f, Ta = 0.f, scale = 0.f, qx = 0.f, qy = 0.f, qz = 0.f;
-  uint32_t wx[kFastWords], wy[kFastWords];
-#pragma unroll
-  for (int i = 0; i < kFastWords; i++) { wx[i] = 0u; wy[i] = 0u; }
-  if (io.brdf && !(io.brdf[qi] > 0.f)) {
-    flags = FAST_SKIP;
-  } else {
-    const int k = io.k;
-    qx = io.q[(size_t)qi * 3 + 0]; qy = io.q[(size_t)qi * 3 + 1]; qz = io.q[(size_t)qi * 3 + 2];
-    const float fx = (qx - g.lo[0]) * g.inv_cell, fy = (qy - g.lo[1]) * g.inv_cell, fz = (qz - g.lo[2]) * g.inv_cell;
-    const int cx = min(max(__float2int_rd(fx), 0), g.nx - 1), cy = min(max(__float2int_rd(fy), 0), g.ny - 1),
-              cz = min(max(__float2int_rd(fz), 0), g.nz - 1);
-    const int x0 = max(cx - 2, 0), x1 = min(cx + 2, g.nx - 1);
-    const int y0 = max(cy - 2, 0), y1 = min(cy + 2, g.ny - 1);
-    const int z0 = max(cz - 2, 0), z1 = min(cz + 2, g.nz - 1);
-    /* G as in k_grid_query: every node closer than G lies inside the block */
-    float Gc = INFINITY;
-    if (x0 > 0) Gc = fminf(Gc, fx - (float)x0);
-    if (x1 < g.nx - 1) Gc = fminf(Gc, (float)(x1 + 1) - fx);
-    if (y0 > 0) Gc = fminf(Gc, fy - (float)y0);
-    if (y1 < g.ny - 1) Gc = fminf(Gc, (float)(y1 + 1) - fy);
-    if (z0 > 0) Gc = fminf(Gc, fz - (float)z0);
-    if (z1 < g.nz - 1) Gc = fminf(Gc, (float)(z1 + 1) - fz);
-    const float G = Gc * g.cell - g.margin;
-    const float Rmax2 = fminf(G > 0.f ? G * G : 0.f, io.cutoff2);
-    /* mean density of the block -> radius expected to hold 1.3 k + 12 nodes. The 5x5 rows are unrolled
-     * (rows outside the grid read a clamped address and count nothing) so that all 50 loads are in flight */
-    int m0 = 0;
-    uint32_t rbase[kFastRows];
-#pragma unroll
-    for (int r = 0; r < kFastRows; r++) {
-      const int rz = cz - 2 + r / 5, ry = cy - 2 + r % 5;
-      const bool in = rz >= z0 && rz <= z1 && ry >= y0 && ry <= y1;
-      rbase[r] = in ? ((uint32_t)rz * (uint32_t)g.ny + (uint32_t)ry) * (uint32_t)g.nx : 0xffffffffu;
-      const uint32_t bs = in ? rbase[r] : 0u;
-      const int c = (int)(__ldg(g.cell_start + bs + x1 + 1) - __ldg(g.cell_start + bs + x0));
-      m0 += in ? c : 0;
-    }
-    const float fk = (float)k, eK = 1.3f * fk + 12.f;
-    float eR = 0.f; /* nodes expected inside R2 */
-    if (m0 > 0) {
-      const float vol = (float)((x1 - x0 + 1) * (y1 - y0 + 1) * (z1 - z0 + 1)) * (g.cell * g.cell * g.cell);
-      const float rho = __fdividef(4.18879f * (float)m0, vol);
-      const float Rg = pow23(__fdividef(eK, rho));
-      if (Rg < Rmax2) { R2 = Rg; eR = eK; }
-      else { R2 = Rmax2; eR = rho * R2 * sqrtf(R2); }
-    }
-    if (!(eR >= fk + 4.f) || !(R2 > 0.f) || !(R2 < INFINITY)) {
-      flags = FAST_HANDOVER;
-    } else {
-      /* histogram window: bin 0 below the radius expected to hold k - 3 sigma nodes, 30 linear bins up to R2 */
-      const float delta = 3.f * sqrtf(fk) + 2.f;
-      Ta = R2 * pow23(__fdividef(fmaxf(fk - delta, 0.5f), eR));
-      scale = __fdividef(30.f, R2 - Ta);
-      /* ball-trimmed rows (same arithmetic as k_grid_query): all loads first, then the serial flattening */
-      int st[kFastRows], len[kFastRows];
-#pragma unroll
-      for (int r = 0; r < kFastRows; r++) {
-        const int rz = cz - 2 + r / 5, ry = cy - 2 + r % 5;
-        const float ylo = g.lo[1] + (float)ry * g.cell, zlo = g.lo[2] + (float)rz * g.cell;
-        const float dy = fmaxf(fmaxf(ylo - qy, qy - (ylo + g.cell)) - g.margin, 0.f);
-        const float dz = fmaxf(fmaxf(zlo - qz, qz - (zlo + g.cell)) - g.margin, 0.f);
-        const float dyz2 = dy * dy + dz * dz;
-        const float t2 = fmaxf(R2 - dyz2, 1e-30f);
-        const float w = t2 * rsqrtf(t2) * 1.0001f + g.margin;
-        const int xa = max(cell_idx(qx - w, g.lo[0], g.inv_cell, g.nx), x0);
-        const int xb = min(cell_idx(qx + w, g.lo[0], g.inv_cell, g.nx), x1);
-        const bool use = rbase[r] != 0xffffffffu && dyz2 < R2 && xa <= xb;
-        const uint32_t bs = use ? rbase[r] : 0u;
-        st[r] = (int)__ldg(g.cell_start + bs + (use ? xa : 0));
-        len[r] = use ? (int)__ldg(g.cell_start + bs + (use ? xb + 1 : 0)) - st[r] : 0;
-      }
-#pragma unroll
-      for (int r = 0; r < kFastRows; r++) {
-        if (len[r] > 0) {
-          if (mc + len[r] <= kFastMaxScan) {
-            my[kRowsAt + nr] = (uint32_t)(st[r] - mc);
-            wx[mc >> 5] |= 1u << (mc & 31);
-            nr++;
-          } else {
-            flags = FAST_HANDOVER;
-          }
-          mc += len[r];
-        }
-      }
-      /* wy[i] = the row holding element 32 i */
-      int runs = 0;
-#pragma unroll
-      for (int i = 0; i < kFastWords; i++) {
-        wy[i] = (uint32_t)max(runs + (int)(wx[i] & 1u) - 1, 0);
-        runs += __popc(wx[i]);
-      }
-      if (mc < k) flags = FAST_HANDOVER;
-    }
-  }
-  my[0] = __float_as_uint(R2); my[1] = __float_as_uint(Ta); my[2] = __float_as_uint(scale); my[3] = __float_as_uint(qx);
-  my[4] = __float_as_uint(qy); my[5] = __float_as_uint(qz);
-  my[6] = (uint32_t)(min(mc, 0xffff) | (nr << 16) | (flags << 24)); my[7] = (uint32_t)qi;
-#pragma unroll
-  for (int i = 0; i < kFastWords; i++) { my[kWordsAt + 2 * i] = wx[i]; my[kWordsAt + 2 * i + 1] = wy[i]; }
-  __syncthreads();
-  const int first = blockIdx.x * kPrepBlock, nd = min(kPrepBlock, cnt - first);
-  uint32_t* out = reinterpret_cast<uint32_t*>(desc + first);
-  for (int w = threadIdx.x; w < nd * kDescWords; w += kPrepBlock) {
-    const int di = w / kDescWords;
-    out[w] = sd[di * kStride + (w - di * kDescWords)];
-  }
-}
+constexpr int kFastMaxH = 4;                  /* widest block of the fast path: 9x9 rows (3 rounds) */
+constexpr int kFastAttempts = 4;
 
 struct __align__(16) FastScratch {
-  uint64_t keys[kBuf];  /* compacted candidates, then the k results in output order */
-  uint64_t bl[32];      /* candidates of the bin that holds the k-th */
+  uint2 keys[kBuf];         /* (dist² bits, node id) of the candidates inside the search radius */
+  uint2 words[kFastWords];  /* x: bitmap of row starts among elements [32 i, 32 i + 32); y: row holding element 32 i */
+  int off[32];              /* per non-empty row: first record - first flat index */
   int hist[32];
+  uint32_t bl[32];          /* dist² bits of the bin that holds the k-th candidate */
 };
 
+/* histogram window per candidate count n (count ~ r^3, binomial spread at the k-th): bin 0 ends at Ta = R2 * x,
+ * 30 linear bins up to R2 with scale = y / R2 */
+constexpr int kWinSize = kBuf + 1;
+struct FastParams {
+  const float4* sq;   /* queries in processing order */
+  float R2;           /* first search radius², already capped by the block guarantee and the cutoff */
+  float Rc2;          /* (its radius in cells + the margins)² */
+  float margin_c;     /* GridView::margin in cells */
+  float2 win[kWinSize];
+};
+
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 template <bool GATHER>
-__global__ void __launch_bounds__(kWarps * 32, 8)
-k_grid_fast(const GridView g, const float4* __restrict__ color4, const pmk::QueryIO io, const FastDesc* __restrict__ desc,
-            int cnt, int* __restrict__ ho_list, int* __restrict__ ho_count) {
+__global__ void __launch_bounds__(kWarps * 32, 6)
+k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::QueryIO io, const __grid_constant__ FastParams fp,
+           int* __restrict__ ho_list, int* __restrict__ ho_count) {
   __shared__ FastScratch scratch[kWarps];
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u, le_not0 = (lt | (1u << lane)) & ~1u;
   FastScratch& ws = scratch[threadIdx.x >> 5];
   const int k = io.k;
-  for (int u = blockIdx.x * kWarps + (threadIdx.x >> 5); u < cnt; u += gridDim.x * kWarps) {
-    const FastDesc* d = desc + u;
-    const float4 ha = __ldg(reinterpret_cast<const float4*>(d));
-    const float4 hb4 = __ldg(reinterpret_cast<const float4*>(d) + 1);
-    /* the next descriptor of this warp on its way into L2 while this query is answered */
-    if (lane < 7 && u + gridDim.x * kWarps < cnt)
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(d + gridDim.x * kWarps) + lane * 32));
-    const int info = __float_as_int(hb4.z), qi = __float_as_int(hb4.w);
-    const int mc = info & 0xffff, nr = (info >> 16) & 0xff, fl = info >> 24;
-    if (fl != FAST_OK) {
-      if (fl == FAST_SKIP) { if (GATHER && lane < 3) io.rgb[(size_t)qi * 3 + lane] = 0.f; }
-      else if (lane == 0) ho_list[atomicAdd(ho_count, 1)] = qi;
-      continue;
+  const float fk = (float)k;
+  /* rows of the 5x5 block of the first attempt: lane -> (oy, oz) */
+  const int oz5 = div_small(lane, 5) - 2, oy5 = lane - (oz5 + 2) * 5 - 2;
+  for (int t = blockIdx.x * kWarps + (threadIdx.x >> 5); t < io.nq; t += gridDim.x * kWarps) {
+    const float4 qv = __ldg(fp.sq + t);
+    const int qi = __float_as_int(qv.w);
+    float brdf = 0.f;
+    if (GATHER) {
+      brdf = __ldg(io.brdf + qi);
+      if (!(brdf > 0.f)) {
+        if (lane < 3) io.rgb[(size_t)qi * 3 + lane] = 0.f;
+        continue;
+      }
     }
-    const float R2 = ha.x, Ta = ha.y, scale = ha.z, qx = ha.w, qy = hb4.x, qz = hb4.y;
-    uint2 wd = make_uint2(0u, 0u);
-    int row = 0;
-    if (lane < nr) row = __ldg(&d->rows[lane]);
-    if (lane < kFastWords) wd = __ldg(&d->words[lane]);
+    const float qx = qv.x, qy = qv.y, qz = qv.z;
+    const float fx = (qx - g.lo[0]) * g.inv_cell, fy = (qy - g.lo[1]) * g.inv_cell, fz = (qz - g.lo[2]) * g.inv_cell;
+    const int cx = min(max(__float2int_rd(fx), 0), g.nx - 1), cy = min(max(__float2int_rd(fy), 0), g.ny - 1),
+              cz = min(max(__float2int_rd(fz), 0), g.nz - 1);
+    const float uy = fy - (float)cy, uz = fz - (float)cz; /* position inside the own cell, in cells */
     ws.hist[lane] = 0;
 
-    /* ---- scan: every lane pulls one record per step; those inside the radius are compacted ---- */
-    int n = 0;
-    for (int i = 0; i * 32 < mc; i++) {
-      const unsigned sx = __shfl_sync(0xffffffffu, wd.x, i), sy = __shfl_sync(0xffffffffu, wd.y, i);
-      const int run = (int)sy + __popc(sx & le_not0);
-      const int off = __shfl_sync(0xffffffffu, row, run);
-      const int j = i * 32 + lane;
-      /* lanes past the end read a record of the last row's neighbourhood (the array is padded) and drop it */
-      const float4 p = __ldg(g.pts + (off + j));
-      const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
-      const bool pass = j < mc && d2 < R2;
-      const unsigned b = __ballot_sync(0xffffffffu, pass);
-      if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = encode(d2, __float_as_int(p.w));
-      n += __popc(b);
+    /* ---- candidates: rows of the (2h+1)^3 block trimmed to the ball, flattened, scanned. Everything is in cell
+     * units; the margins cover the rounding of this and of the build's cell assignment. ---- */
+    int h = 2, n = 0, attempt = 0, r0 = 0, nrows = 25;
+    int oy = oy5, oz = oz5;
+    float R2 = fp.R2, Rc2 = fp.Rc2;
+    bool give_up = false;
+    while (true) {
+      {
+        const int ry = cy + oy, rz = cz + oz;
+        const float dyc = fmaxf(fmaxf((float)oy - uy, uy - (float)(oy + 1)), 0.f);
+        const float dzc = fmaxf(fmaxf((float)oz - uz, uz - (float)(oz + 1)), 0.f);
+        const float t2 = Rc2 - dyc * dyc - dzc * dzc;
+        int st = 0, len = 0;
+        if (r0 + lane < nrows && (unsigned)ry < (unsigned)g.ny && (unsigned)rz < (unsigned)g.nz && t2 > 0.f) {
+          const float w = sqrt_approx(t2) * 1.0001f; /* half-width of the ball in this row, rounded up */
+          const int xa = max(__float2int_rd(fx - w), max(cx - h, 0)), xb = min(__float2int_rd(fx + w), min(cx + h, g.nx - 1));
+          if (xa <= xb) {
+            const uint32_t* cs = g.cell_start + (uint32_t)((rz * g.ny + ry) * g.nx); /* < 2^30 cells */
+            st = (int)__ldg(cs + xa);
+            len = (int)__ldg(cs + xb + 1) - st;
+          }
+        }
+        int incl = len;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int v = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += v;
+        }
+        const int mc = __shfl_sync(0xffffffffu, incl, 31);
+        if (mc > kFastMaxScan) { give_up = true; break; }
+        if (mc > 0) {
+          const int P = incl - len;
+          __syncwarp();
+          if (lane < kFastWords) ws.words[lane] = make_uint2(0u, 0u);
+          __syncwarp();
+          const unsigned nonempty = __ballot_sync(0xffffffffu, len > 0);
+          if (len > 0) {
+            const int d = __popc(nonempty & lt);
+            atomicOr(&ws.words[P >> 5].x, 1u << (P & 31));
+            ws.off[d] = st - P;
+#pragma unroll 1
+            for (int i = (P + 31) >> 5; i * 32 < P + len; i++) ws.words[i].y = (unsigned)d;
+          }
+          __syncwarp();
+          for (int i = 0; i * 32 < mc; i++) {
+            const int j = i * 32 + lane;
+            const uint2 w = ws.words[i];
+            const int run = (int)w.y + __popc(w.x & le_not0);
+            /* lanes past the end read a record behind the last row (the array is padded) and drop it */
+            const float4 p = __ldg(g.pts + (ws.off[run] + j));
+            const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+            const bool pass = j < mc && d2 < R2;
+            const unsigned b = __ballot_sync(0xffffffffu, pass);
+            /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
+            if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p.w));
+            n += __popc(b);
+          }
+        }
+      }
+      r0 += 32;
+      if (r0 >= nrows) {
+        if (n >= k && n <= kBuf) break;
+        /* rescale the radius by the count seen (count ~ r^3), widen the block if the exactness bound asks for it */
+        if (++attempt >= kFastAttempts || (n < k && !(R2 < io.cutoff2))) { give_up = true; break; }
+        R2 = fminf(R2 * pow23(__fdividef(1.3f * fk + 12.f, (float)max(n, k >> 2))), io.cutoff2);
+        const float Rc = sqrtf(R2) * g.inv_cell + 2.f * fp.margin_c;
+        h = max(__float2int_ru(Rc + 2.f * fp.margin_c), 2);
+        if (h > kFastMaxH) { give_up = true; break; }
+        Rc2 = Rc * Rc;
+        nrows = (2 * h + 1) * (2 * h + 1);
+        r0 = 0; n = 0;
+      }
+      {
+        const int row = r0 + lane, side = 2 * h + 1;
+        const int rzo = div_small(row, side);
+        oy = row - rzo * side - h; oz = rzo - h;
+      }
     }
-    if (n < k || n > kBuf) { /* the radius guess did not hold */
+    if (give_up) {
       if (lane == 0) ho_list[atomicAdd(ho_count, 1)] = qi;
       __syncwarp();
       continue;
     }
     __syncwarp();
 
-    /* ---- selection: histogram over dist²; the atomics' return values are positions inside a bin ---- */
+    /* ---- the k-th smallest dist²: histogram over [Ta, R2), bin 0 = everything expected below k - 3 sigma ---- */
     const int ns = (n + 31) >> 5;
-    uint64_t key[kSlots];
-    int bp[kSlots]; /* bin << 8 | position in the bin; bin 63 = empty slot */
-    int n0 = 0;
+    uint2 kv[kSlots];
+    int bp[kSlots]; /* bin << 8 | position in the bin */
+    {
+      const float2 wn = fp.win[n];
+      const float Ta = R2 * wn.x, scale = __fdividef(wn.y, R2);
 #pragma unroll
-    for (int s = 0; s < kSlots; s++) {
-      key[s] = 0; bp[s] = 63 << 8;
-      if (s < ns) {
-        const int idx = lane + 32 * s;
-        const bool valid = idx < n;
-        if (valid) key[s] = ws.keys[idx];
-        const float f = __uint_as_float((uint32_t)(key[s] >> 32));
-        const bool is0 = valid && f < Ta;
-        const unsigned b0 = __ballot_sync(0xffffffffu, is0);
-        if (is0) bp[s] = n0 + __popc(b0 & lt);
-        else if (valid) {
+      for (int s = 0; s < kSlots; s++) {
+        kv[s] = make_uint2(0xffffffffu, 0u);
+        bp[s] = 63 << 8;
+        if (s < ns && lane + 32 * s < n) {
+          kv[s] = ws.keys[lane + 32 * s];
           /* monotone in dist²: subtraction, multiplication by a positive constant, floor, clamp */
-          const int bin = min(__float2int_rd((f - Ta) * scale) + 1, 30);
+          const int bin = min(max(__float2int_rd((__uint_as_float(kv[s].x) - Ta) * scale) + 1, 0), 30);
           bp[s] = (bin << 8) | atomicAdd(&ws.hist[bin], 1);
         }
-        n0 += __popc(b0);
       }
     }
     __syncwarp();
-    const int cntb = lane == 0 ? n0 : ws.hist[lane]; /* hist[31] stays 0 */
+    const int cntb = ws.hist[lane]; /* hist[31] stays 0 */
     int incl = cntb;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -677,59 +629,62 @@ k_grid_fast(const GridView g, const float4* __restrict__ color4, const pmk::Quer
     const int kbin = __popc(__ballot_sync(0xffffffffu, incl < k)); /* first bin whose running count reaches k; n >= k */
     const int clo = __shfl_sync(0xffffffffu, incl - cntb, kbin);
     const int nb = __shfl_sync(0xffffffffu, cntb, kbin);
-    if (nb > 32) {
+    uint32_t tau = 0u;
+    bool exact = nb <= 32;
+    if (exact) {
+#pragma unroll
+      for (int s = 0; s < kSlots; s++)
+        if (s < ns && (bp[s] >> 8) == kbin) ws.bl[bp[s] & 255] = kv[s].x;
+      __syncwarp();
+      /* one member per lane: tau = the (k - clo)-th smallest of them */
+      const int need = k - clo;
+      const uint32_t mine = lane < nb ? ws.bl[lane] : 0xffffffffu;
+      int rank = 0;
+      for (int j = 0; j < nb; j++) rank += ws.bl[j] < mine;
+      tau = __reduce_max_sync(0xffffffffu, rank < need ? mine : 0u); /* lanes >= nb hold rank nb >= need */
+      exact = __popc(__ballot_sync(0xffffffffu, mine <= tau)) == need;
+    }
+    if (!exact) { /* over-full bin, or equal distances at the k-th place: the id order decides */
       if (lane == 0) ho_list[atomicAdd(ho_count, 1)] = qi;
       __syncwarp();
       continue;
     }
-    __syncwarp();
-    ws.hist[lane] = incl - cntb; /* first output position of every bin */
-    __syncwarp();
-#pragma unroll
-    for (int s = 0; s < kSlots; s++) {
-      if (s < ns) {
-        const int bin = bp[s] >> 8, pos = bp[s] & 255;
-        if (bin < kbin) ws.keys[ws.hist[bin] + pos] = key[s];
-        else if (bin == kbin) ws.bl[pos] = key[s];
-      }
-    }
-    __syncwarp();
-    /* the boundary bin: nb <= 32 candidates, one per lane, exact rank by 64-bit key */
-    uint64_t mine = ~0ull;
-    if (lane < nb) mine = ws.bl[lane];
-    int rank = 0;
-    for (int j = 0; j < nb; j++) rank += ws.bl[j] < mine;
-    const int need = k - clo;
-    const bool acc_b = lane < nb && rank < need;
-    if (acc_b) ws.keys[clo + rank] = mine;
-    const unsigned last = __ballot_sync(0xffffffffu, acc_b && rank == need - 1);
-    const float r2 = __uint_as_float((uint32_t)__shfl_sync(0xffffffffu, (int)(mine >> 32), __ffs(last) - 1));
-    __syncwarp();
 
-    /* ---- output: keys[0 .. k) ---- */
+    /* ---- output: every candidate with dist² <= tau, ballot-compacted ---- */
     if (!GATHER) {
-      int2* ids2 = reinterpret_cast<int2*>(io.ids + (size_t)qi * k);
-      float2* d22 = io.d2 ? reinterpret_cast<float2*>(io.d2 + (size_t)qi * k) : nullptr;
-      for (int p = 2 * lane; p < k; p += 64) {
-        const uint64_t e0 = ws.keys[p], e1 = ws.keys[p + 1];
-        ids2[p >> 1] = make_int2((int)(uint32_t)e0, (int)(uint32_t)e1);
-        if (d22) d22[p >> 1] = make_float2(__uint_as_float((uint32_t)(e0 >> 32)), __uint_as_float((uint32_t)(e1 >> 32)));
+      int32_t* ids = io.ids + (size_t)qi * k;
+      float* d2o = io.d2 ? io.d2 + (size_t)qi * k : nullptr;
+      int base = 0;
+#pragma unroll
+      for (int s = 0; s < kSlots; s++) {
+        if (s < ns) {
+          const bool a = kv[s].x <= tau;
+          const unsigned b = __ballot_sync(0xffffffffu, a);
+          if (a) {
+            const int p = base + __popc(b & lt);
+            ids[p] = (int32_t)kv[s].y;
+            if (d2o) d2o[p] = __uint_as_float(kv[s].x);
+          }
+          base += __popc(b);
+        }
       }
-      if (io.r2 && lane == 0) io.r2[qi] = r2;
+      if (io.r2 && lane == 0) io.r2[qi] = __uint_as_float(tau);
     } else {
       /* gatherPhotons (ray-tracer/cuda/shading.h:93-121), summed across the warp */
-      const float brdf = __ldg(io.brdf + qi);
+      const float r2 = __uint_as_float(tau);
       const float rad = __fsqrt_rn(r2);
       float fr = 0.f, fg = 0.f, fb = 0.f;
-      for (int p = lane; p < k; p += 32) {
-        const uint64_t e = ws.keys[p];
-        const float4 c = __ldg(color4 + (uint32_t)e);
-        const float dist = __fsqrt_rn(__uint_as_float((uint32_t)(e >> 32)));
-        const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
-        const float sc = __fmul_rn(__fmul_rn(brdf, c.w), w);
-        fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
-        fg = __fadd_rn(fg, __fmul_rn(sc, c.y));
-        fb = __fadd_rn(fb, __fmul_rn(sc, c.z));
+#pragma unroll
+      for (int s = 0; s < kSlots; s++) {
+        if (s < ns && kv[s].x <= tau) {
+          const float4 c = __ldg(color4 + kv[s].y);
+          const float dist = __fsqrt_rn(__uint_as_float(kv[s].x));
+          const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
+          const float sc = __fmul_rn(__fmul_rn(brdf, c.w), w);
+          fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
+          fg = __fadd_rn(fg, __fmul_rn(sc, c.y));
+          fb = __fadd_rn(fb, __fmul_rn(sc, c.z));
+        }
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
@@ -994,7 +949,7 @@ GridView view_of(const pm_map* m) {
 
 int host_cell_of(float v, float lo, float inv_cell) {
   const float u = (v - lo) * inv_cell; /* same float arithmetic as cell_of() */
-  return (int)std::floor(u);
+  return (int)std::floor(std::min(std::max(u, 0.f), 1e9f)); /* NaN / inf never reach the cast */
 }
 
 }  // namespace
@@ -1026,6 +981,13 @@ int cells_reorder(pm_ctx* ctx, pm_map* m) {
   return PM_OK;
 }
 
+/* candidates expected inside the first radius: a k + b (tuning knobs PM_FAST_EK_A / PM_FAST_EK_B, read once) */
+static float fast_expected_count(int k) {
+  static const float a = getenv("PM_FAST_EK_A") ? (float)atof(getenv("PM_FAST_EK_A")) : 1.25f;
+  static const float b = getenv("PM_FAST_EK_B") ? (float)atof(getenv("PM_FAST_EK_B")) : 10.f;
+  return a * (float)k + b;
+}
+
 int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
   const bool given = cell_size > 0.f; /* cells-only map: the caller names the cell, nothing is sampled (there is no tree) */
   if (!given && m->n < kMinGridNodes) return PM_OK;
@@ -1054,9 +1016,20 @@ int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
      * distributions (uniform clouds) take the 98th percentile plus a little; broad ones would pay
      * for their tail in every dense neighbourhood, so they take the 90th and leave the rest to the
      * kd-tree kernel. */
-    rk = r98 < 1.25f * r50 ? r98 * 1.03f : std::sqrt(r2[(size_t)(ns * 0.90)]);
-    cell = 0.5f * rk;
     uniform_like = r98 < 1.25f * r50;
+    rk = uniform_like ? r98 * 1.03f : std::sqrt(r2[(size_t)(ns * 0.90)]);
+    cell = 0.5f * rk;
+    /* degenerate cloud (most sampled neighbourhoods are coincident photons): kd-tree kernels only */
+    if (!(cell > 0.f) || !std::isfinite(cell)) return PM_OK;
+    m->tuned_r50 = r50;
+    if (uniform_like) {
+      /* the fast path starts every query at the radius expected to hold 1.25 kTuneK + 10 photons and needs two
+       * cells (less the margins) to cover it: see fast_first_radius2 */
+      float maxabs0 = 0.f;
+      for (int d = 0; d < 6; d++) maxabs0 = std::max(maxabs0, std::fabs(m->bounds[d]));
+      const float r_first = r50 * std::cbrt(fast_expected_count(kTuneK) / ((float)kTuneK - 0.33f));
+      cell = (0.5f * r_first + 2.f * 16.f * FLT_EPSILON * maxabs0) / (1.f - 2.5e-3f);
+    }
   }
   float maxabs = 0.f;
   for (int d = 0; d < 3; d++) {
@@ -1113,31 +1086,46 @@ int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
   return PM_OK;
 }
 
+/* first search radius² of the fast path for k neighbours: the radius expected to hold 1.25 k + 10 photons, from the
+ * sampled median distance to the kTuneK-th neighbour (volume ~ count), capped by what a 5x5x5 block guarantees */
+static float fast_first_radius2(const pm_map* m, int k, float cutoff2) {
+  const float ek = fast_expected_count(k);
+  const float r = m->tuned_r50 * std::cbrt(ek / ((float)kTuneK - 0.33f));
+  const float rmax = 2.f * m->cell - 4.f * m->cell_margin;
+  const float rr = std::min(r, rmax);
+  return std::min(rr * rr, cutoff2);
+}
+
 int grid_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gather, int* fb_list, int* fb_count) {
   const GridView g = view_of(map);
   const int64_t cap = (int64_t)ctx->sm_count * 64;
-  if (map->fast_path && io.k <= kBuf / 2) {
-    /* uniform-like cloud: descriptor pass + streaming kernel, k_grid_query only for the handed-over queries */
+  if (map->fast_path && io.sq && io.k <= kBuf / 2) {
+    /* uniform-like cloud: k_knn_fast, k_grid_query only for the handed-over queries */
     int *ho_list = nullptr, *ho_count = nullptr;
-    FastDesc* desc = nullptr;
-    PM_CHECK(ctx->get_scratch(pm::S_FAST0, (size_t)std::min<int64_t>(io.nq, kFastChunk), &desc));
     PM_CHECK(ctx->get_scratch(pm::S_FAST1, (size_t)io.nq, &ho_list));
     PM_CHECK(ctx->get_scratch(pm::S_FAST2, (size_t)4, &ho_count));
     PM_CUDA(cudaMemsetAsync(ho_count, 0, sizeof(int), ctx->stream));
-    for (int64_t t0 = 0; t0 < io.nq; t0 += kFastChunk) {
-      const int cnt = (int)std::min<int64_t>(kFastChunk, io.nq - t0);
-      k_fast_prep<<<(unsigned)div_up(cnt, kPrepBlock), kPrepBlock, 0, ctx->stream>>>(g, io, (int)t0, cnt, desc);
-      const unsigned grid = (unsigned)std::min<int64_t>(div_up(cnt, kWarps), cap);
-      if (gather) k_grid_fast<true><<<grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, desc, cnt, ho_list, ho_count);
-      else k_grid_fast<false><<<grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, desc, cnt, ho_list, ho_count);
-      ctx->launches += 2;
+    FastParams fp;
+    fp.sq = io.sq;
+    fp.R2 = fast_first_radius2(map, io.k, io.cutoff2);
+    fp.margin_c = map->cell_margin * map->inv_cell;
+    const float rc = std::sqrt(fp.R2) * map->inv_cell + 2.f * fp.margin_c;
+    fp.Rc2 = rc * rc;
+    for (int n = 0; n < kWinSize; n++) {
+      const float fk = (float)io.k, fn = (float)std::max(n, io.k);
+      const float delta = 3.f * std::sqrt(fk * (1.f - fk / fn)) + 2.f;
+      const float x = std::pow(std::max(fk - delta, 0.5f) / fn, 2.f / 3.f);
+      fp.win[n] = make_float2(x, 30.f / (1.f - x));
     }
+    const unsigned fgrid = (unsigned)std::min<int64_t>(div_up(io.nq, kWarps), (int64_t)ctx->sm_count * 6 * 4);
+    if (gather) k_knn_fast<true><<<fgrid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fp, ho_list, ho_count);
+    else k_knn_fast<false><<<fgrid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fp, ho_list, ho_count);
     pmk::QueryIO rest = io;
     rest.order = ho_list;
     const unsigned grid = (unsigned)std::min<int64_t>(div_up(io.nq, kWarps), (int64_t)ctx->sm_count * 8);
     if (gather) k_grid_query<true><<<grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, rest, ho_count, fb_list, fb_count);
     else k_grid_query<false><<<grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, rest, ho_count, fb_list, fb_count);
-    ctx->launches++;
+    ctx->launches += 2;
     ctx->ho_count_dev = ho_count;
     PM_CUDA(cudaGetLastError());
     return PM_OK;

@@ -71,6 +71,8 @@ struct pm_ctx {
   int sm_count = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev_order = nullptr;   /* pm_ctx_wait_stream */
+  int* host_counts = nullptr;       /* pinned: [0] kd-tree fallbacks, [1] hand-overs of the last query call */
   /* second stream + events for the chunked host-buffer pipeline of pm_knn (created on first use) */
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_kernel[2] = {nullptr, nullptr}, ev_copy[2] = {nullptr, nullptr};
@@ -125,7 +127,8 @@ struct pm_map {
   float cell = 0.f, inv_cell = 0.f, cell_margin = 0.f;
   int gdim[3] = {0, 0, 0};
   float tuned_rk = 0.f;                      /* sampled k-th neighbour distance the cell size came from */
-  bool fast_path = false;                    /* uniform-like cloud: k_fast_prep + k_grid_fast answer most queries */
+  float tuned_r50 = 0.f;                     /* median of the sampled distances to the 64th neighbour */
+  bool fast_path = false;                    /* uniform-like cloud: k_knn_fast answers most queries */
   bool cells_only = false;                   /* pm_map_build_cells: input order, no kd-tree; fixed-radius gathers only */
 };
 

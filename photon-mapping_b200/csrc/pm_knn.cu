@@ -1,4 +1,4 @@
-/* pm_knn.cu — stage 3: k-nearest-photon search and the fused radiance estimate.
+/* pm_knn.cu — stage 3 entry points: k-nearest-photon search and the fused radiance estimate.
  *
  * Replaces cukd::stackBased::knn<HeapCandidateList<k>> (externals/cudaKDTree/cukd/knn.h:298-364,
  * 536-549; traverse-default-stack-based.h:24-90) as instantiated by
@@ -8,26 +8,17 @@
  * nodes with dist² < cutoff²; dist² = fma(dz,dz, fma(dx,dx, dy*dy)), d = node - query
  * (the contraction nvcc emits for cukd's dot(d,d) in the reference kernel).
  *
- * B200 design (v1):
- *   - queries are Morton-sorted (24-bit code inside the map's AABB, radix sort of 4-byte ids) so the
- *     32 lanes of a warp walk nearly the same root-to-leaf paths: node fetches coalesce into a few
- *     sectors and the traversal stays convergent;
- *   - the tree is traversed through a 16-byte (x, y, z, split_dim) copy — one LDG.128 per node
- *     instead of a 44-byte-stride AoS access;
- *   - the candidate heap lives in shared memory, laid out [slot][thread] so that every heap access
- *     of a warp hits 32 distinct banks no matter which slot each lane touches (the reference's
- *     per-thread uint64[k] array is dynamically indexed and therefore spills to local memory);
- *     the heap root is mirrored in a register so the common "reject" case costs one compare.
+ * This file holds the query ordering (a counting sort of the queries into 2^21 Morton bins of the map's box, so
+ * that the warps of a CTA work on neighbouring queries and share their candidate rows in L1/L2), the pipelined
+ * host-buffer variant of pm_knn and the ABI entry points. The kernels that answer the queries live in
+ * pm_grid.cu (uniform grid, one warp per query) and pm_kdwarp.cu (warp-cooperative kd-tree walk).
  */
-#include <cub/cub.cuh>
 #include <cfloat>
 #include "pm_knn.cuh"
 
 namespace {
 
 using pmk::encode;
-
-constexpr int kBlock = 128;
 
 /* expands 10 bits into every third bit */
 __device__ __forceinline__ uint32_t part1by2(uint32_t v) {
@@ -41,197 +32,164 @@ __device__ __forceinline__ uint32_t part1by2(uint32_t v) {
 
 struct Box6 { float lo[3]; float inv[3]; };
 
-__global__ void k_morton(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int nq, Box6 box,
-                         uint32_t* __restrict__ keys, int* __restrict__ ids) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nq) return;
-  ids[i] = i;
-  /* queries that will not be evaluated (brdf <= 0) sort to the end so that whole warps retire at once */
-  if (skip_if_not_positive && !(skip_if_not_positive[i] > 0.f)) { keys[i] = 0x00FFFFFFu; return; }
+/* ---- query ordering: counting sort into Morton bins ------------------------------------------------
+ * 7 bits per axis inside the map's box (queries outside are clamped onto its faces) + one last bin for queries that
+ * will not be evaluated (brdf <= 0), so whole warps retire at once. Three kernels: histogram (one global atomic per
+ * query, the last bin warp-aggregated), exclusive scan of the 2^21 + 1 counters (single pass, decoupled look-back),
+ * scatter (the atomic's return value is the slot inside the bin). The order inside a bin is whatever the atomics
+ * hand out; results do not depend on it. */
+constexpr int kQBits = 7;
+constexpr int kQBins = (1 << (3 * kQBits)) + 1;
+constexpr int kScanTile = 2048;                       /* counters per CTA of the scan: 256 threads x 8 */
+constexpr int kScanTiles = (kQBins + kScanTile - 1) / kScanTile;
+
+__device__ __forceinline__ uint32_t bin_of(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int i,
+                                           const Box6& box) {
+  if (skip_if_not_positive && !(skip_if_not_positive[i] > 0.f)) return (uint32_t)(kQBins - 1);
   uint32_t code = 0;
 #pragma unroll
   for (int d = 0; d < 3; d++) {
     float t = (q[(size_t)i * 3 + d] - box.lo[d]) * box.inv[d];
-    t = fminf(fmaxf(t, 0.f), 255.f);
+    t = fminf(fmaxf(t, 0.f), (float)((1 << kQBits) - 1)); /* drops NaN */
     code |= part1by2((uint32_t)t) << d;
   }
-  keys[i] = code;
+  return code;
 }
 
-/* Shared-memory max-heap of uint64 entries, one column per thread. */
-template <int K>
-struct SmemHeap {
-  uint64_t* col;  /* &heap[0][threadIdx.x]; slot s is col[s * kBlock] */
-  uint64_t top;   /* register mirror of slot 0 */
-
-  __device__ __forceinline__ void init(uint64_t* base, float cutoff2) {
-    col = base + threadIdx.x;
-    top = encode(cutoff2, -1);
-#pragma unroll 8
-    for (int s = 0; s < K; s++) col[s * kBlock] = top;
-  }
-  __device__ __forceinline__ float max_dist2() const { return __uint_as_float((uint32_t)(top >> 32)); }
-  /* cukd HeapCandidateList::push (knn.h:327-359): replace the root, sift down */
-  __device__ __forceinline__ void push(float d2, int id) {
-    const uint64_t e = encode(d2, id);
-    if (e >= top) return;
-    int pos = 0;
-    uint64_t new_top = e;
-    while (true) {
-      const int c0 = 2 * pos + 1;
-      if (c0 >= K) break;
-      uint64_t v = col[c0 * kBlock];
-      int c = c0;
-      if (c0 + 1 < K) {
-        const uint64_t v1 = col[(c0 + 1) * kBlock];
-        if (v1 > v) { v = v1; c = c0 + 1; }
-      }
-      if (v < e) break;
-      col[pos * kBlock] = v;
-      if (pos == 0) new_top = v;
-      pos = c;
-    }
-    col[pos * kBlock] = e;
-    top = new_top;
-  }
-};
-
-/* stack-based traversal, literal in its visiting order (traverse-default-stack-based.h:49-88) */
-template <int K>
-__device__ __forceinline__ void traverse(const float4* __restrict__ nodes, int n, float qx, float qy, float qz,
-                                         SmemHeap<K>& heap) {
-  struct Entry { int node; float d2; };
-  Entry stack[32];
-  int sp = 0;
-  int curr = 0;
-  float cull = heap.max_dist2();
-  while (true) {
-    while (curr < n) {
-      const float4 nd = __ldg(nodes + curr);
-      const int dim = __float_as_int(nd.w);
-      const float dx = nd.x - qx, dy = nd.y - qy, dz = nd.z - qz;
-      const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-      heap.push(d2, curr);
-      cull = heap.max_dist2();
-      const float dp = dim == 0 ? -dx : (dim == 1 ? -dy : -dz); /* query - node along the split axis */
-      const bool left_close = dp < 0.f;
-      const int l = 2 * curr + 1;
-      const int close_child = left_close ? l : l + 1;
-      const int far_child = left_close ? l + 1 : l;
-      const float plane2 = __fmul_rn(dp, dp);
-      if (plane2 < cull && far_child < n) { stack[sp].node = far_child; stack[sp].d2 = plane2; sp++; }
-      curr = close_child;
-    }
-    bool found = false;
-    while (sp > 0) {
-      --sp;
-      if (stack[sp].d2 >= cull) continue;
-      curr = stack[sp].node;
-      found = true;
-      break;
-    }
-    if (!found) return;
-  }
+__global__ void k_qbin_count(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int nq, Box6 box,
+                             uint32_t* __restrict__ codes, uint32_t* __restrict__ hist) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool in = i < nq;
+  const uint32_t code = in ? bin_of(q, skip_if_not_positive, i, box) : 0u;
+  if (in) codes[i] = code;
+  const bool last = in && code == (uint32_t)(kQBins - 1);
+  const unsigned lb = __ballot_sync(0xffffffffu, last);
+  if (last) { if ((threadIdx.x & 31) == __ffs(lb) - 1) atomicAdd(hist + code, (uint32_t)__popc(lb)); }
+  else if (in) atomicAdd(hist + code, 1u);
 }
 
-/* one thread per query; with `list` the queries are list[0 .. *list_count), else order[t] (or t) */
-template <int K, bool GATHER>
-__global__ void __launch_bounds__(kBlock)
-k_kd(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n, pmk::QueryIO io,
-     const int* __restrict__ list, const int* __restrict__ list_count) {
-  extern __shared__ uint64_t smem_heap[];
-  const int total = list ? *list_count : io.nq;
-  for (int t = blockIdx.x * kBlock + threadIdx.x; t < total; t += gridDim.x * kBlock) {
-    const int qi = list ? list[t] : (io.order ? io.order[t] : t);
-    float f = 0.f;
-    if (GATHER) {
-      f = io.brdf[qi];
-      if (!(f > 0.f)) { /* flux = brdf * ... is +0 for brdf == 0; negative marks "no query" (render pipeline) */
-        io.rgb[(size_t)qi * 3 + 0] = 0.f; io.rgb[(size_t)qi * 3 + 1] = 0.f; io.rgb[(size_t)qi * 3 + 2] = 0.f;
-        continue;
-      }
-    }
-    SmemHeap<K> heap;
-    heap.init(smem_heap, io.cutoff2);
-    const float qx = io.q[(size_t)qi * 3 + 0], qy = io.q[(size_t)qi * 3 + 1], qz = io.q[(size_t)qi * 3 + 2];
-    traverse<K>(nodes, n, qx, qy, qz, heap);
-    if (!GATHER) {
-      if (io.r2) io.r2[qi] = heap.max_dist2();
-      if (io.ids) {
-        /* each thread streams its own row; K is even so rows are 8-byte aligned */
-        int2* ids2 = reinterpret_cast<int2*>(io.ids + (size_t)qi * K);
-        float2* d22 = io.d2 ? reinterpret_cast<float2*>(io.d2 + (size_t)qi * K) : nullptr;
-#pragma unroll 4
-        for (int s = 0; s < K; s += 2) {
-          const uint64_t a = heap.col[s * kBlock], b = heap.col[(s + 1) * kBlock];
-          ids2[s >> 1] = make_int2((int)(uint32_t)a, (int)(uint32_t)b);
-          if (d22) d22[s >> 1] = make_float2(__uint_as_float((uint32_t)(a >> 32)), __uint_as_float((uint32_t)(b >> 32)));
-        }
-      }
+/* in place: counts -> exclusive offsets. status[t] = flag << 32 | value with flag 1 = the tile's own sum, 2 = the
+ * inclusive sum up to and including the tile; tiles take their number from a counter so that a tile never waits for
+ * one that has not started */
+__global__ void __launch_bounds__(256)
+k_qbin_scan(uint32_t* __restrict__ hist, int nbins, unsigned long long* __restrict__ status, int* __restrict__ tile_counter) {
+  __shared__ int s_tile;
+  __shared__ uint32_t s_warp[8];
+  __shared__ uint32_t s_prefix;
+  if (threadIdx.x == 0) s_tile = atomicAdd(tile_counter, 1);
+  __syncthreads();
+  const int tile = s_tile;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int base = tile * kScanTile + threadIdx.x * 8;
+  uint32_t v[8];
+#pragma unroll
+  for (int e = 0; e < 8; e++) v[e] = base + e < nbins ? hist[base + e] : 0u;
+  uint32_t sum = 0;
+#pragma unroll
+  for (int e = 0; e < 8; e++) sum += v[e];
+  uint32_t incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += u;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  uint32_t wbase = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < 8; w++) {
+    if (w < warp) wbase += s_warp[w];
+    total += s_warp[w];
+  }
+  if (warp == 0) {
+    uint32_t prefix = 0;
+    if (tile == 0) {
+      if (lane == 0) atomicExch(status, (2ull << 32) | total);
     } else {
-      /* gatherPhotons (shading.h:93-121); arithmetic as written there, one rounding per op */
-      const float r2 = heap.max_dist2();
-      const float rad = __fsqrt_rn(r2);
-      float fr = 0.f, fg = 0.f, fb = 0.f;
-      for (int s = 0; s < K; s++) {
-        const int id = (int)(uint32_t)heap.col[s * kBlock];
-        if (id < 0 || id > n) continue; /* sic, shading.h:105 */
-        const float4 p = __ldg(nodes + id);
-        const float4 c = __ldg(color4 + id);
-        const float dx = p.x - qx, dy = p.y - qy, dz = p.z - qz;
-        const float dist = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
-        const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
-        const float sc = __fmul_rn(__fmul_rn(f, c.w), w);
-        fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
-        fg = __fadd_rn(fg, __fmul_rn(sc, c.y));
-        fb = __fadd_rn(fb, __fmul_rn(sc, c.z));
+      if (lane == 0) atomicExch(status + tile, (1ull << 32) | total);
+      /* look back 32 tiles at a time */
+      int first = tile - 1;
+      while (true) {
+        const int tt = first - lane;
+        unsigned long long st = 0;
+        bool ready;
+        do {
+          st = tt >= 0 ? *((volatile unsigned long long*)(status + tt)) : (2ull << 32);
+          ready = (st >> 32) != 0;
+        } while (!__all_sync(0xffffffffu, ready));
+        const unsigned full = __ballot_sync(0xffffffffu, (st >> 32) == 2);
+        /* lanes up to and including the nearest tile with an inclusive sum contribute */
+        const int stop = full ? __ffs(full) - 1 : 32;
+        uint32_t c = lane <= stop ? (uint32_t)st : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        prefix += c;
+        if (full) break;
+        first -= 32;
       }
-      const float k1 = (1 - (2.f / 3.f) * (1.f / 1.1f));
-      const float denom = __fmul_rn(__fmul_rn(__fmul_rn(k1, 2.f), 3.14159274101257324f), r2);
-      io.rgb[(size_t)qi * 3 + 0] = __fdiv_rn(fr, denom);
-      io.rgb[(size_t)qi * 3 + 1] = __fdiv_rn(fg, denom);
-      io.rgb[(size_t)qi * 3 + 2] = __fdiv_rn(fb, denom);
+      if (lane == 0) atomicExch(status + tile, (2ull << 32) | (prefix + total));
     }
-    __syncwarp();
+    if (lane == 0) s_prefix = prefix;
+  }
+  __syncthreads();
+  uint32_t run = s_prefix + wbase + incl - sum;
+#pragma unroll
+  for (int e = 0; e < 8; e++) {
+    if (base + e < nbins) hist[base + e] = run;
+    run += v[e];
   }
 }
 
-/* Morton order of the queries inside the map's box → permutation in scratch slot S_PERM */
-int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float* brdf_dev, int nq, int** perm_out) {
-  uint32_t *keys_in, *keys_out; int *ids_in, *perm;
-  PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)nq, &keys_in));
-  PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)nq, &keys_out));
-  PM_CHECK(ctx->get_scratch(pm::S_VALS0, (size_t)nq, &ids_in));
+__global__ void k_qbin_scatter(const float* __restrict__ q, const uint32_t* __restrict__ codes, int nq,
+                               uint32_t* __restrict__ cursor, int* __restrict__ perm, float4* __restrict__ sq) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool in = i < nq;
+  const uint32_t code = in ? codes[i] : 0u;
+  const bool last = in && code == (uint32_t)(kQBins - 1);
+  const unsigned lb = __ballot_sync(0xffffffffu, last);
+  uint32_t pos = 0;
+  if (last) {
+    const int leader = __ffs(lb) - 1;
+    if ((threadIdx.x & 31) == leader) pos = atomicAdd(cursor + code, (uint32_t)__popc(lb));
+    pos = __shfl_sync(lb, pos, leader) + __popc(lb & ((1u << (threadIdx.x & 31)) - 1u));
+  } else if (in) {
+    pos = atomicAdd(cursor + code, 1u);
+  }
+  if (in) {
+    perm[pos] = i;
+    if (sq) sq[pos] = make_float4(q[(size_t)i * 3 + 0], q[(size_t)i * 3 + 1], q[(size_t)i * 3 + 2], __int_as_float(i));
+  }
+}
+
+/* Morton-bin order of the queries inside the map's box -> permutation in scratch slot S_PERM and, with `sq_out`, the
+ * queries themselves in that order as float4 (x, y, z, bits(index)) in S_VALS1 */
+int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float* brdf_dev, int nq, int** perm_out,
+                 float4** sq_out) {
+  uint32_t *codes, *hist; int* perm; float4* sq = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)nq, &codes));
   PM_CHECK(ctx->get_scratch(pm::S_PERM, (size_t)nq, &perm));
+  if (sq_out) PM_CHECK(ctx->get_scratch(pm::S_VALS1, (size_t)nq, &sq));
+  /* counters, then the scan's tile states and its tile counter: one memset */
+  const size_t hist_words = ((size_t)kQBins + 3) & ~(size_t)3;
+  const size_t bytes = hist_words * 4 + (size_t)kScanTiles * 8 + 16;
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS1, bytes, &hist));
+  unsigned long long* status = reinterpret_cast<unsigned long long*>(hist + hist_words);
+  int* tile_counter = reinterpret_cast<int*>(status + kScanTiles);
+  PM_CUDA(cudaMemsetAsync(hist, 0, bytes, ctx->stream));
   Box6 box;
   for (int d = 0; d < 3; d++) {
     box.lo[d] = map->bounds[d];
     const float w = map->bounds[3 + d] - map->bounds[d];
-    box.inv[d] = w > 0.f ? 256.f / w : 0.f;
+    box.inv[d] = w > 0.f ? (float)(1 << kQBits) / w : 0.f;
   }
-  k_morton<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, keys_in, ids_in);
-  size_t tb = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tb, keys_in, keys_out, ids_in, perm, nq, 0, 24, ctx->stream);
-  void* tmp = nullptr;
-  PM_CHECK(ctx->get_scratch(pm::S_CUB, tb, &tmp));
-  PM_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, keys_in, keys_out, ids_in, perm, nq, 0, 24, ctx->stream));
-  ctx->launches += 6; /* k_morton + histogram + scan + 3 onesweep passes */
-  *perm_out = perm;
-  return PM_OK;
-}
-
-template <int K, bool GATHER>
-int launch_kd(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, const int* list, const int* list_count) {
-  const size_t smem = sizeof(uint64_t) * K * kBlock;
-  PM_CUDA(cudaFuncSetAttribute(k_kd<K, GATHER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  /* a list of unknown (device-side) length is served by a fixed, persistent grid */
-  int64_t grid = pm::div_up(io.nq, kBlock);
-  const int64_t cap = (int64_t)ctx->sm_count * (list ? 2 : 64);
-  if (grid > cap) grid = cap;
-  if (grid < 1) grid = 1;
-  k_kd<K, GATHER><<<(unsigned)grid, kBlock, smem, ctx->stream>>>(map->nodes4, map->color4, (int)map->n, io, list, list_count);
-  ctx->launches++;
+  const unsigned grid = (unsigned)pm::div_up(nq, 256);
+  k_qbin_count<<<grid, 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, codes, hist);
+  k_qbin_scan<<<kScanTiles, 256, 0, ctx->stream>>>(hist, kQBins, status, tile_counter);
+  k_qbin_scatter<<<grid, 256, 0, ctx->stream>>>(q_dev, codes, nq, hist, perm, sq);
+  ctx->launches += 3;
   PM_CUDA(cudaGetLastError());
+  *perm_out = perm;
+  if (sq_out) *sq_out = sq;
   return PM_OK;
 }
 
@@ -267,28 +225,18 @@ __global__ void k_bounds(const float4* __restrict__ nodes, int n, uint32_t* __re
   }
 }
 
-template <bool GATHER>
-int dispatch_kd(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, const int* list, const int* list_count) {
-  switch (io.k) {
-    case 8: return launch_kd<8, GATHER>(ctx, map, io, list, list_count);
-    case 16: return launch_kd<16, GATHER>(ctx, map, io, list, list_count);
-    case 32: return launch_kd<32, GATHER>(ctx, map, io, list, list_count);
-    case 50: return launch_kd<50, GATHER>(ctx, map, io, list, list_count);
-    case 64: return launch_kd<64, GATHER>(ctx, map, io, list, list_count);
-    default: pm::set_error("k must be one of 8, 16, 32, 50, 64 (got %d)", io.k); return PM_ERR_UNSUPPORTED;
-  }
-}
-
-/* answers one batch on device pointers: Morton order, grid kernel, kd-tree kernel for the rest */
+/* answers one batch on device pointers: Morton-bin order, grid kernels, kd-tree kernel for the rest. The event pair
+ * (time_it) brackets the whole batch, ordering pass included. */
 int run_queries(pm_ctx* ctx, const pm_map* map, pmk::QueryIO io, bool gather, bool time_it) {
+  if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   int* perm = nullptr;
-  PM_CHECK(sort_queries(ctx, map, io.q, gather ? io.brdf : nullptr, io.nq, &perm));
+  float4* sq = nullptr;
+  PM_CHECK(sort_queries(ctx, map, io.q, gather ? io.brdf : nullptr, io.nq, &perm, map->fast_path ? &sq : nullptr));
   io.order = perm;
+  io.sq = sq;
   ctx->fb_count_dev = nullptr;
   ctx->ho_count_dev = nullptr;
-  if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
-  static const bool kd_only = getenv("PM_KD_ONLY") != nullptr; /* measurement knob: every query through the kd-tree kernel */
-  if (map->grid_pts && !kd_only) {
+  if (map->grid_pts) {
     int *fb_list = nullptr, *fb_count = nullptr;
     PM_CHECK(ctx->get_scratch(pm::S_MISC1, (size_t)io.nq, &fb_list));
     PM_CHECK(ctx->get_scratch(pm::S_MISC2, (size_t)4, &fb_count));
@@ -303,16 +251,17 @@ int run_queries(pm_ctx* ctx, const pm_map* map, pmk::QueryIO io, bool gather, bo
   return PM_OK;
 }
 
-/* end of a synchronous query call: wait, then read the kernel time and the fallback count */
+/* end of a synchronous query call: the two counters travel to pinned host memory on the stream, one wait, then the
+ * kernel time */
 int finish_stats(pm_ctx* ctx, const pm_map* map) {
-  int fb = 0, ho = 0;
   const bool have = map && map->n >= 1;
-  if (have && ctx->fb_count_dev) PM_CUDA(cudaMemcpyAsync(&fb, ctx->fb_count_dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-  if (have && ctx->ho_count_dev) PM_CUDA(cudaMemcpyAsync(&ho, ctx->ho_count_dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  ctx->host_counts[0] = ctx->host_counts[1] = 0;
+  if (have && ctx->fb_count_dev) PM_CUDA(cudaMemcpyAsync(ctx->host_counts, ctx->fb_count_dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  if (have && ctx->ho_count_dev) PM_CUDA(cudaMemcpyAsync(ctx->host_counts + 1, ctx->ho_count_dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   PM_CUDA(cudaStreamSynchronize(ctx->stream));
   if (have) PM_CUDA(cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev0, ctx->ev1));
-  ctx->last_fallbacks = have && ctx->fb_count_dev ? fb : (have ? -1 : 0);
-  ctx->last_handovers = have && ctx->ho_count_dev ? ho : 0;
+  ctx->last_fallbacks = have && ctx->fb_count_dev ? ctx->host_counts[0] : (have ? -1 : 0);
+  ctx->last_handovers = have && ctx->ho_count_dev ? ctx->host_counts[1] : 0;
   return PM_OK;
 }
 
@@ -363,11 +312,7 @@ int knn_pipelined(pm_ctx* ctx, const pm_map* map, const float* q_dev, int64_t nq
 namespace pm {
 
 int kd_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gather, const int* list, const int* list_count) {
-  /* the warp-cooperative kernel answers everything; the per-thread restatement of cukd's traversal stays
-   * selectable (PM_KD_KERNEL=thread) as the literal reference order */
-  static const bool per_thread = getenv("PM_KD_KERNEL") && !strcmp(getenv("PM_KD_KERNEL"), "thread");
-  if (!per_thread) return kdw_query(ctx, map, io, gather, list, list_count);
-  return gather ? dispatch_kd<true>(ctx, map, io, list, list_count) : dispatch_kd<false>(ctx, map, io, list, list_count);
+  return kdw_query(ctx, map, io, gather, list, list_count);
 }
 
 int map_bounds(pm_ctx* ctx, pm_map* m) {
@@ -488,7 +433,7 @@ int pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const flo
     PM_CUDA(cudaMemsetAsync(oc.dev, 0, sizeof(int32_t) * (size_t)nq, ctx->stream));
   } else {
     int* perm = nullptr;
-    PM_CHECK(sort_queries(ctx, map, (const float*)h_dev, (const float*)b_dev, (int)nq, &perm));
+    PM_CHECK(sort_queries(ctx, map, (const float*)h_dev, (const float*)b_dev, (int)nq, &perm, nullptr));
     int *fb_list = nullptr, *fb_count = nullptr;
     PM_CHECK(ctx->get_scratch(pm::S_MISC1, (size_t)nq, &fb_list));
     PM_CHECK(ctx->get_scratch(pm::S_MISC2, (size_t)4, &fb_count));

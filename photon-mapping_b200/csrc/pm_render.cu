@@ -242,12 +242,13 @@ __global__ void k_end_sample(Chunk c) {
 /* make_8bit / make_rgba (owl_device.h:81-93): int(f * 256.f) is cvt.rzi (NaN -> 0, saturating) */
 __device__ __forceinline__ uint32_t make_8bit(float f) { return (uint32_t)min(255, max(0, __float2int_rz(f * 256.f))); }
 
-__global__ void k_write(Chunk c, int spp, uint32_t* __restrict__ fb) {
+__global__ void k_write(Chunk c, int spp, uint32_t* __restrict__ fb, float* __restrict__ rgb) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= c.count) return;
   const int64_t p = c.begin + i;
   const int px = (int)(p % c.W), py = (int)(p / c.W);
   const vec3 col = xyz(c.final_c[i]) * __fdiv_rn(1.f, (float)spp);
+  if (rgb) { rgb[3 * p] = col.x; rgb[3 * p + 1] = col.y; rgb[3 * p + 2] = col.z; } /* by launch index px + W * py */
   const int y = c.H - py; /* deviceCode.cu:224-227; row H (py == 0) is out of bounds and is not written */
   if (y >= c.H) return;
   fb[(size_t)px + (size_t)c.W * y] = (make_8bit(col.x) << 0) + (make_8bit(col.y) << 8) + (make_8bit(col.z) << 16) + (0xffu << 24);
@@ -260,6 +261,13 @@ extern "C" {
 int pm_render(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_lights, const pm_map* global_map,
               const pm_map* caustic_map, const pm_camera* camera, int width, int height, int spp, int depth,
               const float sky[3], int64_t pixel_begin, int64_t pixel_end, uint32_t* fb) {
+  return pm_render_rgb(ctx, scene, lights, n_lights, global_map, caustic_map, camera, width, height, spp, depth, sky,
+                       pixel_begin, pixel_end, fb, nullptr);
+}
+
+int pm_render_rgb(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_lights, const pm_map* global_map,
+                  const pm_map* caustic_map, const pm_camera* camera, int width, int height, int spp, int depth,
+                  const float sky[3], int64_t pixel_begin, int64_t pixel_end, uint32_t* fb, float* rgb_linear) {
   PM_REQUIRE(ctx && scene && camera && sky && fb, "ctx/scene/camera/sky/fb is NULL");
   PM_REQUIRE((!global_map || !global_map->cells_only) && (!caustic_map || !caustic_map->cells_only),
              "maps built by pm_map_build_cells carry no kd-tree: fixed-radius gathers only");
@@ -282,6 +290,13 @@ int pm_render(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_
   if (!fb_dev) {
     PM_CHECK(ctx->get_scratch(pm::S_STAGE_OUT0, (size_t)width * height, &fb_d));
     PM_CUDA(cudaMemcpyAsync(fb_d, fb, fb_bytes, cudaMemcpyHostToDevice, st)); /* keep what other tiles wrote */
+  }
+  const size_t rgb_bytes = sizeof(float) * 3 * (size_t)width * height;
+  const bool rgb_dev = !rgb_linear || pm::is_device_ptr(rgb_linear);
+  float* rgb_d = rgb_linear;
+  if (!rgb_dev) {
+    PM_CHECK(ctx->get_scratch(pm::S_STAGE_OUT1, (size_t)3 * width * height, &rgb_d));
+    PM_CUDA(cudaMemcpyAsync(rgb_d, rgb_linear, rgb_bytes, cudaMemcpyHostToDevice, st)); /* keep other tiles' pixels */
   }
   const int64_t total = pixel_end - pixel_begin;
   const int64_t chunk_max = (int64_t)1 << 21;
@@ -332,12 +347,13 @@ int pm_render(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_
         k_end_sample<<<nb, 128, 0, st>>>(c);
         ctx->launches++;
       }
-      k_write<<<nb, 128, 0, st>>>(c, spp, fb_d);
+      k_write<<<nb, 128, 0, st>>>(c, spp, fb_d, rgb_d);
       ctx->launches++;
       PM_CUDA(cudaGetLastError());
     }
   }
   if (!fb_dev) PM_CUDA(cudaMemcpyAsync(fb, fb_d, fb_bytes, cudaMemcpyDeviceToHost, st));
+  if (!rgb_dev) PM_CUDA(cudaMemcpyAsync(rgb_linear, rgb_d, rgb_bytes, cudaMemcpyDeviceToHost, st));
   PM_CUDA(cudaStreamSynchronize(st));
   ctx->last_kernel_ms = ms_gather; /* device time of the global-map gather kernels of this call */
   return PM_OK;

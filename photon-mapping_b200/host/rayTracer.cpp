@@ -5,7 +5,9 @@
 //
 //   rayTracer [config.toml]
 #include <chrono>
+#include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <iostream>
 
@@ -40,13 +42,33 @@ static pm_camera setup_camera(V3 from, V3 at, V3 up, float fovy, int W, int H) {
   return c;
 }
 
+// readPhotonsFromFile (ray-tracer/src/hostCode.cu:26-52): an unreadable file is reported and yields no photons — the
+// render goes on with direct light only. One pass over the file: a text line holds nine "%.6f" numbers, so it is at
+// least 81 bytes long and size / 64 + 16 records always suffice.
 static std::vector<pm_photon40> read_photons(const std::string& path) {
-  int64_t n = 0;
   const bool bin = path.size() > 4 && path.compare(path.size() - 4, 4, ".bin") == 0;  // written by photonMapping for *.bin names
-  auto rd = bin ? pm_photons_read_bin : pm_photons_read_text;
-  check(rd(path.c_str(), nullptr, 0, &n));
-  std::vector<pm_photon40> v((size_t)n);
-  if (n) check(rd(path.c_str(), v.data(), n, &n));
+  int64_t n = 0, cap = 0;
+  if (bin) {
+    if (pm_photons_read_bin(path.c_str(), nullptr, 0, &cap) != PM_OK) {
+      std::cerr << "Error reading photons file " << path << ": " << pm_last_error() << std::endl;
+      return {};
+    }
+  } else {
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) {
+      std::cerr << "Error opening photons file " << path << std::endl;
+      return {};
+    }
+    std::fseek(f, 0, SEEK_END);
+    cap = (int64_t)std::ftell(f) / 64 + 16;
+    std::fclose(f);
+  }
+  std::vector<pm_photon40> v((size_t)cap);
+  if ((bin ? pm_photons_read_bin : pm_photons_read_text)(path.c_str(), v.data(), cap, &n) != PM_OK) {
+    std::cerr << "Error reading photons file " << path << ": " << pm_last_error() << std::endl;
+    return {};
+  }
+  v.resize((size_t)std::min(n, cap));
   return v;
 }
 

@@ -53,6 +53,15 @@ def ppm_update(N, r2, tau, flux, count, alpha: float):
     N[:] = np.where(hit, n_new, N)
 
 
+def paths_launched(lights, casted: int) -> int:
+    """Paths one emission call launches over ALL ranks: per light int(power * int(casted / sum(power)))
+    (photon-mapping/src/hostCode.cu:86,102-110; pm_emit.cu) — at most `casted`, less when the per-watt truncation
+    bites. The radiance estimate is normalised by this number, not by the requested count."""
+    total = float(np.sum(lights["power"])) if len(lights) else 0.0
+    per_watt = int(int(casted) / total) if total > 0 else 0
+    return sum(int(float(l["power"]) * per_watt) for l in lights)
+
+
 def progressive_render(pkg, ctx, scene, tri_mesh, mats, lights, camera, width: int, height: int, passes: int,
                        photons_per_pass: int, r0: float, alpha: float = 0.7, max_depth: int = 8, seed: int = 1, group=None,
                        device=None):
@@ -73,7 +82,7 @@ def progressive_render(pkg, ctx, scene, tri_mesh, mats, lights, camera, width: i
         g40, n, paths, _ = scene.emit_photons(lights, photons_per_pass, max_depth, False, seed=seed + p,
                                               rng_mode=pkg.RNG_COUNTER, first_photon=rank, photon_stride=world,
                                               capacity=(photons_per_pass // world + len(lights) + 1) * max(1, max_depth))
-        emitted += photons_per_pass
+        emitted += paths_launched(lights, photons_per_pass)
         g44, _ = pkg.photons_to_maps(ctx, g40, np.zeros(0, pkg.PHOTON40))
         pmap = pkg.PhotonMap.build(ctx, g44) if len(g44) else None
         if pmap is not None:
@@ -144,7 +153,7 @@ def progressive_render_device(pkg, ctx, scene, tri_mesh, mats, lights, camera, w
                                      seed + p, pkg.RNG_COUNTER, rank, world, d40.data_ptr(), cap, ctypes.byref(cnt),
                                      ctypes.byref(npaths), ctypes.byref(nseg)))
         n = cnt.value
-        emitted += photons_per_pass
+        emitted += paths_launched(lights, photons_per_pass)
         lap()
         if n > 0:
             pkg._check(L.pm_photons_to_maps(ctx.handle, d40.data_ptr(), n, None, 0, g44.data_ptr(), None))

@@ -1,4 +1,4 @@
-"""Extracts the reference's Cornell-box asset into a small committed fixture (geometry, materials,
+"""Extracts the reference's Cornell-box, sphere and dragon-box assets into small committed fixtures (geometry, materials,
 lights), so the tests and the bench can use the reference's own C1 scene on the GPU box where
 /root/reference does not exist.  Run in the build container:  python tests/golden/make_scenes.py
 Source: /root/reference/assets/models/cornell-box/{cornell-box.glb, cornell-box.mtl, lights.txt}."""
@@ -15,7 +15,8 @@ import __graft_entry__ as graft  # noqa: E402
 pkg = graft.load_package()
 from photon_mapping_b200 import scene_io  # noqa: E402
 
-for name, rel in [("cornell_box", "cornell-box/cornell-box.glb"), ("sphere", "sphere/sphere.glb")]:
+for name, rel in [("cornell_box", "cornell-box/cornell-box.glb"), ("sphere", "sphere/sphere.glb"),
+                  ("dragon_box", "dragon/dragon-box.glb")]:
     path = os.path.join("/root/reference/assets/models", rel)
     if not os.path.exists(path):
         print("skip", path)

@@ -35,6 +35,45 @@ def test_trace_closest_matches_bruteforce_on_reference_assets(pkg, ctx, orc, nam
     assert np.array_equal(occ, oracle_occluded(orc, sc, rays))
 
 
+def test_trace_closest_dragon_box(pkg, ctx, orc):
+    """assets/models/dragon/dragon-box.glb (91 226 triangles, the reference's largest asset) through the LBVH."""
+    sc = load_scene("dragon_box")
+    assert len(sc["tris"]) == 91226
+    s = make_scene(pkg, ctx, sc)
+    lo, hi = scene_box(sc)
+    rays = random_rays(12000, 23, lo - 0.5, hi + 0.5)
+    rays["org"][:3000] = sc["lights"]["pos"][0]  # what stage 1 shoots
+    # a block aimed at the dragon itself (the walls take most random rays)
+    dv = sc["verts"][sc["tris"][sc["tri_mesh"] == 0].reshape(-1)]
+    tgt = dv[np.random.default_rng(5).integers(0, len(dv), 3000)]
+    d = tgt - rays["org"][3000:6000]
+    rays["dir"][3000:6000] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    got = s.trace_closest(rays)
+    want = oracle_trace(orc, sc, rays)
+    assert (sc["tri_mesh"][want["prim"][want["prim"] >= 0]] == 0).sum() > 2000  # the dragon is hit
+    assert np.array_equal(got["prim"], want["prim"])
+    assert got["t"].tobytes() == want["t"].tobytes()
+    assert np.array_equal(s.trace_occluded(rays), oracle_occluded(orc, sc, rays))
+
+
+def test_trace_closest_c4_room_1m_triangles(pkg, ctx, orc):
+    """The procedural 1 000 012-triangle room of C4 (photon-mapping_b200/scenes.py) against brute force."""
+    import __graft_entry__ as graft
+
+    sc = graft.load_package_module("scenes").c4_room()
+    assert len(sc["tris"]) == 1_000_012
+    s = make_scene(pkg, ctx, sc)
+    rays = random_rays(2400, 31, [-20, 0, -20], [20, 40, 20])
+    rays["org"][:600] = sc["lights"]["pos"][0]
+    rays["org"][600:1200] = sc["lights"]["pos"][1]
+    got = s.trace_closest(rays)
+    want = oracle_trace(orc, sc, rays)
+    assert (want["prim"] >= 0).mean() > 0.9 and (want["prim"] < 1_000_000).sum() > 300  # walls and the sphere
+    assert np.array_equal(got["prim"], want["prim"])
+    assert got["t"].tobytes() == want["t"].tobytes()
+    assert np.array_equal(s.trace_occluded(rays), oracle_occluded(orc, sc, rays))
+
+
 @pytest.mark.parametrize("nt", [1, 2, 3, 17, 1000, 4096, 4097, 20000])  # <= 4096: host SAH hierarchy, above: LBVH
 def test_trace_closest_soup(pkg, ctx, orc, nt):
     sc = soup_scene(nt, nt)

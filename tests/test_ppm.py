@@ -26,6 +26,16 @@ def test_ppm_update_arithmetic():
     assert (r2 <= [4, 4, 4, 1]).all()  # radii never grow
 
 
+def test_paths_launched_follows_the_per_watt_truncation():
+    """photon-mapping/src/hostCode.cu:86,102-110: int(power * int(casted / sum(power))) per light."""
+    ppm = graft.load_package_module("ppm")
+    LIGHT = np.dtype([("pos", "<f4", 3), ("rgb", "<f4", 3), ("power", "<f8")])
+    lights = np.zeros(3, LIGHT)
+    lights["power"] = [10.0, 2.5, 0.3]
+    assert ppm.paths_launched(lights, 1000) == int(10.0 * 78) + int(2.5 * 78) + int(0.3 * 78) == 998
+    assert ppm.paths_launched(lights[:1], 999) == 990 and ppm.paths_launched(lights[:0], 5) == 0
+
+
 @pytest.mark.gpu
 def test_progressive_passes_match_oracle_loop(pkg, ctx, orc):
     ppm = graft.load_package_module("ppm")
@@ -53,7 +63,7 @@ def test_progressive_passes_match_oracle_loop(pkg, ctx, orc):
         ppm.ppm_update(N, r2, tau, flux, cnt, alpha)
     assert np.array_equal(got["N"], N) and np.array_equal(got["r2"], r2)  # counts are exact, so are N and r²
     assert np.allclose(got["tau"], tau, rtol=2e-4, atol=1e-6)
-    assert got["emitted"] == passes * per_pass and np.isfinite(got["radiance"]).all() and got["radiance"].max() > 0
+    assert got["emitted"] == passes * ppm.paths_launched(sc["lights"], per_pass) and np.isfinite(got["radiance"]).all() and got["radiance"].max() > 0
     assert (r2 < np.float32(r0) ** 2).any()
 
 
@@ -73,7 +83,8 @@ def test_device_resident_loop_equals_host_loop(pkg, ctx):
                                         alpha, depth, seed=9, stats=stats)
     assert np.array_equal(dev["N"], host["N"]) and np.array_equal(dev["r2"], host["r2"])
     assert np.array_equal(dev["tau"], host["tau"]) and np.array_equal(dev["radiance"], host["radiance"])
-    assert len(stats) == passes and all(s["stored"] > 0 for s in stats) and dev["emitted"] == passes * per_pass
+    assert len(stats) == passes and all(s["stored"] > 0 for s in stats)
+    assert dev["emitted"] == sum(s["paths"] for s in stats) == passes * ppm.paths_launched(sc["lights"], per_pass)
 
 
 @pytest.mark.gpu
