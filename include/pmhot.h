@@ -176,6 +176,15 @@ int  pm_emit_photons_keyed(pm_ctx* ctx, const pm_scene* scene, const pm_light* l
                            pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
                            int64_t* n_paths, int64_t* n_segments);
 
+/* pm_emit_photons into device memory that also writes ONE BYTE PER PATH of this rank (path_counts_dev, in the rank's
+ * path order: light by light, launch indices first_photon, first_photon + photon_stride, ...): how many photons the
+ * path stored. That table is all pm_exchange_photons needs to merge the shards of several ranks without keys or a sort. */
+int  pm_emit_photons_counted(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host, int n_lights,
+                             int64_t casted, int max_depth, int caustics_mode,
+                             uint64_t seed, int rng_mode, int64_t first_photon, int64_t photon_stride,
+                             pm_photon40* out_dev, uint8_t* path_counts_dev, int64_t capacity, int64_t* count,
+                             int64_t* n_paths, int64_t* n_segments);
+
 /* pm_emit_photons_keyed with one pm_light_shape per light (shapes == NULL: all point lights; out_keys may be NULL) */
 int  pm_emit_photons_shaped(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host,
                             const pm_light_shape* shapes_host, int n_lights,
@@ -274,6 +283,49 @@ int  pm_view_photons(pm_ctx* ctx, const pm_scene* scene, const pm_photon40* phot
 /* the 4x4 projection * view matrix (column-major, glm layout) pm_view_photons uses: test hook */
 void pm_view_matrix(const float look_from[3], const float look_at[3], const float look_up[3], float fovy,
                     int width, int height, float out16[16]);
+
+/* ---- multi-GPU (the reference is single-GPU: owlContextCreate(nullptr, 1),
+ * photon-mapping/src/hostCode.cu:145). One process per GPU; the collectives are NCCL calls made by the library on
+ * the context's stream. libnccl.so.2 is bound at run time (PM_ERR_UNSUPPORTED if it cannot be loaded). ---------- */
+typedef struct pm_comm pm_comm;
+#define PM_COMM_ID_BYTES 128
+#define PM_DTYPE_F32 0
+#define PM_DTYPE_I32 1
+#define PM_DTYPE_I64 2
+/* rank 0 calls pm_comm_unique_id and hands the 128 bytes to the other ranks by whatever channel the host has (a
+ * file, MPI, torch.distributed); then every rank calls pm_comm_create (ncclCommInitRank; collective). */
+int  pm_comm_unique_id(void* id_out, int bytes);
+int  pm_comm_create(pm_ctx* ctx, const void* id_bytes, int rank, int world, pm_comm** out);
+void pm_comm_destroy(pm_comm* comm);
+int  pm_comm_rank(const pm_comm* comm);
+int  pm_comm_world(const pm_comm* comm);
+/* in-place sum over the ranks (comm == NULL or world 1: nothing to do); synchronous on return */
+int  pm_comm_allreduce_sum(pm_ctx* ctx, pm_comm* comm, void* buf_dev, int64_t count, int dtype);
+/* recv_dev[r * bytes_per_rank ...] = rank r's send_dev[0 .. bytes_per_rank) */
+int  pm_comm_allgather(pm_ctx* ctx, pm_comm* comm, const void* send_dev, void* recv_dev, int64_t bytes_per_rank);
+
+/* The path's one exchange. Every rank traced its share of the SAME emission (pm_emit_photons_counted with
+ * first_photon = rank, photon_stride = world, same lights / casted) and holds shard_dev[0 .. n_shard) plus one count
+ * byte per path. On return out_dev[0 .. *total) holds the photons of ALL ranks as 44-byte map records (power as
+ * given, split_dim 0) in exactly the order a single GPU would have produced them — (light, launch index, bounce) —
+ * on every rank. Two all-gathers (counts, padded records), two prefix sums, one placement kernel; no keys, no sort.
+ * collective_ms (may be NULL): device time of the all-gathers. comm == NULL: one rank (a plain 40 -> 44 conversion). */
+int  pm_exchange_photons(pm_ctx* ctx, pm_comm* comm, const pm_light* lights_host, int n_lights, int64_t casted,
+                         const pm_photon40* shard_dev, int64_t n_shard, const uint8_t* path_counts_dev, float power,
+                         pm_photon44* out_dev, int64_t capacity, int64_t* total, float* collective_ms);
+/* the placement step alone, on tables that are already gathered (test hook; also what a host with its own transport
+ * calls): counts_all_dev[r * counts_pitch + p], shards_dev[r * shard_pitch + i] */
+int  pm_exchange_place(pm_ctx* ctx, int world, const pm_light* lights_host, int n_lights, int64_t casted,
+                       const uint8_t* counts_all_dev, int64_t counts_pitch, const pm_photon40* shards_dev,
+                       int64_t shard_pitch, float power, pm_photon44* out_dev, int64_t capacity, int64_t* total);
+/* pm_map_build_shard + the two node-table all-reduces + pm_map_build_finish in one call: the same tree, array and
+ * map as pm_map_build on every rank (world must be a power of two, else every rank builds the whole tree) */
+int  pm_map_build_sharded(pm_ctx* ctx, pm_comm* comm, pm_photon44* photons_dev, int64_t n, float* bounds_host, pm_map** out);
+/* one progressive pass's state update (Hachisuka et al.): sums (flux.rgb, count) over the ranks (one all-reduce of
+ * 16 bytes per hit point; skipped for one rank), then per hit point M = count, N' = N + alpha M,
+ * ratio = N' / (N + M), r2 *= ratio, tau = (tau + flux) * ratio. All device pointers. */
+int  pm_ppm_update(pm_ctx* ctx, pm_comm* comm, int64_t n_points, const float* flux_dev, const int32_t* count_dev,
+                   float alpha, float* N_dev, float* r2_dev, float* tau_dev, float* collective_ms);
 
 /* ---- photon wire format (≙ writeAlivePhotons / readPhotonsFromFile) ------------------ */
 /* text: 9 floats "pos dir color", std::fixed, 6 decimals (photon-mapping/src/hostCode.cu:31-49) */

@@ -74,6 +74,25 @@ _SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p,
          c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64)],
     ),
+    "pm_emit_photons_counted": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p,
+         c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64)],
+    ),
+    "pm_comm_unique_id": (c_int, [c_void_p, c_int]),
+    "pm_comm_create": (c_int, [c_void_p, c_void_p, c_int, c_int, POINTER(c_void_p)]),
+    "pm_comm_destroy": (None, [c_void_p]),
+    "pm_comm_rank": (c_int, [c_void_p]),
+    "pm_comm_world": (c_int, [c_void_p]),
+    "pm_comm_allreduce_sum": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int]),
+    "pm_comm_allgather": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64]),
+    "pm_exchange_photons": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p, c_int64, c_void_p, c_float,
+                                    c_void_p, c_int64, POINTER(c_int64), POINTER(c_float)]),
+    "pm_exchange_place": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_float,
+                                  c_void_p, c_int64, POINTER(c_int64)]),
+    "pm_map_build_sharded": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, POINTER(c_void_p)]),
+    "pm_ppm_update": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
+                              POINTER(c_float)]),
     "pm_photons_to_maps": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "pm_map_build": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, POINTER(c_void_p)]),
     "pm_map_from_tree": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_void_p)]),

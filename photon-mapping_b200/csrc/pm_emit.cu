@@ -186,6 +186,12 @@ __global__ void k_compact(int64_t n_paths, int slots_per_path, const pm_photon40
   }
 }
 
+/* per-path store counts of a batch as bytes (max_depth <= 64): what pm_exchange_photons gathers */
+__global__ void k_counts_u8(int64_t n, const int* __restrict__ counts, uint8_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (uint8_t)counts[i];
+}
+
 struct CountToI64 {
   const int* c;
   __device__ int64_t operator()(int64_t i) const { return (int64_t)c[i]; }
@@ -212,8 +218,9 @@ extern "C" {
 static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, const pm_light_shape* shapes, int n_lights, int64_t casted,
                      int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
                      int64_t photon_stride, pm_photon40* out, uint64_t* out_keys, int64_t capacity, int64_t* count,
-                     int64_t* n_paths, int64_t* n_segments) {
+                     int64_t* n_paths, int64_t* n_segments, uint8_t* out_path_counts = nullptr) {
   PM_REQUIRE(ctx && scene && count, "ctx/scene/count is NULL");
+  PM_REQUIRE(!out_path_counts || pm::is_device_ptr(out_path_counts), "path_counts must be device memory");
   PM_REQUIRE(n_lights >= 0 && n_lights <= kMaxLights, "n_lights out of range (max 64)");
   PM_REQUIRE(n_lights == 0 || lights, "lights is NULL");
   PM_REQUIRE(casted >= 0 && casted <= 0x7fffffff, "casted out of range (int in the reference)");
@@ -309,6 +316,10 @@ static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights,
       size_t tb = scan_bytes;
       PM_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, tb, it, offsets, (int)nb + 1, st));
     }
+    if (out_path_counts) {
+      k_counts_u8<<<(unsigned)pm::div_up(nb, 256), 256, 0, st>>>(nb, counts, out_path_counts + b0);
+      ctx->launches++;
+    }
     int64_t batch_total = 0;
     PM_CUDA(cudaMemcpyAsync(&batch_total, offsets + nb, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
     PM_CUDA(cudaStreamSynchronize(st));
@@ -366,6 +377,16 @@ int pm_emit_photons_keyed(pm_ctx* ctx, const pm_scene* scene, const pm_light* li
   PM_REQUIRE(out_keys || capacity == 0, "out_keys is NULL");
   return emit_impl(ctx, scene, lights, nullptr, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
                    photon_stride, out, out_keys, capacity, count, n_paths, n_segments);
+}
+
+int pm_emit_photons_counted(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_lights, int64_t casted,
+                            int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
+                            int64_t photon_stride, pm_photon40* out_dev, uint8_t* path_counts_dev, int64_t capacity,
+                            int64_t* count, int64_t* n_paths, int64_t* n_segments) {
+  PM_REQUIRE(path_counts_dev, "path_counts is NULL");
+  PM_REQUIRE(capacity == 0 || pm::is_device_ptr(out_dev), "out must be device memory");
+  return emit_impl(ctx, scene, lights, nullptr, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
+                   photon_stride, out_dev, nullptr, capacity, count, n_paths, n_segments, path_counts_dev);
 }
 
 int pm_emit_photons_shaped(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, const pm_light_shape* shapes, int n_lights,

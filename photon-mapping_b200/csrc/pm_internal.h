@@ -38,6 +38,9 @@ void set_error(const char* fmt, ...);
 
 inline int64_t div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+/* limits of the multi-GPU entry points (pm_comm.cu): lights as in pm_emit_photons, ranks of one node */
+constexpr int kMaxLightsComm = 64, kMaxRanksComm = 16;
+
 /* Buffers a photon map owns (query-side copies, grid copy) come from the device's stream-ordered pool: a render
  * loop that builds and drops one map per pass (progressive mode: 64 of them) then reuses the same memory without
  * the device-wide synchronisation and the page mapping cost of cudaMalloc / cudaFree. pm_ctx_create lets the pool

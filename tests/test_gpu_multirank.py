@@ -69,3 +69,80 @@ def test_sharded_build_equals_single_gpu_build(pkg, ctx, n, world):
         assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
         got.close()
         ref.close()
+
+
+@pytest.mark.parametrize("caustics,power", [(False, 1.0), (True, 0.5)])
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_sortfree_exchange_places_shards_in_single_gpu_order(pkg, ctx, world, caustics, power):
+    """pm_emit_photons_counted per emulated rank + pm_exchange_place (the single-GPU part of pm_exchange_photons: two
+    prefix sums over the gathered per-path count bytes + the placement kernel) equal the single-rank emission
+    converted by pm_photons_to_maps, byte for byte — no keys, no sort."""
+    import ctypes
+
+    import torch
+
+    L = pkg.lib()
+    sc = load_scene("sphere" if caustics else "cornell_box")
+    scene = pkg.Scene(ctx, sc["verts"], sc["tris"], sc["tri_mesh"], sc["mats"])
+    lights = np.ascontiguousarray(sc["lights"], pkg.LIGHT)
+    casted, depth = 50001, 7
+    full, n, paths, _ = scene.emit_photons(lights, casted, depth, caustics, seed=3, rng_mode=pkg.RNG_COUNTER)
+    want = np.zeros(n, pkg.PHOTON44)
+    pkg._check(L.pm_photons_to_maps(ctx.handle, full.ctypes.data, n, None, 0, want.ctypes.data, None))
+    want["power"] = power
+    mg = graft.load_package_module("multigpu")
+    sizes = mg.light_launch_sizes(lights, casted)
+    pmax = max(mg.rank_path_count(sizes, r, world) for r in range(world))
+    pitch = (pmax + 15) // 16 * 16 + 16
+    cap_r = casted * depth // world + 64
+    counts_all = torch.zeros((world, pitch), dtype=torch.uint8, device="cuda")
+    shards = torch.zeros((world, cap_r, 40), dtype=torch.uint8, device="cuda")
+    total_local = 0
+    for r in range(world):
+        cnt, npaths, nseg = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int64(0)
+        pkg._check(L.pm_emit_photons_counted(ctx.handle, scene.handle, lights.ctypes.data, len(lights), casted, depth,
+                                             1 if caustics else 0, 3, pkg.RNG_COUNTER, r, world, shards[r].data_ptr(),
+                                             counts_all[r].data_ptr(), cap_r, ctypes.byref(cnt), ctypes.byref(npaths),
+                                             ctypes.byref(nseg)))
+        assert npaths.value == mg.rank_path_count(sizes, r, world)
+        assert int(counts_all[r].sum().item()) == cnt.value
+        total_local += cnt.value
+    assert total_local == n
+    out = torch.zeros((n + 5, 44), dtype=torch.uint8, device="cuda")
+    total = ctypes.c_int64(0)
+    pkg._check(L.pm_exchange_place(ctx.handle, world, lights.ctypes.data, len(lights), casted, counts_all.data_ptr(), pitch,
+                                   shards.data_ptr(), cap_r, power, out.data_ptr(), n + 5, ctypes.byref(total)))
+    assert total.value == n
+    got = out[:n].cpu().numpy().reshape(-1).view(pkg.PHOTON44)
+    assert got.tobytes() == want.tobytes()
+    assert int(out[n:].sum().item()) == 0  # nothing written past the end
+    # too small an output is reported, not overrun
+    rc = L.pm_exchange_place(ctx.handle, world, lights.ctypes.data, len(lights), casted, counts_all.data_ptr(), pitch,
+                             shards.data_ptr(), cap_r, power, out.data_ptr(), n - 1, ctypes.byref(total))
+    assert rc == -5 and total.value == n  # PM_ERR_CAPACITY
+
+
+def test_ppm_update_kernel_equals_numpy_update(pkg, ctx):
+    """pm_ppm_update (one rank: no collective) against ppm.ppm_update, bit for bit."""
+    import ctypes
+
+    import torch
+
+    ppm = graft.load_package_module("ppm")
+    rng = np.random.default_rng(12)
+    npx = 50000
+    N = (rng.random(npx, dtype=np.float32) * 40).astype(np.float32)
+    N[::7] = 0
+    r2 = (rng.random(npx, dtype=np.float32) + np.float32(0.01)).astype(np.float32)
+    tau = rng.random((npx, 3), dtype=np.float32)
+    flux = rng.random((npx, 3), dtype=np.float32)
+    count = rng.integers(0, 30, npx).astype(np.int32)
+    count[::5] = 0
+    flux[count == 0] = 0
+    dN, dr2, dtau = (torch.from_numpy(a.copy()).cuda() for a in (N, r2, tau))
+    dflux, dcount = torch.from_numpy(flux).cuda(), torch.from_numpy(count).cuda()
+    pkg._check(pkg.lib().pm_ppm_update(ctx.handle, None, npx, dflux.data_ptr(), dcount.data_ptr(), 0.7, dN.data_ptr(),
+                                       dr2.data_ptr(), dtau.data_ptr(), None))
+    ppm.ppm_update(N, r2, tau, flux, count, 0.7)
+    assert np.array_equal(dN.cpu().numpy(), N) and np.array_equal(dr2.cpu().numpy(), r2)
+    assert np.array_equal(dtau.cpu().numpy(), tau)
