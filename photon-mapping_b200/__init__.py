@@ -232,6 +232,58 @@ class Context:
         return lib().pm_ctx_last_handover_count(self.handle)
 
 
+class Comm:
+    """pm_comm: this rank's handle on the NCCL communicator the library's multi-GPU calls use (pm_exchange_photons,
+    pm_map_build_sharded, pm_ppm_update, pm_comm_allreduce_sum). The reference is single-GPU; SURVEY §8(e)."""
+
+    ID_BYTES = 128
+
+    def __init__(self, ctx: Context, id_bytes: bytes, rank: int, world: int):
+        h = c_void_p()
+        buf = ctypes.create_string_buffer(bytes(id_bytes), self.ID_BYTES)
+        _check(lib().pm_comm_create(ctx.handle, buf, rank, world, ctypes.byref(h)))
+        self.ctx, self.handle, self.rank, self.world = ctx, h, rank, world
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = ctypes.create_string_buffer(Comm.ID_BYTES)
+        _check(lib().pm_comm_unique_id(buf, Comm.ID_BYTES))
+        return buf.raw
+
+    @classmethod
+    def from_torch_distributed(cls, ctx: Context, group=None) -> "Comm":
+        """Rank 0 draws the NCCL id, torch.distributed (any backend) carries its 128 bytes to the other ranks."""
+        import torch
+        import torch.distributed as dist
+
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        dev = torch.device("cuda", ctx.device) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+        t = torch.zeros(cls.ID_BYTES, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            t.copy_(torch.frombuffer(bytearray(cls.unique_id()), dtype=torch.uint8))
+        dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        return cls(ctx, bytes(t.cpu().numpy().tobytes()), rank, world)
+
+    def allreduce_sum(self, t) -> None:
+        """In-place sum of a CUDA float32 / int32 / int64 tensor over the ranks."""
+        import torch
+
+        code = {torch.float32: 0, torch.int32: 1, torch.int64: 2}[t.dtype]
+        self.ctx.after_torch(t)
+        _check(lib().pm_comm_allreduce_sum(self.ctx.handle, self.handle, t.data_ptr(), t.numel(), code))
+
+    def close(self) -> None:
+        if getattr(self, "handle", None):
+            lib().pm_comm_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class PhotonMap:
     """pm_map: a photon array in left-balanced kd-tree order (≙ cukd::buildTree output)."""
 
@@ -279,6 +331,17 @@ class PhotonMap:
         ctx.after_torch(photons)  # the all-reduces run on torch's stream
         _check(lib().pm_map_build_finish(ctx.handle, _ptr(photons), n, elem.data_ptr(), dim.data_ptr(), bounds.ctypes.data,
                                          ctypes.byref(h)))
+        return cls(ctx, h, n, bounds, photons)
+
+    @classmethod
+    def build_sharded_comm(cls, ctx: Context, comm: "Comm | None", photons) -> "PhotonMap":
+        """pm_map_build_sharded: shard pass + the two node-table all-reduces + finish, all inside the library."""
+        n = _count(photons, 44)
+        h = c_void_p()
+        bounds = np.zeros(6, np.float32)
+        ctx.after_torch(photons)
+        _check(lib().pm_map_build_sharded(ctx.handle, comm.handle if comm else None, _ptr(photons), n, bounds.ctypes.data,
+                                          ctypes.byref(h)))
         return cls(ctx, h, n, bounds, photons)
 
     @classmethod

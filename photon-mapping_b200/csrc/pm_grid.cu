@@ -92,16 +92,20 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
   __shared__ WarpScratch scratch[kWarps];
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u, le_not0 = (lt | (1u << lane)) & ~1u;
-  WarpScratch& ws = scratch[threadIdx.x >> 5];
+  /* the warp index through a shuffle: the compiler then knows it (and every branch on the query index) to be
+   * warp-uniform and drops the divergence guards around the warp-level primitives below */
+  const int wid = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  WarpScratch& ws = scratch[wid];
   const int k = io.k;
   const float cell3 = g.cell * g.cell * g.cell;
 
   const int total = nq_dev ? *nq_dev : io.nq; /* a hand-over list has a device-side length */
-  for (int t = blockIdx.x * kWarps + (threadIdx.x >> 5); t < total; t += gridDim.x * kWarps) {
-    const int qi = io.order ? io.order[t] : t;
+  for (int t = blockIdx.x * kWarps + wid; t < total; t += gridDim.x * kWarps) {
+    /* loaded values pass through a shuffle so that the compiler sees them as warp-uniform */
+    const int qi = __shfl_sync(0xffffffffu, io.order ? io.order[t] : t, 0);
     float brdf = 0.f;
     if (GATHER) {
-      brdf = io.brdf[qi];
+      brdf = __shfl_sync(0xffffffffu, io.brdf[qi], 0);
       if (!(brdf > 0.f)) {
         if (lane < 3) io.rgb[(size_t)qi * 3 + lane] = 0.f;
         continue;
@@ -485,23 +489,26 @@ __device__ __forceinline__ float sqrt_approx(float x) {
 }
 
 template <bool GATHER>
-__global__ void __launch_bounds__(kWarps * 32, 6)
+__global__ void __launch_bounds__(kWarps * 32, GATHER ? 4 : 5) /* no spills: a reloaded value is no longer warp-uniform to the compiler */
 k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::QueryIO io, const __grid_constant__ FastParams fp,
            int* __restrict__ ho_list, int* __restrict__ ho_count) {
   __shared__ FastScratch scratch[kWarps];
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u, le_not0 = (lt | (1u << lane)) & ~1u;
-  FastScratch& ws = scratch[threadIdx.x >> 5];
+  /* the warp index through a shuffle: the compiler then knows it (and every branch on the query index) to be
+   * warp-uniform and drops the divergence guards around the warp-level primitives below */
+  const int wid = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  FastScratch& ws = scratch[wid];
   const int k = io.k;
   const float fk = (float)k;
   /* rows of the 5x5 block of the first attempt: lane -> (oy, oz) */
   const int oz5 = div_small(lane, 5) - 2, oy5 = lane - (oz5 + 2) * 5 - 2;
-  for (int t = blockIdx.x * kWarps + (threadIdx.x >> 5); t < io.nq; t += gridDim.x * kWarps) {
+  for (int t = blockIdx.x * kWarps + wid; t < io.nq; t += gridDim.x * kWarps) {
     const float4 qv = __ldg(fp.sq + t);
     const int qi = __float_as_int(qv.w);
     float brdf = 0.f;
     if (GATHER) {
-      brdf = __ldg(io.brdf + qi);
+      brdf = __shfl_sync(0xffffffffu, __ldg(io.brdf + qi), 0); /* warp-uniform to the compiler */
       if (!(brdf > 0.f)) {
         if (lane < 3) io.rgb[(size_t)qi * 3 + lane] = 0.f;
         continue;
@@ -558,18 +565,30 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
             for (int i = (P + 31) >> 5; i * 32 < P + len; i++) ws.words[i].y = (unsigned)d;
           }
           __syncwarp();
-          for (int i = 0; i * 32 < mc; i++) {
-            const int j = i * 32 + lane;
-            const uint2 w = ws.words[i];
-            const int run = (int)w.y + __popc(w.x & le_not0);
-            /* lanes past the end read a record behind the last row (the array is padded) and drop it */
-            const float4 p = __ldg(g.pts + (ws.off[run] + j));
-            const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
-            const bool pass = j < mc && d2 < R2;
-            const unsigned b = __ballot_sync(0xffffffffu, pass);
-            /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
-            if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p.w));
-            n += __popc(b);
+          /* four steps at a time: the addresses of all four come out of shared memory first, so four record loads are
+           * in flight per lane before the first distance is needed */
+          for (int i0 = 0; i0 * 32 < mc; i0 += 4) {
+            float4 p[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              if ((i0 + u) * 32 < mc) {
+                const uint2 w = ws.words[i0 + u];
+                const int run = (int)w.y + __popc(w.x & le_not0);
+                /* lanes past the end read a record behind the last row (the array is padded) and drop it */
+                p[u] = __ldg(g.pts + (ws.off[run] + (i0 + u) * 32 + lane));
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              if ((i0 + u) * 32 < mc) {
+                const float d2 = pmk::dist2(p[u].x, p[u].y, p[u].z, qx, qy, qz);
+                const bool pass = (i0 + u) * 32 + lane < mc && d2 < R2;
+                const unsigned b = __ballot_sync(0xffffffffu, pass);
+                /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
+                if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p[u].w));
+                n += __popc(b);
+              }
+            }
           }
         }
       }
@@ -600,7 +619,6 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
     __syncwarp();
 
     /* ---- the k-th smallest dist²: histogram over [Ta, R2), bin 0 = everything expected below k - 3 sigma ---- */
-    const int ns = (n + 31) >> 5;
     uint2 kv[kSlots];
     int bp[kSlots]; /* bin << 8 | position in the bin */
     {
@@ -610,7 +628,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
       for (int s = 0; s < kSlots; s++) {
         kv[s] = make_uint2(0xffffffffu, 0u);
         bp[s] = 63 << 8;
-        if (s < ns && lane + 32 * s < n) {
+        if (lane + 32 * s < n) {
           kv[s] = ws.keys[lane + 32 * s];
           /* monotone in dist²: subtraction, multiplication by a positive constant, floor, clamp */
           const int bin = min(max(__float2int_rd((__uint_as_float(kv[s].x) - Ta) * scale) + 1, 0), 30);
@@ -634,7 +652,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
     if (exact) {
 #pragma unroll
       for (int s = 0; s < kSlots; s++)
-        if (s < ns && (bp[s] >> 8) == kbin) ws.bl[bp[s] & 255] = kv[s].x;
+        if ((bp[s] >> 8) == kbin) ws.bl[bp[s] & 255] = kv[s].x;
       __syncwarp();
       /* one member per lane: tau = the (k - clo)-th smallest of them */
       const int need = k - clo;
@@ -650,23 +668,26 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
       continue;
     }
 
-    /* ---- output: every candidate with dist² <= tau, ballot-compacted ---- */
+    /* ---- output: every candidate with dist² <= tau ---- */
     if (!GATHER) {
-      int32_t* ids = io.ids + (size_t)qi * k;
-      float* d2o = io.d2 ? io.d2 + (size_t)qi * k : nullptr;
+      /* ballot-compacted into keys[0 .. k) (every lane holds its candidates in registers by now), then whole rows
+       * leave as coalesced 8-byte stores */
+      __syncwarp();
       int base = 0;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
-        if (s < ns) {
-          const bool a = kv[s].x <= tau;
-          const unsigned b = __ballot_sync(0xffffffffu, a);
-          if (a) {
-            const int p = base + __popc(b & lt);
-            ids[p] = (int32_t)kv[s].y;
-            if (d2o) d2o[p] = __uint_as_float(kv[s].x);
-          }
-          base += __popc(b);
-        }
+        const bool a = kv[s].x <= tau;
+        const unsigned b = __ballot_sync(0xffffffffu, a);
+        if (a) ws.keys[base + __popc(b & lt)] = kv[s];
+        base += __popc(b);
+      }
+      __syncwarp();
+      int2* ids2 = reinterpret_cast<int2*>(io.ids + (size_t)qi * k); /* k is even: rows are 8-byte aligned */
+      float2* d22 = io.d2 ? reinterpret_cast<float2*>(io.d2 + (size_t)qi * k) : nullptr;
+      for (int p = lane; 2 * p < k; p += 32) {
+        const uint4 e = reinterpret_cast<const uint4*>(ws.keys)[p]; /* entries 2p, 2p + 1 */
+        ids2[p] = make_int2((int)e.y, (int)e.w);
+        if (d22) d22[p] = make_float2(__uint_as_float(e.x), __uint_as_float(e.z));
       }
       if (io.r2 && lane == 0) io.r2[qi] = __uint_as_float(tau);
     } else {
@@ -676,7 +697,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
       float fr = 0.f, fg = 0.f, fb = 0.f;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
-        if (s < ns && kv[s].x <= tau) {
+        if (kv[s].x <= tau) {
           const float4 c = __ldg(color4 + kv[s].y);
           const float dist = __fsqrt_rn(__uint_as_float(kv[s].x));
           const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
@@ -720,10 +741,11 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
   __shared__ WarpScratch scratch[kWarps];
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u, le_not0 = (lt | (1u << lane)) & ~1u;
-  WarpScratch& ws = scratch[threadIdx.x >> 5];
-  for (int t = blockIdx.x * kWarps + (threadIdx.x >> 5); t < nq; t += gridDim.x * kWarps) {
-    const int qi = order ? order[t] : t;
-    const float f = brdf[qi], R2 = radius2[qi];
+  const int wid = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); /* warp-uniform to the compiler */
+  WarpScratch& ws = scratch[wid];
+  for (int t = blockIdx.x * kWarps + wid; t < nq; t += gridDim.x * kWarps) {
+    const int qi = __shfl_sync(0xffffffffu, order ? order[t] : t, 0); /* warp-uniform to the compiler */
+    const float f = __shfl_sync(0xffffffffu, brdf[qi], 0), R2 = __shfl_sync(0xffffffffu, radius2[qi], 0);
     if (!(f > 0.f) || !(R2 > 0.f)) { /* no hit point here */
       if (lane < 3) out_flux[(size_t)qi * 3 + lane] = 0.f;
       if (lane == 0) out_count[qi] = 0;

@@ -199,16 +199,18 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3)
 k_kdw(const float4* __restrict__ nodes, const float4* __restrict__ color4, int n, int first_bucket_node, const Box6f box,
       pmk::QueryIO io, const int* __restrict__ list, const int* __restrict__ list_count) {
   __shared__ KdwScratch scratch[kWarpsPerCta];
-  KdwScratch& ws = scratch[threadIdx.x >> 5];
+  const int wid = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); /* warp-uniform to the compiler */
+  KdwScratch& ws = scratch[wid];
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u;
   const int total = list ? *list_count : io.nq;
   const int k = io.k;
-  for (int t = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5); t < total; t += gridDim.x * kWarpsPerCta) {
-    const int qi = list ? list[t] : (io.order ? io.order[t] : t);
+  for (int t = blockIdx.x * kWarpsPerCta + wid; t < total; t += gridDim.x * kWarpsPerCta) {
+    /* loaded values pass through a shuffle so that the compiler sees them as warp-uniform */
+    const int qi = __shfl_sync(0xffffffffu, list ? list[t] : (io.order ? io.order[t] : t), 0);
     float brdf = 0.f;
     if (GATHER) {
-      brdf = io.brdf[qi];
+      brdf = __shfl_sync(0xffffffffu, io.brdf[qi], 0);
       if (!(brdf > 0.f)) {
         if (lane < 3) io.rgb[(size_t)qi * 3 + lane] = 0.f;
         continue;
