@@ -14,7 +14,7 @@ B="python bench.py --steps 3 --warmup 3 --no-pipelines --no-cpu-baseline --no-st
 timeout 600 $B > gpurun_out/${tag}_plain.log 2>&1 && \
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/${tag}_launches.csv $B > gpurun_out/${tag}_ncu_l.log 2>&1
 # one warm pm_knn step: its six kernels (3 binning + fast + general + kd), skipping the 3 builds' tuning samples and 3 warm-up steps
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'k_qbin|k_knn_fast|k_grid_query|k_kdw' -s 30 -c 6 \
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'k_qbin|k_knn_fast|k_grid_query|k_kdw' -s 28 -c 6 \
   -o gpurun_out/${tag}_knn_step $B > gpurun_out/${tag}_ncu_f.log 2>&1
 timeout 300 python tools/prof_emit.py cornell 4000000 3 > gpurun_out/${tag}_plain_emit.log 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_walk -s 1 -c 1 -o gpurun_out/${tag}_walk \
