@@ -478,6 +478,7 @@ struct FastParams {
   const float4* sq;   /* queries in processing order */
   float R2;           /* first search radius², already capped by the block guarantee and the cutoff */
   float Rc2;          /* (its radius in cells + the margins)² */
+  float rcpR2;        /* 1 / R2 */
   float margin_c;     /* GridView::margin in cells */
   float2 win[kWinSize];
 };
@@ -525,7 +526,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
      * units; the margins cover the rounding of this and of the build's cell assignment. ---- */
     int h = 2, n = 0, attempt = 0, r0 = 0, nrows = 25;
     int oy = oy5, oz = oz5;
-    float R2 = fp.R2, Rc2 = fp.Rc2;
+    float R2 = fp.R2, Rc2 = fp.Rc2, rcpR2 = fp.rcpR2;
     bool give_up = false;
     while (true) {
       {
@@ -565,30 +566,39 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
             for (int i = (P + 31) >> 5; i * 32 < P + len; i++) ws.words[i].y = (unsigned)d;
           }
           __syncwarp();
-          /* four steps at a time: the addresses of all four come out of shared memory first, so four record loads are
-           * in flight per lane before the first distance is needed */
-          for (int i0 = 0; i0 * 32 < mc; i0 += 4) {
-            float4 p[4];
+          /* full steps two at a time: both addresses come out of shared memory first, so two record loads per lane
+           * are in flight before the first distance is needed (one step's chain LDS -> LDS -> LDG -> compare is ~400
+           * cycles; with one load in flight the warps of an SM cannot cover it) */
+          int i = 0;
+          for (; (i + 2) * 32 <= mc; i += 2) {
+            float4 p[2];
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-              if ((i0 + u) * 32 < mc) {
-                const uint2 w = ws.words[i0 + u];
-                const int run = (int)w.y + __popc(w.x & le_not0);
-                /* lanes past the end read a record behind the last row (the array is padded) and drop it */
-                p[u] = __ldg(g.pts + (ws.off[run] + (i0 + u) * 32 + lane));
-              }
+            for (int u = 0; u < 2; u++) {
+              const uint2 w = ws.words[i + u];
+              const int run = (int)w.y + __popc(w.x & le_not0);
+              p[u] = __ldg(g.pts + (ws.off[run] + (i + u) * 32 + lane));
             }
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-              if ((i0 + u) * 32 < mc) {
-                const float d2 = pmk::dist2(p[u].x, p[u].y, p[u].z, qx, qy, qz);
-                const bool pass = (i0 + u) * 32 + lane < mc && d2 < R2;
-                const unsigned b = __ballot_sync(0xffffffffu, pass);
-                /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
-                if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p[u].w));
-                n += __popc(b);
-              }
+            for (int u = 0; u < 2; u++) {
+              const float d2 = pmk::dist2(p[u].x, p[u].y, p[u].z, qx, qy, qz);
+              const bool pass = d2 < R2;
+              const unsigned b = __ballot_sync(0xffffffffu, pass);
+              /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
+              if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p[u].w));
+              n += __popc(b);
             }
+          }
+          for (; i * 32 < mc; i++) {
+            const int j = i * 32 + lane;
+            const uint2 w = ws.words[i];
+            const int run = (int)w.y + __popc(w.x & le_not0);
+            /* lanes past the end read a record behind the last row (the array is padded) and drop it */
+            const float4 p = __ldg(g.pts + (ws.off[run] + j));
+            const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+            const bool pass = j < mc && d2 < R2;
+            const unsigned b = __ballot_sync(0xffffffffu, pass);
+            if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p.w));
+            n += __popc(b);
           }
         }
       }
@@ -602,6 +612,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
         h = max(__float2int_ru(Rc + 2.f * fp.margin_c), 2);
         if (h > kFastMaxH) { give_up = true; break; }
         Rc2 = Rc * Rc;
+        rcpR2 = __fdividef(1.f, R2);
         nrows = (2 * h + 1) * (2 * h + 1);
         r0 = 0; n = 0;
       }
@@ -621,19 +632,24 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
     /* ---- the k-th smallest dist²: histogram over [Ta, R2), bin 0 = everything expected below k - 3 sigma ---- */
     uint2 kv[kSlots];
     int bp[kSlots]; /* bin << 8 | position in the bin */
+    const bool four = n > 3 * 32; /* the fourth register slot is needed by about one query in five */
+    kv[kSlots - 1] = make_uint2(0xffffffffu, 0u);
+    bp[kSlots - 1] = 63 << 8;
     {
       const float2 wn = fp.win[n];
-      const float Ta = R2 * wn.x, scale = __fdividef(wn.y, R2);
+      const float Ta = R2 * wn.x, scale = wn.y * rcpR2;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
-        kv[s] = make_uint2(0xffffffffu, 0u);
-        bp[s] = 63 << 8;
-        if (lane + 32 * s < n) {
-          kv[s] = ws.keys[lane + 32 * s];
-          /* monotone in dist²: subtraction, multiplication by a positive constant, floor, clamp */
-          const int bin = min(max(__float2int_rd((__uint_as_float(kv[s].x) - Ta) * scale) + 1, 0), 30);
-          bp[s] = (bin << 8) | atomicAdd(&ws.hist[bin], 1);
-        }
+        if (s == kSlots - 1 && !four) break;
+        /* branch-free: slots past n read stale entries, count nothing and become +inf */
+        const bool valid = lane + 32 * s < n;
+        kv[s] = ws.keys[lane + 32 * s];
+        /* monotone in dist²: subtraction, multiplication by a positive constant, floor, clamp */
+        const int bin = min(max(__float2int_rd((__uint_as_float(kv[s].x) - Ta) * scale) + 1, 0), 30);
+        int pos = 0;
+        if (valid) pos = atomicAdd(&ws.hist[bin], 1);
+        bp[s] = valid ? (bin << 8) | pos : 63 << 8;
+        if (!valid) kv[s].x = 0xffffffffu;
       }
     }
     __syncwarp();
@@ -652,7 +668,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
     if (exact) {
 #pragma unroll
       for (int s = 0; s < kSlots; s++)
-        if ((bp[s] >> 8) == kbin) ws.bl[bp[s] & 255] = kv[s].x;
+        if ((bp[s] >> 8) == kbin) ws.bl[bp[s] & 255] = kv[s].x; /* an unused fourth slot holds bin 63 */
       __syncwarp();
       /* one member per lane: tau = the (k - clo)-th smallest of them */
       const int need = k - clo;
@@ -676,6 +692,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
       int base = 0;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
+        if (s == kSlots - 1 && !four) break;
         const bool a = kv[s].x <= tau;
         const unsigned b = __ballot_sync(0xffffffffu, a);
         if (a) ws.keys[base + __popc(b & lt)] = kv[s];
@@ -684,10 +701,10 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
       __syncwarp();
       int2* ids2 = reinterpret_cast<int2*>(io.ids + (size_t)qi * k); /* k is even: rows are 8-byte aligned */
       float2* d22 = io.d2 ? reinterpret_cast<float2*>(io.d2 + (size_t)qi * k) : nullptr;
-      for (int p = lane; 2 * p < k; p += 32) {
-        const uint4 e = reinterpret_cast<const uint4*>(ws.keys)[p]; /* entries 2p, 2p + 1 */
-        ids2[p] = make_int2((int)e.y, (int)e.w);
-        if (d22) d22[p] = make_float2(__uint_as_float(e.x), __uint_as_float(e.z));
+      if (2 * lane < k) { /* k <= 64: one pair of entries (2 lane, 2 lane + 1) per lane */
+        const uint4 e = reinterpret_cast<const uint4*>(ws.keys)[lane];
+        ids2[lane] = make_int2((int)e.y, (int)e.w);
+        if (d22) d22[lane] = make_float2(__uint_as_float(e.x), __uint_as_float(e.z));
       }
       if (io.r2 && lane == 0) io.r2[qi] = __uint_as_float(tau);
     } else {
@@ -1133,6 +1150,7 @@ int grid_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gath
     fp.margin_c = map->cell_margin * map->inv_cell;
     const float rc = std::sqrt(fp.R2) * map->inv_cell + 2.f * fp.margin_c;
     fp.Rc2 = rc * rc;
+    fp.rcpR2 = 1.f / fp.R2;
     for (int n = 0; n < kWinSize; n++) {
       const float fk = (float)io.k, fn = (float)std::max(n, io.k);
       const float delta = 3.f * std::sqrt(fk * (1.f - fk / fn)) + 2.f;

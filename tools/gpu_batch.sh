@@ -20,6 +20,7 @@ timeout 300 python tools/prof_emit.py cornell 4000000 3 > gpurun_out/${tag}_plai
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_walk -s 1 -c 1 -o gpurun_out/${tag}_walk \
   python tools/prof_emit.py cornell 4000000 3 > gpurun_out/${tag}_ncu_w.log 2>&1
 timeout 300 python tools/prof_build.py 10000000 2 > gpurun_out/${tag}_plain_build.log 2>&1 && \
-timeout 1500 ncu --set full --clock-control none -k regex:'k_extract|k_split|k_level|k_finish_subtrees|k_emit_nodes|k_make_soa|k_gather|k_cell_ids|k_grid_fill|DeviceRadixSort' \
-  -o gpurun_out/${tag}_build python tools/prof_build.py 10000000 1 > gpurun_out/${tag}_ncu_b.log 2>&1
+timeout 1500 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__inst_executed.avg.per_cycle_active,l1tex__throughput.avg.pct_of_peak_sustained_elapsed,lts__throughput.avg.pct_of_peak_sustained_elapsed,gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed,sm__warps_active.avg.pct_of_peak_sustained_active,launch__registers_per_thread \
+  --clock-control none -o gpurun_out/${tag}_build python tools/prof_build.py 10000000 1 > gpurun_out/${tag}_ncu_b.log 2>&1
+du -sh gpurun_out
 ls -la gpurun_out | tail -30
