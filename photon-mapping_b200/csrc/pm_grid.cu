@@ -54,6 +54,7 @@ constexpr int64_t kMinCellCap = (int64_t)1 << 24, kMaxCellCap = (int64_t)1 << 30
 struct GridView {
   const float4* pts;
   const uint32_t* cell_start;
+  const uint32_t* cell_start_t; /* fast-path maps: the same offsets with x slowest, [(x * nz + z) * ny + y], x in [0, nx] */
   float lo[3];
   float cell, inv_cell, margin;
   int nx, ny, nz;
@@ -462,26 +463,30 @@ constexpr int kFastWords = 12;                /* flat index space of one round o
 constexpr int kFastMaxScan = kFastWords * 32;
 constexpr int kFastMaxH = 4;                  /* widest block of the fast path: 9x9 rows (3 rounds) */
 constexpr int kFastAttempts = 4;
+constexpr int kFastProbes = 12;               /* counting probes per query before it is handed over */
 
 struct __align__(16) FastScratch {
   uint2 keys[kBuf];         /* (dist² bits, node id) of the candidates inside the search radius */
   uint2 words[kFastWords];  /* x: bitmap of row starts among elements [32 i, 32 i + 32); y: row holding element 32 i */
   int off[32];              /* per non-empty row: first record - first flat index */
-  int hist[32];
-  uint32_t bl[32];          /* dist² bits of the bin that holds the k-th candidate */
 };
 
-/* histogram window per candidate count n (count ~ r^3, binomial spread at the k-th): bin 0 ends at Ta = R2 * x,
- * 30 linear bins up to R2 with scale = y / R2 */
+/* first counting threshold per candidate count n: T = R2 * win[n], the dist² below which k of n candidates are
+ * expected (count ~ r^3) */
 constexpr int kWinSize = kBuf + 1;
 struct FastParams {
   const float4* sq;   /* queries in processing order */
   float R2;           /* first search radius², already capped by the block guarantee and the cutoff */
   float Rc2;          /* (its radius in cells + the margins)² */
-  float rcpR2;        /* 1 / R2 */
   float margin_c;     /* GridView::margin in cells */
-  float2 win[kWinSize];
+  float win[kWinSize];
 };
+
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 
 __device__ __forceinline__ float sqrt_approx(float x) {
   float r;
@@ -520,13 +525,12 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
     const int cx = min(max(__float2int_rd(fx), 0), g.nx - 1), cy = min(max(__float2int_rd(fy), 0), g.ny - 1),
               cz = min(max(__float2int_rd(fz), 0), g.nz - 1);
     const float uy = fy - (float)cy, uz = fz - (float)cz; /* position inside the own cell, in cells */
-    ws.hist[lane] = 0;
 
     /* ---- candidates: rows of the (2h+1)^3 block trimmed to the ball, flattened, scanned. Everything is in cell
      * units; the margins cover the rounding of this and of the build's cell assignment. ---- */
     int h = 2, n = 0, attempt = 0, r0 = 0, nrows = 25;
     int oy = oy5, oz = oz5;
-    float R2 = fp.R2, Rc2 = fp.Rc2, rcpR2 = fp.rcpR2;
+    float R2 = fp.R2, Rc2 = fp.Rc2;
     bool give_up = false;
     while (true) {
       {
@@ -539,9 +543,11 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
           const float w = sqrt_approx(t2) * 1.0001f; /* half-width of the ball in this row, rounded up */
           const int xa = max(__float2int_rd(fx - w), max(cx - h, 0)), xb = min(__float2int_rd(fx + w), min(cx + h, g.nx - 1));
           if (xa <= xb) {
-            const uint32_t* cs = g.cell_start + (uint32_t)((rz * g.ny + ry) * g.nx); /* < 2^30 cells */
-            st = (int)__ldg(cs + xa);
-            len = (int)__ldg(cs + xb + 1) - st;
+            /* the x-slowest copy of the offset table: the five rows of a z-slab that share xa sit in one 20-byte run,
+             * so the 25 lanes touch about a dozen 128-byte lines per load instead of 22 (< 2^30 cells: 32-bit index) */
+            const int zy = rz * g.ny + ry, plane = g.nz * g.ny;
+            st = (int)__ldg(g.cell_start_t + (uint32_t)(xa * plane + zy));
+            len = (int)__ldg(g.cell_start_t + (uint32_t)((xb + 1) * plane + zy)) - st;
           }
         }
         int incl = len;
@@ -566,17 +572,22 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
             for (int i = (P + 31) >> 5; i * 32 < P + len; i++) ws.words[i].y = (unsigned)d;
           }
           __syncwarp();
-          /* full steps two at a time: both addresses come out of shared memory first, so two record loads per lane
-           * are in flight before the first distance is needed (one step's chain LDS -> LDS -> LDG -> compare is ~400
-           * cycles; with one load in flight the warps of an SM cannot cover it) */
+          /* the per-row offsets move from shared memory into registers (lane d holds row d's): a step fetches its
+           * offset with one shuffle */
+          const int offreg = ws.off[lane];
+          /* full steps two at a time: both addresses are known before the first record arrives, so two loads per lane
+           * are in flight (one step's chain LDS -> SHFL -> LDG -> compare is ~400 cycles; with one load in flight the
+           * warps of an SM cannot cover it). Unrolled over the 12 words of the flat space: constant smem addresses. */
           int i = 0;
-          for (; (i + 2) * 32 <= mc; i += 2) {
+#pragma unroll
+          for (int pr = 0; pr < kFastWords / 2; pr++) {
+            if ((2 * pr + 2) * 32 > mc) break;
             float4 p[2];
 #pragma unroll
             for (int u = 0; u < 2; u++) {
-              const uint2 w = ws.words[i + u];
+              const uint2 w = ws.words[2 * pr + u];
               const int run = (int)w.y + __popc(w.x & le_not0);
-              p[u] = __ldg(g.pts + (ws.off[run] + (i + u) * 32 + lane));
+              p[u] = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + (2 * pr + u) * 32 + lane));
             }
 #pragma unroll
             for (int u = 0; u < 2; u++) {
@@ -587,13 +598,14 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
               if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p[u].w));
               n += __popc(b);
             }
+            i = 2 * pr + 2;
           }
           for (; i * 32 < mc; i++) {
             const int j = i * 32 + lane;
             const uint2 w = ws.words[i];
             const int run = (int)w.y + __popc(w.x & le_not0);
             /* lanes past the end read a record behind the last row (the array is padded) and drop it */
-            const float4 p = __ldg(g.pts + (ws.off[run] + j));
+            const float4 p = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + j));
             const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
             const bool pass = j < mc && d2 < R2;
             const unsigned b = __ballot_sync(0xffffffffu, pass);
@@ -612,7 +624,6 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
         h = max(__float2int_ru(Rc + 2.f * fp.margin_c), 2);
         if (h > kFastMaxH) { give_up = true; break; }
         Rc2 = Rc * Rc;
-        rcpR2 = __fdividef(1.f, R2);
         nrows = (2 * h + 1) * (2 * h + 1);
         r0 = 0; n = 0;
       }
@@ -629,56 +640,45 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
     }
     __syncwarp();
 
-    /* ---- the k-th smallest dist²: histogram over [Ta, R2), bin 0 = everything expected below k - 3 sigma ---- */
+    /* ---- the k-th smallest dist², by counting: every lane holds its 3 - 4 candidates in registers, a probe counts
+     * those with dist² <= T (per-lane compares + one warp reduction) and the bracket (Tlo, Thi] is narrowed by linear
+     * interpolation on the counts until exactly k lie below T. No histogram: shared-memory atomics cost about one
+     * L1 wavefront per lane and were half of this kernel's shared-memory traffic. The first T is the quantile the
+     * count ~ r^3 law predicts for the n candidates found. ---- */
     uint2 kv[kSlots];
-    int bp[kSlots]; /* bin << 8 | position in the bin */
     const bool four = n > 3 * 32; /* the fourth register slot is needed by about one query in five */
     kv[kSlots - 1] = make_uint2(0xffffffffu, 0u);
-    bp[kSlots - 1] = 63 << 8;
-    {
-      const float2 wn = fp.win[n];
-      const float Ta = R2 * wn.x, scale = wn.y * rcpR2;
 #pragma unroll
-      for (int s = 0; s < kSlots; s++) {
-        if (s == kSlots - 1 && !four) break;
-        /* branch-free: slots past n read stale entries, count nothing and become +inf */
-        const bool valid = lane + 32 * s < n;
-        kv[s] = ws.keys[lane + 32 * s];
-        /* monotone in dist²: subtraction, multiplication by a positive constant, floor, clamp */
-        const int bin = min(max(__float2int_rd((__uint_as_float(kv[s].x) - Ta) * scale) + 1, 0), 30);
-        int pos = 0;
-        if (valid) pos = atomicAdd(&ws.hist[bin], 1);
-        bp[s] = valid ? (bin << 8) | pos : 63 << 8;
-        if (!valid) kv[s].x = 0xffffffffu;
+    for (int s = 0; s < kSlots; s++) {
+      if (s == kSlots - 1 && !four) break;
+      kv[s] = ws.keys[lane + 32 * s]; /* branch-free: slots past n read stale entries and become +inf */
+      if (lane + 32 * s >= n) kv[s].x = 0xffffffffu;
+    }
+    uint32_t tau = 0u;
+    bool exact = false;
+    {
+      float Tlo = 0.f, Thi = R2, T = n == k ? R2 : R2 * fp.win[n]; /* every candidate has dist² < R2 */
+      int clo = 0, chi = n;
+#pragma unroll 1
+      for (int it = 0; it < kFastProbes; it++) {
+        const uint32_t tb = __float_as_uint(T);
+        int c = (kv[0].x <= tb) + (kv[1].x <= tb) + (kv[2].x <= tb);
+        if (four) c += kv[3].x <= tb;
+        c = __reduce_add_sync(0xffffffffu, c);
+        if (c == k) {
+          uint32_t m = 0u;
+#pragma unroll
+          for (int s = 0; s < kSlots; s++) m = max(m, kv[s].x <= tb ? kv[s].x : 0u);
+          tau = __reduce_max_sync(0xffffffffu, m); /* the k-th smallest itself */
+          exact = true;
+          break;
+        }
+        if (c < k) { Tlo = T; clo = c; } else { Thi = T; chi = c; }
+        T = Tlo + (Thi - Tlo) * ((float)(k - clo) * rcp_approx((float)(chi - clo))); /* clo < k < chi */
+        if (!(T > Tlo && T < Thi)) break; /* no value left between the bracket's ends */
       }
     }
-    __syncwarp();
-    const int cntb = ws.hist[lane]; /* hist[31] stays 0 */
-    int incl = cntb;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
-    }
-    const int kbin = __popc(__ballot_sync(0xffffffffu, incl < k)); /* first bin whose running count reaches k; n >= k */
-    const int clo = __shfl_sync(0xffffffffu, incl - cntb, kbin);
-    const int nb = __shfl_sync(0xffffffffu, cntb, kbin);
-    uint32_t tau = 0u;
-    bool exact = nb <= 32;
-    if (exact) {
-#pragma unroll
-      for (int s = 0; s < kSlots; s++)
-        if ((bp[s] >> 8) == kbin) ws.bl[bp[s] & 255] = kv[s].x; /* an unused fourth slot holds bin 63 */
-      __syncwarp();
-      /* one member per lane: tau = the (k - clo)-th smallest of them */
-      const int need = k - clo;
-      const uint32_t mine = lane < nb ? ws.bl[lane] : 0xffffffffu;
-      int rank = 0;
-      for (int j = 0; j < nb; j++) rank += ws.bl[j] < mine;
-      tau = __reduce_max_sync(0xffffffffu, rank < need ? mine : 0u); /* lanes >= nb hold rank nb >= need */
-      exact = __popc(__ballot_sync(0xffffffffu, mine <= tau)) == need;
-    }
-    if (!exact) { /* over-full bin, or equal distances at the k-th place: the id order decides */
+    if (!exact) { /* equal distances at the k-th place (the id order decides), or an odd distribution */
       if (lane == 0) ho_list[atomicAdd(ho_count, 1)] = qi;
       __syncwarp();
       continue;
@@ -969,6 +969,16 @@ __global__ void k_grid_fill(const float4* __restrict__ nodes, int n, const uint3
   }
 }
 
+/* cell_start[(z * ny + y) * nx + x] -> cell_start_t[(x * nz + z) * ny + y] for x in [0, nx]; column nx holds the end
+ * of every row (= the start of the next row's first cell) */
+__global__ void k_cells_transpose(const uint32_t* __restrict__ cs, int nx, int ny, int nz, uint32_t* __restrict__ out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t rows = (int64_t)ny * nz;
+  if (t >= rows * (nx + 1)) return;
+  const int64_t x = t / rows, zy = t - x * rows; /* consecutive threads write consecutive words */
+  out[t] = __ldg(cs + zy * nx + x);
+}
+
 __global__ void k_sample_queries(const float4* __restrict__ nodes, int n, int ns, float* __restrict__ q) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= ns) return;
@@ -979,7 +989,7 @@ __global__ void k_sample_queries(const float4* __restrict__ nodes, int n, int ns
 
 GridView view_of(const pm_map* m) {
   GridView g;
-  g.pts = m->grid_pts; g.cell_start = m->cell_start;
+  g.pts = m->grid_pts; g.cell_start = m->cell_start; g.cell_start_t = m->cell_start_t;
   for (int d = 0; d < 3; d++) g.lo[d] = m->bounds[d];
   g.cell = m->cell; g.inv_cell = m->inv_cell; g.margin = m->cell_margin;
   g.nx = m->gdim[0]; g.ny = m->gdim[1]; g.nz = m->gdim[2];
@@ -1122,6 +1132,18 @@ int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
                                                                     m->grid_pts, m->cell_start);
   ctx->launches += 6;
   PM_CUDA(cudaGetLastError());
+  if (m->fast_path) {
+    const int64_t words = (int64_t)(dim[0] + 1) * dim[1] * dim[2];
+    if (pm::map_alloc(&m->cell_start_t, sizeof(uint32_t) * (size_t)words, st) != cudaSuccess) {
+      cudaGetLastError();
+      m->cell_start_t = nullptr;
+      m->fast_path = false; /* the general kernel answers everything */
+    } else {
+      k_cells_transpose<<<(unsigned)div_up(words, 256), 256, 0, st>>>(m->cell_start, dim[0], dim[1], dim[2], m->cell_start_t);
+      ctx->launches++;
+      PM_CUDA(cudaGetLastError());
+    }
+  }
   return PM_OK;
 }
 
@@ -1150,13 +1172,8 @@ int grid_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gath
     fp.margin_c = map->cell_margin * map->inv_cell;
     const float rc = std::sqrt(fp.R2) * map->inv_cell + 2.f * fp.margin_c;
     fp.Rc2 = rc * rc;
-    fp.rcpR2 = 1.f / fp.R2;
-    for (int n = 0; n < kWinSize; n++) {
-      const float fk = (float)io.k, fn = (float)std::max(n, io.k);
-      const float delta = 3.f * std::sqrt(fk * (1.f - fk / fn)) + 2.f;
-      const float x = std::pow(std::max(fk - delta, 0.5f) / fn, 2.f / 3.f);
-      fp.win[n] = make_float2(x, 30.f / (1.f - x));
-    }
+    for (int n = 0; n < kWinSize; n++)
+      fp.win[n] = std::pow(((float)io.k + 0.5f) / (float)std::max(n, io.k + 1), 2.f / 3.f);
     const unsigned fgrid = (unsigned)std::min<int64_t>(div_up(io.nq, kWarps), (int64_t)ctx->sm_count * 6 * 4);
     if (gather) k_knn_fast<true><<<fgrid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fp, ho_list, ho_count);
     else k_knn_fast<false><<<fgrid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fp, ho_list, ho_count);

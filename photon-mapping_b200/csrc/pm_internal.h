@@ -127,6 +127,7 @@ struct pm_map {
   /* uniform-grid copy for the warp-cooperative query kernels (pm_grid.cu); absent for small maps */
   float4* grid_pts = nullptr;                /* (x, y, z, bits(node id)) sorted by cell, x fastest */
   uint32_t* cell_start = nullptr;            /* n_cells + 1 offsets into grid_pts */
+  uint32_t* cell_start_t = nullptr;          /* fast-path maps: the offsets again with x slowest ((nx + 1) * ny * nz words) */
   float cell = 0.f, inv_cell = 0.f, cell_margin = 0.f;
   int gdim[3] = {0, 0, 0};
   float tuned_rk = 0.f;                      /* sampled k-th neighbour distance the cell size came from */

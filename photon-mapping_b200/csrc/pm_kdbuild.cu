@@ -792,6 +792,7 @@ void pm_map_destroy(pm_map* m) {
   pm::map_free(m->color4);
   pm::map_free(m->grid_pts);
   pm::map_free(m->cell_start);
+  pm::map_free(m->cell_start_t);
   cudaStreamSynchronize((cudaStream_t)0); /* the frees have happened: the next build may take the memory on its own stream */
   delete m;
 }

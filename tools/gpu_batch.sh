@@ -7,10 +7,16 @@ mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/${tag}_smi.txt 2>&1
 timeout 1500 python -m pytest tests -m gpu -q -rP > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest exit $?" >> gpurun_out/${tag}_pytest.log
 tail -5 gpurun_out/${tag}_pytest.log
+B="python bench.py --steps 3 --warmup 3 --no-pipelines --no-cpu-baseline --no-stage-extras"
+if [ -n "$quick" ]; then
+  timeout 600 python bench.py --steps 20 --warmup 3 --no-pipelines --no-cpu-baseline --no-stage-extras > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench exit $?"
+  tail -c 1200 gpurun_out/${tag}_bench.json; tail -5 gpurun_out/${tag}_bench.err
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'k_knn_fast' -s 4 -c 1 \
+    -o gpurun_out/${tag}_knn_step $B > gpurun_out/${tag}_ncu_f.log 2>&1
+  du -sh gpurun_out; exit 0
+fi
 timeout 1200 python bench.py --steps 20 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench exit $?"
 tail -c 600 gpurun_out/${tag}_bench.json; tail -5 gpurun_out/${tag}_bench.err
-if [ -n "$quick" ]; then exit 0; fi
-B="python bench.py --steps 3 --warmup 3 --no-pipelines --no-cpu-baseline --no-stage-extras"
 timeout 600 $B > gpurun_out/${tag}_plain.log 2>&1 && \
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/${tag}_launches.csv $B > gpurun_out/${tag}_ncu_l.log 2>&1
 # one warm pm_knn step: its six kernels (3 binning + fast + general + kd), skipping the 3 builds' tuning samples and 3 warm-up steps
