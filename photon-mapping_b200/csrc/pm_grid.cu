@@ -575,42 +575,44 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
           /* the per-row offsets move from shared memory into registers (lane d holds row d's): a step fetches its
            * offset with one shuffle */
           const int offreg = ws.off[lane];
-          /* full steps two at a time: both addresses are known before the first record arrives, so two loads per lane
-           * are in flight (one step's chain LDS -> SHFL -> LDG -> compare is ~400 cycles; with one load in flight the
-           * warps of an SM cannot cover it). Unrolled over the 12 words of the flat space: constant smem addresses. */
-          int i = 0;
+          /* Steps in pairs, software-pipelined: the records of pair i + 1 are requested before pair i is tested, so two
+           * to four loads per lane are in flight (one step's chain LDS -> SHFL -> LDG -> compare is ~400 cycles; with
+           * one load in flight the warps of an SM cannot cover it). Unrolled over the 12 words of the flat space
+           * (constant shared-memory addresses); a step past the end of the flat space loads nothing and tests
+           * nothing, lanes past the end read a record behind the last row (the array is padded) and drop it. */
+          const int steps = (mc + 31) >> 5;
+          float4 pc[2], pn[2];
+#pragma unroll
+          for (int u = 0; u < 2; u++) {
+            if (u < steps) {
+              const uint2 w = ws.words[u];
+              const int run = (int)w.y + __popc(w.x & le_not0);
+              pc[u] = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + u * 32 + lane));
+            }
+          }
 #pragma unroll
           for (int pr = 0; pr < kFastWords / 2; pr++) {
-            if ((2 * pr + 2) * 32 > mc) break;
-            float4 p[2];
+            if (2 * pr >= steps) break;
 #pragma unroll
             for (int u = 0; u < 2; u++) {
-              const uint2 w = ws.words[2 * pr + u];
-              const int run = (int)w.y + __popc(w.x & le_not0);
-              p[u] = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + (2 * pr + u) * 32 + lane));
+              if (pr + 1 < kFastWords / 2 && 2 * pr + 2 + u < steps) {
+                const uint2 w = ws.words[2 * pr + 2 + u];
+                const int run = (int)w.y + __popc(w.x & le_not0);
+                pn[u] = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + (2 * pr + 2 + u) * 32 + lane));
+              }
             }
 #pragma unroll
             for (int u = 0; u < 2; u++) {
-              const float d2 = pmk::dist2(p[u].x, p[u].y, p[u].z, qx, qy, qz);
-              const bool pass = d2 < R2;
-              const unsigned b = __ballot_sync(0xffffffffu, pass);
-              /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
-              if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p[u].w));
-              n += __popc(b);
+              if (2 * pr + u < steps) {
+                const float d2 = pmk::dist2(pc[u].x, pc[u].y, pc[u].z, qx, qy, qz);
+                const bool pass = (2 * pr + u) * 32 + lane < mc && d2 < R2;
+                const unsigned b = __ballot_sync(0xffffffffu, pass);
+                /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
+                if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(pc[u].w));
+                n += __popc(b);
+              }
             }
-            i = 2 * pr + 2;
-          }
-          for (; i * 32 < mc; i++) {
-            const int j = i * 32 + lane;
-            const uint2 w = ws.words[i];
-            const int run = (int)w.y + __popc(w.x & le_not0);
-            /* lanes past the end read a record behind the last row (the array is padded) and drop it */
-            const float4 p = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + j));
-            const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
-            const bool pass = j < mc && d2 < R2;
-            const unsigned b = __ballot_sync(0xffffffffu, pass);
-            if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p.w));
-            n += __popc(b);
+            pc[0] = pn[0]; pc[1] = pn[1];
           }
         }
       }
@@ -662,8 +664,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
 #pragma unroll 1
       for (int it = 0; it < kFastProbes; it++) {
         const uint32_t tb = __float_as_uint(T);
-        int c = (kv[0].x <= tb) + (kv[1].x <= tb) + (kv[2].x <= tb);
-        if (four) c += kv[3].x <= tb;
+        int c = (kv[0].x <= tb) + (kv[1].x <= tb) + (kv[2].x <= tb) + (kv[3].x <= tb); /* an unused slot is +inf */
         c = __reduce_add_sync(0xffffffffu, c);
         if (c == k) {
           uint32_t m = 0u;
