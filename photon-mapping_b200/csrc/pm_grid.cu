@@ -495,7 +495,7 @@ __device__ __forceinline__ float sqrt_approx(float x) {
 }
 
 template <bool GATHER>
-__global__ void __launch_bounds__(kWarps * 32, GATHER ? 4 : 5) /* no spills: a reloaded value is no longer warp-uniform to the compiler */
+__global__ void __launch_bounds__(kWarps * 32, GATHER ? 4 : 6) /* no spills: a reloaded value is no longer warp-uniform to the compiler */
 k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::QueryIO io, const __grid_constant__ FastParams fp,
            int* __restrict__ ho_list, int* __restrict__ ho_count) {
   __shared__ FastScratch scratch[kWarps];
@@ -575,44 +575,42 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
           /* the per-row offsets move from shared memory into registers (lane d holds row d's): a step fetches its
            * offset with one shuffle */
           const int offreg = ws.off[lane];
-          /* Steps in pairs, software-pipelined: the records of pair i + 1 are requested before pair i is tested, so two
-           * to four loads per lane are in flight (one step's chain LDS -> SHFL -> LDG -> compare is ~400 cycles; with
-           * one load in flight the warps of an SM cannot cover it). Unrolled over the 12 words of the flat space
-           * (constant shared-memory addresses); a step past the end of the flat space loads nothing and tests
-           * nothing, lanes past the end read a record behind the last row (the array is padded) and drop it. */
-          const int steps = (mc + 31) >> 5;
-          float4 pc[2], pn[2];
-#pragma unroll
-          for (int u = 0; u < 2; u++) {
-            if (u < steps) {
-              const uint2 w = ws.words[u];
-              const int run = (int)w.y + __popc(w.x & le_not0);
-              pc[u] = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + u * 32 + lane));
-            }
-          }
+          /* full steps two at a time: both addresses are known before the first record arrives, so two loads per lane
+           * are in flight (one step's chain LDS -> SHFL -> LDG -> compare is ~400 cycles; with one load in flight the
+           * warps of an SM cannot cover it). Unrolled over the 12 words of the flat space: constant smem addresses. */
+          int i = 0;
 #pragma unroll
           for (int pr = 0; pr < kFastWords / 2; pr++) {
-            if (2 * pr >= steps) break;
+            if ((2 * pr + 2) * 32 > mc) break;
+            float4 p[2];
 #pragma unroll
             for (int u = 0; u < 2; u++) {
-              if (pr + 1 < kFastWords / 2 && 2 * pr + 2 + u < steps) {
-                const uint2 w = ws.words[2 * pr + 2 + u];
-                const int run = (int)w.y + __popc(w.x & le_not0);
-                pn[u] = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + (2 * pr + 2 + u) * 32 + lane));
-              }
+              const uint2 w = ws.words[2 * pr + u];
+              const int run = (int)w.y + __popc(w.x & le_not0);
+              p[u] = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + (2 * pr + u) * 32 + lane));
             }
 #pragma unroll
             for (int u = 0; u < 2; u++) {
-              if (2 * pr + u < steps) {
-                const float d2 = pmk::dist2(pc[u].x, pc[u].y, pc[u].z, qx, qy, qz);
-                const bool pass = (2 * pr + u) * 32 + lane < mc && d2 < R2;
-                const unsigned b = __ballot_sync(0xffffffffu, pass);
-                /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
-                if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(pc[u].w));
-                n += __popc(b);
-              }
+              const float d2 = pmk::dist2(p[u].x, p[u].y, p[u].z, qx, qy, qz);
+              const bool pass = d2 < R2;
+              const unsigned b = __ballot_sync(0xffffffffu, pass);
+              /* beyond the buffer everything lands in the last slot; n > kBuf is detected below */
+              if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p[u].w));
+              n += __popc(b);
             }
-            pc[0] = pn[0]; pc[1] = pn[1];
+            i = 2 * pr + 2;
+          }
+          for (; i * 32 < mc; i++) {
+            const int j = i * 32 + lane;
+            const uint2 w = ws.words[i];
+            const int run = (int)w.y + __popc(w.x & le_not0);
+            /* lanes past the end read a record behind the last row (the array is padded) and drop it */
+            const float4 p = __ldg(g.pts + (__shfl_sync(0xffffffffu, offreg, run) + j));
+            const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+            const bool pass = j < mc && d2 < R2;
+            const unsigned b = __ballot_sync(0xffffffffu, pass);
+            if (pass) ws.keys[min(n + __popc(b & lt), kBuf - 1)] = make_uint2(__float_as_uint(d2), __float_as_uint(p.w));
+            n += __popc(b);
           }
         }
       }
