@@ -459,8 +459,9 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
  *     block if the exactness bound needs one (balls cut by the cloud's faces take this path); what still fails
  *     after kFastAttempts goes to the hand-over list that k_grid_query answers.
  * Queries arrive pre-ordered as float4 (x, y, z, bits(index)) from the binning pass of pm_knn.cu. */
-constexpr int kFastWords = 12;                /* flat index space of one round of rows: 384 candidates */
-constexpr int kFastMaxScan = kFastWords * 32;
+constexpr int kFastWords = 24;                /* flat index space of one round of rows: 768 candidates (the rows of a */
+constexpr int kFastMaxScan = kFastWords * 32; /* retry on a 7- or 9-cell-wide block are up to 9 cells long)            */
+constexpr int kFastPairs = 6;                 /* steps taken two at a time by the unrolled part of the scan (a 5x5x5 block needs ~8) */
 constexpr int kFastMaxH = 4;                  /* widest block of the fast path: 9x9 rows (3 rounds) */
 constexpr int kFastAttempts = 4;
 constexpr int kFastProbes = 12;               /* counting probes per query before it is handed over */
@@ -580,7 +581,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
            * warps of an SM cannot cover it). Unrolled over the 12 words of the flat space: constant smem addresses. */
           int i = 0;
 #pragma unroll
-          for (int pr = 0; pr < kFastWords / 2; pr++) {
+          for (int pr = 0; pr < kFastPairs; pr++) {
             if ((2 * pr + 2) * 32 > mc) break;
             float4 p[2];
 #pragma unroll

@@ -33,36 +33,36 @@ __device__ __forceinline__ uint32_t part1by2(uint32_t v) {
 struct Box6 { float lo[3]; float inv[3]; };
 
 /* ---- query ordering: counting sort into Morton bins ------------------------------------------------
- * 7 bits per axis inside the map's box (queries outside are clamped onto its faces) + one last bin for queries that
+ * 4 to 7 bits per axis inside the map's box (queries outside are clamped onto its faces) + one last bin for queries that
  * will not be evaluated (brdf <= 0), so whole warps retire at once. Three kernels: histogram (one global atomic per
- * query, the last bin warp-aggregated), exclusive scan of the 2^21 + 1 counters (single pass, decoupled look-back),
+ * query, the last bin warp-aggregated), exclusive scan of the counters (single pass, decoupled look-back),
  * scatter (the atomic's return value is the slot inside the bin). The order inside a bin is whatever the atomics
  * hand out; results do not depend on it. */
-constexpr int kQBits = 7;
-constexpr int kQBins = (1 << (3 * kQBits)) + 1;
+constexpr int kQBitsMax = 7;
+constexpr int kQBinsMax = (1 << (3 * kQBitsMax)) + 1;
 constexpr int kScanTile = 2048;                       /* counters per CTA of the scan: 256 threads x 8 */
-constexpr int kScanTiles = (kQBins + kScanTile - 1) / kScanTile;
+constexpr int kScanTilesMax = (kQBinsMax + kScanTile - 1) / kScanTile;
 
 __device__ __forceinline__ uint32_t bin_of(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int i,
-                                           const Box6& box) {
-  if (skip_if_not_positive && !(skip_if_not_positive[i] > 0.f)) return (uint32_t)(kQBins - 1);
+                                           const Box6& box, int bits) {
+  if (skip_if_not_positive && !(skip_if_not_positive[i] > 0.f)) return 1u << (3 * bits);
   uint32_t code = 0;
 #pragma unroll
   for (int d = 0; d < 3; d++) {
     float t = (q[(size_t)i * 3 + d] - box.lo[d]) * box.inv[d];
-    t = fminf(fmaxf(t, 0.f), (float)((1 << kQBits) - 1)); /* drops NaN */
+    t = fminf(fmaxf(t, 0.f), (float)((1 << bits) - 1)); /* drops NaN */
     code |= part1by2((uint32_t)t) << d;
   }
   return code;
 }
 
-__global__ void k_qbin_count(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int nq, Box6 box,
+__global__ void k_qbin_count(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int nq, Box6 box, int bits,
                              uint32_t* __restrict__ codes, uint32_t* __restrict__ hist) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const bool in = i < nq;
-  const uint32_t code = in ? bin_of(q, skip_if_not_positive, i, box) : 0u;
+  const uint32_t code = in ? bin_of(q, skip_if_not_positive, i, box, bits) : 0u;
   if (in) codes[i] = code;
-  const bool last = in && code == (uint32_t)(kQBins - 1);
+  const bool last = in && code == 1u << (3 * bits);
   const unsigned lb = __ballot_sync(0xffffffffu, last);
   if (last) { if ((threadIdx.x & 31) == __ffs(lb) - 1) atomicAdd(hist + code, (uint32_t)__popc(lb)); }
   else if (in) atomicAdd(hist + code, 1u);
@@ -140,12 +140,12 @@ k_qbin_scan(uint32_t* __restrict__ hist, int nbins, unsigned long long* __restri
   }
 }
 
-__global__ void k_qbin_scatter(const float* __restrict__ q, const uint32_t* __restrict__ codes, int nq,
+__global__ void k_qbin_scatter(const float* __restrict__ q, const uint32_t* __restrict__ codes, int nq, int bits,
                                uint32_t* __restrict__ cursor, int* __restrict__ perm, float4* __restrict__ sq) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const bool in = i < nq;
   const uint32_t code = in ? codes[i] : 0u;
-  const bool last = in && code == (uint32_t)(kQBins - 1);
+  const bool last = in && code == 1u << (3 * bits);
   const unsigned lb = __ballot_sync(0xffffffffu, last);
   uint32_t pos = 0;
   if (last) {
@@ -169,23 +169,27 @@ int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float
   PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)nq, &codes));
   PM_CHECK(ctx->get_scratch(pm::S_PERM, (size_t)nq, &perm));
   if (sq_out) PM_CHECK(ctx->get_scratch(pm::S_VALS1, (size_t)nq, &sq));
+  /* bins per axis: about four queries per bin, 2^4 .. 2^7 (a finer grid only costs the scan) */
+  int bits = 4;
+  while (bits < kQBitsMax && ((int64_t)1 << (3 * bits)) * 4 < nq) bits++;
+  const int bins = (1 << (3 * bits)) + 1, tiles = (bins + kScanTile - 1) / kScanTile;
   /* counters, then the scan's tile states and its tile counter: one memset */
-  const size_t hist_words = ((size_t)kQBins + 3) & ~(size_t)3;
-  const size_t bytes = hist_words * 4 + (size_t)kScanTiles * 8 + 16;
+  const size_t hist_words = ((size_t)bins + 3) & ~(size_t)3;
+  const size_t bytes = hist_words * 4 + (size_t)tiles * 8 + 16;
   PM_CHECK(ctx->get_scratch(pm::S_KEYS1, bytes, &hist));
   unsigned long long* status = reinterpret_cast<unsigned long long*>(hist + hist_words);
-  int* tile_counter = reinterpret_cast<int*>(status + kScanTiles);
+  int* tile_counter = reinterpret_cast<int*>(status + tiles);
   PM_CUDA(cudaMemsetAsync(hist, 0, bytes, ctx->stream));
   Box6 box;
   for (int d = 0; d < 3; d++) {
     box.lo[d] = map->bounds[d];
     const float w = map->bounds[3 + d] - map->bounds[d];
-    box.inv[d] = w > 0.f ? (float)(1 << kQBits) / w : 0.f;
+    box.inv[d] = w > 0.f ? (float)(1 << bits) / w : 0.f;
   }
   const unsigned grid = (unsigned)pm::div_up(nq, 256);
-  k_qbin_count<<<grid, 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, codes, hist);
-  k_qbin_scan<<<kScanTiles, 256, 0, ctx->stream>>>(hist, kQBins, status, tile_counter);
-  k_qbin_scatter<<<grid, 256, 0, ctx->stream>>>(q_dev, codes, nq, hist, perm, sq);
+  k_qbin_count<<<grid, 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, bits, codes, hist);
+  k_qbin_scan<<<tiles, 256, 0, ctx->stream>>>(hist, bins, status, tile_counter);
+  k_qbin_scatter<<<grid, 256, 0, ctx->stream>>>(q_dev, codes, nq, bits, hist, perm, sq);
   ctx->launches += 3;
   PM_CUDA(cudaGetLastError());
   *perm_out = perm;
