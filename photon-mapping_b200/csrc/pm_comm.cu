@@ -256,8 +256,8 @@ int exchange_place(pm_ctx* ctx, const ShardLayout& L, int64_t total_paths, const
   cudaStream_t st = ctx->stream;
   int64_t *goff = nullptr, *roff = nullptr, *tot_dev = nullptr;
   const int64_t table = (int64_t)L.world * L.pcap;
-  PM_CHECK(ctx->get_scratch(pm::S_BUILD5, (size_t)total_paths + 1, &goff));
-  PM_CHECK(ctx->get_scratch(pm::S_BUILD6, (size_t)table + 1, &roff));
+  PM_CHECK(ctx->get_scratch(pm::S_COMM0, (size_t)total_paths + 1, &goff));
+  PM_CHECK(ctx->get_scratch(pm::S_COMM1, (size_t)table + 1, &roff));
   PM_CHECK(ctx->get_scratch(pm::S_MISC0, (size_t)4, &tot_dev));
   GlobalOrderCounts go{L, cnt_all};
   PM_CHECK(scan_i64(ctx, go, total_paths, goff, tot_dev));
@@ -412,8 +412,8 @@ int pm_exchange_photons(pm_ctx* ctx, pm_comm* c, const pm_light* lights, int n_l
   const int64_t my_paths = L.lf[rank][n_lights];
   /* 1. counts: one byte per path, rows padded to pcap */
   uint8_t *cnt_mine = nullptr, *cnt_all = nullptr;
-  PM_CHECK(ctx->get_scratch(pm::S_BUILD7, (size_t)L.pcap, &cnt_mine));
-  PM_CHECK(ctx->get_scratch(pm::S_BUILD8, (size_t)L.pcap * world, &cnt_all));
+  PM_CHECK(ctx->get_scratch(pm::S_COMM2, (size_t)L.pcap, &cnt_mine));
+  PM_CHECK(ctx->get_scratch(pm::S_COMM3, (size_t)L.pcap * world, &cnt_all));
   PM_CUDA(cudaMemsetAsync(cnt_mine, 0, (size_t)L.pcap, st));
   PM_CUDA(cudaMemcpyAsync(cnt_mine, path_counts_dev, (size_t)my_paths, cudaMemcpyDeviceToDevice, st));
   /* 2. shard sizes -> common pitch of the record all-gather */
@@ -434,7 +434,7 @@ int pm_exchange_photons(pm_ctx* ctx, pm_comm* c, const pm_light* lights, int n_l
   if (world > 1) {
     PM_NCCL(nccl()->AllGather(cnt_mine, cnt_all, (size_t)L.pcap, ncclInt8, c->comm, st));
     pm_photon40* stage = nullptr;
-    PM_CHECK(ctx->get_scratch(pm::S_BUILD9, (size_t)cap * world, &stage));
+    PM_CHECK(ctx->get_scratch(pm::S_COMM4, (size_t)cap * world, &stage));
     /* NCCL needs equal contributions: every rank sends `cap` records (the tail of a shorter shard is whatever follows
      * it in the caller's buffer or, if that is shorter than cap, a padded copy) */
     const pm_photon40* send = shard_dev;
@@ -464,7 +464,7 @@ int pm_ppm_update(pm_ctx* ctx, pm_comm* c, int64_t npx, const float* flux_dev, c
   const unsigned grid = (unsigned)pm::div_up(npx, 256);
   if (c && c->world > 1) {
     float* fc = nullptr;
-    PM_CHECK(ctx->get_scratch(pm::S_BUILD10, (size_t)npx * 4, &fc));
+    PM_CHECK(ctx->get_scratch(pm::S_COMM5, (size_t)npx * 4, &fc));
     k_pack_fc<<<grid, 256, 0, st>>>(npx, flux_dev, count_dev, fc);
     PM_CUDA(cudaEventRecord(ctx->ev0, st));
     PM_NCCL(nccl()->AllReduce(fc, fc, (size_t)npx * 4, ncclFloat32, ncclSum, c->comm, st));
@@ -490,8 +490,8 @@ int pm_map_build_sharded(pm_ctx* ctx, pm_comm* c, pm_photon44* photons_dev, int6
   int32_t* elem = nullptr;
   uint8_t* dim = nullptr;
   const size_t dim_words = ((size_t)n + 3) / 4;
-  PM_CHECK(ctx->get_scratch(pm::S_BUILD11, (size_t)n, &elem));
-  PM_CHECK(ctx->get_scratch(pm::S_BUILD12, dim_words * 4, &dim));
+  PM_CHECK(ctx->get_scratch(pm::S_COMM6, (size_t)n, &elem));
+  PM_CHECK(ctx->get_scratch(pm::S_COMM7, dim_words * 4, &dim));
   PM_CUDA(cudaMemsetAsync(dim, 0, dim_words * 4, st));
   float b[6];
   PM_CHECK(pm_map_build_shard(ctx, photons_dev, n, rank, world, elem, dim, b));

@@ -18,6 +18,7 @@ void set_error(const char* fmt, ...);
     cudaError_t e__ = (call);                                                               \
     if (e__ != cudaSuccess) {                                                               \
       pm::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+      cudaGetLastError(); /* reported: do not leave it for an unrelated later check */     \
       return PM_ERR_CUDA;                                                                   \
     }                                                                                       \
   } while (0)
@@ -64,6 +65,7 @@ enum ScratchSlot {
   S_RENDER0, S_RENDER1, S_RENDER2, S_RENDER3, S_RENDER4, S_RENDER5, S_RENDER6, S_RENDER7,
   S_RENDER8, S_RENDER9, S_RENDER10, S_RENDER11,
   S_FAST0, S_FAST1, S_FAST2,
+  S_COMM0, S_COMM1, S_COMM2, S_COMM3, S_COMM4, S_COMM5, S_COMM6, S_COMM7, /* pm_comm.cu: never shared with a build */
   S_COUNT
 };
 
