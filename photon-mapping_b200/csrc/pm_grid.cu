@@ -463,7 +463,7 @@ constexpr int kFastWords = 24;                /* flat index space of one round o
 constexpr int kFastMaxScan = kFastWords * 32; /* retry on a 7- or 9-cell-wide block are up to 9 cells long)            */
 constexpr int kFastPairs = 6;                 /* steps taken two at a time by the unrolled part of the scan (a 5x5x5 block needs ~8) */
 constexpr int kFastMaxH = 4;                  /* widest block of the fast path: 9x9 rows (3 rounds) */
-constexpr int kFastAttempts = 4;
+constexpr int kFastAttempts = 6;
 constexpr int kFastProbes = 12;               /* counting probes per query before it is handed over */
 
 struct __align__(16) FastScratch {
