@@ -496,7 +496,7 @@ __device__ __forceinline__ float sqrt_approx(float x) {
 }
 
 template <bool GATHER>
-__global__ void __launch_bounds__(kWarps * 32, GATHER ? 4 : 6) /* no spills: a reloaded value is no longer warp-uniform to the compiler */
+__global__ void __launch_bounds__(kWarps * 32, GATHER ? 4 : 8) /* no spills: a reloaded value is no longer warp-uniform to the compiler */
 k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::QueryIO io, const __grid_constant__ FastParams fp,
            int* __restrict__ ho_list, int* __restrict__ ho_count) {
   __shared__ FastScratch scratch[kWarps];
@@ -1174,7 +1174,7 @@ int grid_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gath
     fp.Rc2 = rc * rc;
     for (int n = 0; n < kWinSize; n++)
       fp.win[n] = std::pow(((float)io.k + 0.5f) / (float)std::max(n, io.k + 1), 2.f / 3.f);
-    const unsigned fgrid = (unsigned)std::min<int64_t>(div_up(io.nq, kWarps), (int64_t)ctx->sm_count * 6 * 4);
+    const unsigned fgrid = (unsigned)std::min<int64_t>(div_up(io.nq, kWarps), (int64_t)ctx->sm_count * 8 * 4);
     if (gather) k_knn_fast<true><<<fgrid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fp, ho_list, ho_count);
     else k_knn_fast<false><<<fgrid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, io, fp, ho_list, ho_count);
     pmk::QueryIO rest = io;
