@@ -184,17 +184,20 @@ def gpu_baseline_cukd(cloud: np.ndarray, queries: np.ndarray):
     if not os.path.exists(path):
         return None
     ref = ctypes.CDLL(path)
-    d_ref = torch.from_numpy(cloud.view(np.uint8)).cuda()
     d_box = torch.zeros(6, dtype=torch.float32, device="cuda")
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    torch.cuda.synchronize()
-    ev[0].record()
-    rc = ref.ref_build_tree_gpu(ctypes.c_void_p(d_ref.data_ptr()), len(cloud), ctypes.c_void_p(d_box.data_ptr()))
-    ev[1].record()
-    torch.cuda.synchronize()
-    if rc != 0:
-        return {"error": f"ref_build_tree_gpu returned {rc}"}
-    build_ms = ev[0].elapsed_time(ev[1])
+    builds = []
+    for _ in range(2):  # the first call also pays thrust's first allocations: both are reported, the second is compared
+        d_ref = torch.from_numpy(cloud.view(np.uint8)).cuda()
+        torch.cuda.synchronize()
+        ev[0].record()
+        rc = ref.ref_build_tree_gpu(ctypes.c_void_p(d_ref.data_ptr()), len(cloud), ctypes.c_void_p(d_box.data_ptr()))
+        ev[1].record()
+        torch.cuda.synchronize()
+        if rc != 0:
+            return {"error": f"ref_build_tree_gpu returned {rc}"}
+        builds.append(ev[0].elapsed_time(ev[1]))
+    build_ms = min(builds)
     d_q = torch.from_numpy(queries).cuda()
     d_out = torch.zeros((len(queries), K), dtype=torch.int64, device="cuda")
     d_r2 = torch.zeros(len(queries), dtype=torch.float32, device="cuda")
@@ -210,8 +213,8 @@ def gpu_baseline_cukd(cloud: np.ndarray, queries: np.ndarray):
             return {"error": f"ref_knn_gpu returned {rc}"}
         ms.append(ev[0].elapsed_time(ev[1]))
     return {"kind": "oracle/_ref", "what": "cukd::buildTree (thrust builder) + cukd::stackBased::knn<HeapCandidateList<64>>, "
-            "compiled for sm_100a from the reference tree, same B200, same arrays; first (cold) build, best of 3 query runs",
-            "build_ms": build_ms, "knn_ms": min(ms), "q_per_s": len(queries) / (min(ms) * 1e-3),
+            "compiled for sm_100a from the reference tree, same B200, same arrays; best of 2 builds, best of 3 query runs",
+            "build_ms": build_ms, "build_ms_runs": builds, "knn_ms": min(ms), "q_per_s": len(queries) / (min(ms) * 1e-3),
             "r2_checksum": float(d_r2.double().sum().item())}
 
 
@@ -535,7 +538,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                 if gpu_ref and "r2_checksum" in gpu_ref:
                     gpu_ref["r2_checksum_ours"] = float(d_r2.double().sum().item())
                     gpu_ref["speedup_knn_step"] = gpu_ref["knn_ms"] / step_mean
-                    gpu_ref["speedup_build"] = gpu_ref["build_ms"] / build_ms
+                    gpu_ref["speedup_build"] = gpu_ref["build_ms"] / build_ms_warm
             except Exception as e:
                 gpu_ref = {"error": repr(e)}
         build_alg = (88 + 24 * int(np.floor(np.log2(N_PHOTONS)))) * N_PHOTONS  # 640 B/photon at C2

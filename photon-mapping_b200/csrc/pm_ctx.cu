@@ -100,10 +100,12 @@ int pm_ctx_create(int device, pm_ctx** out) {
   c->sm_count = prop.multiProcessorCount;
   PM_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   {
-    /* photon-map buffers come from the stream-ordered pool (pm_internal.h: map_alloc); keep up to 8 GB cached */
+    /* photon-map buffers come from the stream-ordered pool (pm_internal.h: map_alloc); keep up to a third of the
+     * device's memory cached (a 200 M-photon map owns 11 GB: with less, every rebuild pays the page mapping again) */
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-      uint64_t keep = 8ull << 30, cur = 0;
+      uint64_t keep = (uint64_t)prop.totalGlobalMem / 3, cur = 0;
+      if (keep < (8ull << 30)) keep = 8ull << 30;
       cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &cur);
       if (cur < keep) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
     }

@@ -45,7 +45,7 @@ constexpr int kMaxLightsComm = 64, kMaxRanksComm = 16;
 /* Buffers a photon map owns (query-side copies, grid copy) come from the device's stream-ordered pool: a render
  * loop that builds and drops one map per pass (progressive mode: 64 of them) then reuses the same memory without
  * the device-wide synchronisation and the page mapping cost of cudaMalloc / cudaFree. pm_ctx_create lets the pool
- * keep up to 8 GB of freed memory; anything beyond goes back to the driver at the next synchronisation. */
+ * keep up to a third of the device's memory; anything beyond goes back to the driver at the next synchronisation. */
 template <typename T>
 inline cudaError_t map_alloc(T** p, size_t bytes, cudaStream_t st) { return cudaMallocAsync(reinterpret_cast<void**>(p), bytes, st); }
 inline void map_free(void* p) { if (p) cudaFreeAsync(p, (cudaStream_t)0); }

@@ -27,7 +27,7 @@ STEP_KERNELS = ("k_qbin_count", "k_qbin_scan", "k_qbin_scatter", "k_knn_fast", "
 
 
 def short_name(kname: str) -> str:
-    return kname.split("(")[0].replace("void ", "").strip().split("::")[-1].split("<")[0]
+    return kname.split("(")[0].replace("void ", "").strip().split("<")[0].split("::")[-1]
 
 
 if os.path.exists(launches):
@@ -49,7 +49,7 @@ if os.path.exists(launches):
     starts = [i for i, (nm, _) in enumerate(seq) if nm.endswith(STEP_FIRST)]
     groups = [seq[a:b] for a, b in zip(starts, starts[1:])]
     groups = [g for g in groups if not any("k_split" in nm or "k_level" in nm for nm, _ in g)]  # not a map build
-    fast = [g for g in groups if any("k_knn_fast" in nm for nm, _ in g)]  # the C2 steps, not the C1 render's gathers
+    fast = [g for g in groups if any("k_knn_fast<0>" in nm for nm, _ in g)]  # the C2 pm_knn steps, not gathers
     groups = fast or groups
     # (the longest one: bench.py's later end-to-end steps run the same kernels on 131 072-query chunks)
     step = max(groups, key=lambda g: sum(t for _, t in g)) if groups else []
@@ -129,7 +129,7 @@ for rep in reps:
         j["k_walk_source"] = f"profiles/{tag}_k_walk_ncu.txt (last captured launch: the 4 M-path walk of bench.py's stage extras)"
     if "k_level" in per:
         names = [k for k in per if k in ("k_extract", "k_split", "k_level", "k_finish_subtrees", "k_emit_nodes", "k_make_soa", "k_gather44",
-                                         "k_cell_ids", "k_grid_fill") or k.startswith("DeviceRadixSort")]
+                                         "k_cell_ids", "k_grid_fill", "k_cells_transpose", "k_root", "k_sample_queries", "k_kdw") or k.startswith("DeviceRadixSort")]
         j["map_build_10M_dram_bytes_per_launch"] = int(sum(b for k in names for _, b in per[k]))
         j["map_build_10M_kernels"] = {k: [len(per[k]), int(sum(b for _, b in per[k]))] for k in names}
         j["map_build_source"] = f"profiles/{tag}_k_level_ncu.txt ({os.path.basename(rep)}: every kernel of one pm_map_build)"
