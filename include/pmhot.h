@@ -327,6 +327,11 @@ int  pm_map_build_sharded(pm_ctx* ctx, pm_comm* comm, pm_photon44* photons_dev, 
 int  pm_ppm_update(pm_ctx* ctx, pm_comm* comm, int64_t n_points, const float* flux_dev, const int32_t* count_dev,
                    float alpha, float* N_dev, float* r2_dev, float* tau_dev, float* collective_ms);
 
+/* test hook: the gather kernels divide and take square roots with the fast-path instruction sequences of the IEEE
+ * intrinsics (no slow-path call inside the warp-cooperative loops) on operands two predicates accept; this runs n
+ * hashed operand pairs through both and counts accepted operands whose results differ in any bit (must be 0). */
+int  pm_selftest_math(pm_ctx* ctx, int64_t n, uint32_t seed, int64_t* mismatches, int64_t* accepted, int64_t* rejected);
+
 /* ---- photon wire format (≙ writeAlivePhotons / readPhotonsFromFile) ------------------ */
 /* text: 9 floats "pos dir color", std::fixed, 6 decimals (photon-mapping/src/hostCode.cu:31-49) */
 int  pm_photons_write_text(const char* path, const pm_photon40* photons_host, int64_t n);

@@ -117,6 +117,7 @@ _SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
          c_int64, c_int64, c_void_p, c_void_p],
     ),
+    "pm_selftest_math": (c_int, [c_void_p, c_int64, c_uint32, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64)]),
     "pm_photons_write_text": (c_int, [c_char_p, c_void_p, c_int64]),
     "pm_photons_read_text": (c_int, [c_char_p, c_void_p, c_int64, POINTER(c_int64)]),
     "pm_photons_write_bin": (c_int, [c_char_p, c_void_p, c_int64]),

@@ -407,8 +407,10 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
       }
       if (io.r2 && lane == 0) io.r2[qi] = r2;
     } else {
-      /* gatherPhotons (ray-tracer/cuda/shading.h:93-121), summed across the warp */
-      const float rad = __fsqrt_rn(r2);
+      /* gatherPhotons (ray-tracer/cuda/shading.h:93-121), summed across the warp. Division and square root are the
+       * call-free fast paths of pm_knn.cuh; a query with an operand outside their range goes to the kd-tree kernel */
+      bool ok = pmk::sqrt_fast_ok(r2);
+      const float rad = pmk::sqrt_rn_fast(r2);
       float fr = 0.f, fg = 0.f, fb = 0.f;
 #pragma unroll
       for (int s = 0; s <= kSlots; s++) {
@@ -417,8 +419,10 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
         else { a = acc_b; hv = (int)(mine >> 32); id = (uint32_t)mine; }
         if (a) {
           const float4 c = __ldg(color4 + id);
-          const float dist = __fsqrt_rn(__int_as_float(hv));
-          const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
+          const float d2v = __int_as_float(hv);
+          const float dist = pmk::sqrt_rn_fast(d2v);
+          ok = ok && pmk::sqrt_fast_ok(d2v) && pmk::div_fast_ok(dist, rad);
+          const float w = __fsub_rn(1.f, __fmul_rn(pmk::div_rn_fast(dist, rad), 1.1f));
           const float sc = __fmul_rn(__fmul_rn(brdf, c.w), w);
           fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
           fg = __fadd_rn(fg, __fmul_rn(sc, c.y));
@@ -433,10 +437,13 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
       }
       const float k1 = (1 - (2.f / 3.f) * (1.f / 1.1f));
       const float denom = __fmul_rn(__fmul_rn(__fmul_rn(k1, 2.f), 3.14159274101257324f), r2);
-      if (lane == 0) {
-        io.rgb[(size_t)qi * 3 + 0] = __fdiv_rn(fr, denom);
-        io.rgb[(size_t)qi * 3 + 1] = __fdiv_rn(fg, denom);
-        io.rgb[(size_t)qi * 3 + 2] = __fdiv_rn(fb, denom);
+      ok = ok && pmk::div_fast_ok(fr, denom) && pmk::div_fast_ok(fg, denom) && pmk::div_fast_ok(fb, denom);
+      if (!__all_sync(0xffffffffu, ok)) { /* exotic operands: the kd-tree kernel divides with the IEEE intrinsics */
+        if (lane == 0) fb_list[atomicAdd(fb_count, 1)] = qi;
+      } else if (lane == 0) {
+        io.rgb[(size_t)qi * 3 + 0] = pmk::div_rn_fast(fr, denom);
+        io.rgb[(size_t)qi * 3 + 1] = pmk::div_rn_fast(fg, denom);
+        io.rgb[(size_t)qi * 3 + 2] = pmk::div_rn_fast(fb, denom);
       }
     }
     __syncwarp();
@@ -496,7 +503,7 @@ __device__ __forceinline__ float sqrt_approx(float x) {
 }
 
 template <bool GATHER>
-__global__ void __launch_bounds__(kWarps * 32, GATHER ? 4 : 8) /* no spills: a reloaded value is no longer warp-uniform to the compiler */
+__global__ void __launch_bounds__(kWarps * 32, GATHER ? 6 : 8) /* no spills: a reloaded value is no longer warp-uniform to the compiler */
 k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::QueryIO io, const __grid_constant__ FastParams fp,
            int* __restrict__ ho_list, int* __restrict__ ho_count) {
   __shared__ FastScratch scratch[kWarps];
@@ -708,16 +715,20 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
       }
       if (io.r2 && lane == 0) io.r2[qi] = __uint_as_float(tau);
     } else {
-      /* gatherPhotons (ray-tracer/cuda/shading.h:93-121), summed across the warp */
+      /* gatherPhotons (ray-tracer/cuda/shading.h:93-121), summed across the warp; call-free division / square root
+       * (pm_knn.cuh), exotic operands go to the general kernel */
       const float r2 = __uint_as_float(tau);
-      const float rad = __fsqrt_rn(r2);
+      bool ok = pmk::sqrt_fast_ok(r2);
+      const float rad = pmk::sqrt_rn_fast(r2);
       float fr = 0.f, fg = 0.f, fb = 0.f;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
         if (kv[s].x <= tau) {
           const float4 c = __ldg(color4 + kv[s].y);
-          const float dist = __fsqrt_rn(__uint_as_float(kv[s].x));
-          const float w = __fsub_rn(1.f, __fmul_rn(__fdiv_rn(dist, rad), 1.1f));
+          const float d2v = __uint_as_float(kv[s].x);
+          const float dist = pmk::sqrt_rn_fast(d2v);
+          ok = ok && pmk::sqrt_fast_ok(d2v) && pmk::div_fast_ok(dist, rad);
+          const float w = __fsub_rn(1.f, __fmul_rn(pmk::div_rn_fast(dist, rad), 1.1f));
           const float sc = __fmul_rn(__fmul_rn(brdf, c.w), w);
           fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
           fg = __fadd_rn(fg, __fmul_rn(sc, c.y));
@@ -732,10 +743,13 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
       }
       const float k1 = (1 - (2.f / 3.f) * (1.f / 1.1f));
       const float denom = __fmul_rn(__fmul_rn(__fmul_rn(k1, 2.f), 3.14159274101257324f), r2);
-      if (lane == 0) {
-        io.rgb[(size_t)qi * 3 + 0] = __fdiv_rn(fr, denom);
-        io.rgb[(size_t)qi * 3 + 1] = __fdiv_rn(fg, denom);
-        io.rgb[(size_t)qi * 3 + 2] = __fdiv_rn(fb, denom);
+      ok = ok && pmk::div_fast_ok(fr, denom) && pmk::div_fast_ok(fg, denom) && pmk::div_fast_ok(fb, denom);
+      if (!__all_sync(0xffffffffu, ok)) {
+        if (lane == 0) ho_list[atomicAdd(ho_count, 1)] = qi;
+      } else if (lane == 0) {
+        io.rgb[(size_t)qi * 3 + 0] = pmk::div_rn_fast(fr, denom);
+        io.rgb[(size_t)qi * 3 + 1] = pmk::div_rn_fast(fg, denom);
+        io.rgb[(size_t)qi * 3 + 2] = pmk::div_rn_fast(fb, denom);
       }
     }
     __syncwarp();

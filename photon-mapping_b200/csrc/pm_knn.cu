@@ -208,6 +208,39 @@ __global__ void k_fill_f(int64_t total, float* p, float v) {
   if (i < total) p[i] = v;
 }
 
+/* pm_selftest_math: the call-free division / square root of pm_knn.cuh against the IEEE intrinsics on hashed
+ * operands — random bit patterns (every exponent, both signs), and values drawn like the gather's (distances and
+ * radii in [1e-6, 1e3], flux sums of any sign). Counts operands the predicates accept whose results differ. */
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+__global__ void k_selftest_math(int64_t n, uint32_t seed, unsigned long long* __restrict__ out /* mismatches, accepted, rejected */) {
+  unsigned long long bad = 0, acc = 0, rej = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t h0 = mix32((uint32_t)i * 2u + seed), h1 = mix32((uint32_t)i * 2u + 1u + seed * 31u);
+    float a, b;
+    if ((i & 3) == 0) { a = __uint_as_float(h0); b = __uint_as_float(h1); }                 /* any bit pattern */
+    else {
+      /* magnitudes 10^(-6 .. 3), a signed in a quarter of the cases, exact zero now and then */
+      a = exp2f(-20.f + 30.f * (float)(h0 >> 8) * (1.f / 16777216.f));
+      b = exp2f(-20.f + 30.f * (float)(h1 >> 8) * (1.f / 16777216.f));
+      if ((h0 & 3u) == 0u) a = -a;
+      if ((h0 & 0xfcu) == 0u) a = 0.f;
+    }
+    if (pmk::div_fast_ok(a, b)) {
+      acc++;
+      if (__float_as_uint(pmk::div_rn_fast(a, b)) != __float_as_uint(__fdiv_rn(a, b))) bad++;
+    } else rej++;
+    const float x = fabsf(a);
+    if (pmk::sqrt_fast_ok(x)) {
+      acc++;
+      if (__float_as_uint(pmk::sqrt_rn_fast(x)) != __float_as_uint(__fsqrt_rn(x))) bad++;
+    } else rej++;
+  }
+  atomicAdd(out, bad); atomicAdd(out + 1, acc); atomicAdd(out + 2, rej);
+}
+
 /* bounds of a tree-ordered map: ordered-uint atomics, one per block and axis */
 __device__ __forceinline__ uint32_t f2ord(float f) { const uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
 __global__ void k_bounds(const float4* __restrict__ nodes, int n, uint32_t* __restrict__ out /*lo xyz, hi xyz (ordered)*/) {
@@ -356,6 +389,23 @@ int gather_device(pm_ctx* ctx, const pm_map* map, const float* hit_dev, const fl
 }  // namespace pm
 
 extern "C" {
+
+int pm_selftest_math(pm_ctx* ctx, int64_t n, uint32_t seed, int64_t* mismatches, int64_t* accepted, int64_t* rejected) {
+  PM_REQUIRE(ctx && mismatches && n >= 0, "bad arguments");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  unsigned long long* d = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_MISC3, (size_t)4, &d));
+  PM_CUDA(cudaMemsetAsync(d, 0, sizeof(unsigned long long) * 4, ctx->stream));
+  k_selftest_math<<<(unsigned)(ctx->sm_count * 8), 256, 0, ctx->stream>>>(n, seed, d);
+  ctx->launches++;
+  unsigned long long h[3] = {0, 0, 0};
+  PM_CUDA(cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  *mismatches = (int64_t)h[0];
+  if (accepted) *accepted = (int64_t)h[1];
+  if (rejected) *rejected = (int64_t)h[2];
+  return PM_OK;
+}
 
 int pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int k, float cutoff_radius,
            int32_t* out_ids, float* out_dist2, float* out_r2) {
