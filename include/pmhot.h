@@ -131,6 +131,13 @@ int  pm_ctx_sync(pm_ctx* ctx);
  * the context's stream wait for it, without blocking the host. Results need no such step: every pm_* call returns
  * after its work on the context's stream has completed. */
 int  pm_ctx_wait_stream(pm_ctx* ctx, void* other_stream);
+/* device memory for hosts that have no CUDA runtime of their own (the shipped C++ mains link libpmhot only):
+ * zero-filled allocation on the context's device, release, and a copy in any direction (host or device pointers on
+ * either side), synchronous on return. pm_device_count: CUDA devices visible to the process (0 without a driver). */
+int  pm_dev_alloc(pm_ctx* ctx, int64_t bytes, void** out);
+void pm_dev_free(pm_ctx* ctx, void* ptr);
+int  pm_dev_copy(pm_ctx* ctx, void* dst, const void* src, int64_t bytes);
+int  pm_device_count(void);
 /* counters: number of kernels launched by this context since creation / last reset */
 int64_t pm_ctx_launch_count(pm_ctx* ctx);
 void pm_ctx_reset_launch_count(pm_ctx* ctx);
@@ -179,7 +186,8 @@ int  pm_emit_photons_keyed(pm_ctx* ctx, const pm_scene* scene, const pm_light* l
 /* pm_emit_photons into device memory that also writes ONE BYTE PER PATH of this rank (path_counts_dev, in the rank's
  * path order: light by light, launch indices first_photon, first_photon + photon_stride, ...): how many photons the
  * path stored. That table is all pm_exchange_photons needs to merge the shards of several ranks without keys or a sort. */
-int  pm_emit_photons_counted(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host, int n_lights,
+int  pm_emit_photons_counted(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights_host,
+                             const pm_light_shape* shapes_host /* NULL: point lights */, int n_lights,
                              int64_t casted, int max_depth, int caustics_mode,
                              uint64_t seed, int rng_mode, int64_t first_photon, int64_t photon_stride,
                              pm_photon40* out_dev, uint8_t* path_counts_dev, int64_t capacity, int64_t* count,

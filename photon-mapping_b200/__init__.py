@@ -76,9 +76,13 @@ _SIGNATURES = {
     ),
     "pm_emit_photons_counted": (
         c_int,
-        [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_uint64, c_int, c_int64, c_int64, c_void_p,
          c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64)],
     ),
+    "pm_dev_alloc": (c_int, [c_void_p, c_int64, POINTER(c_void_p)]),
+    "pm_dev_free": (None, [c_void_p, c_void_p]),
+    "pm_dev_copy": (c_int, [c_void_p, c_void_p, c_void_p, c_int64]),
+    "pm_device_count": (c_int, []),
     "pm_comm_unique_id": (c_int, [c_void_p, c_int]),
     "pm_comm_create": (c_int, [c_void_p, c_void_p, c_int, c_int, POINTER(c_void_p)]),
     "pm_comm_destroy": (None, [c_void_p]),

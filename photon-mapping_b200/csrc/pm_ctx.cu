@@ -154,6 +154,44 @@ int pm_ctx_wait_stream(pm_ctx* ctx, void* other_stream) {
   return PM_OK;
 }
 
+int pm_dev_alloc(pm_ctx* ctx, int64_t bytes, void** out) {
+  if (!ctx || !out || bytes < 0) { pm::set_error("pm_dev_alloc: bad arguments"); return PM_ERR_INVALID; }
+  *out = nullptr;
+  if (bytes == 0) return PM_OK;
+  PM_CUDA(cudaSetDevice(ctx->device));
+  if (cudaMalloc(out, (size_t)bytes) != cudaSuccess) {
+    cudaGetLastError();
+    *out = nullptr;
+    pm::set_error("pm_dev_alloc: out of device memory allocating %lld bytes", (long long)bytes);
+    return PM_ERR_NOMEM;
+  }
+  PM_CUDA(cudaMemsetAsync(*out, 0, (size_t)bytes, ctx->stream));
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PM_OK;
+}
+
+void pm_dev_free(pm_ctx* ctx, void* ptr) {
+  if (!ctx || !ptr) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  cudaFree(ptr);
+}
+
+int pm_dev_copy(pm_ctx* ctx, void* dst, const void* src, int64_t bytes) {
+  if (!ctx || bytes < 0 || (bytes > 0 && (!dst || !src))) { pm::set_error("pm_dev_copy: bad arguments"); return PM_ERR_INVALID; }
+  if (bytes == 0) return PM_OK;
+  PM_CUDA(cudaSetDevice(ctx->device));
+  PM_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, ctx->stream));
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PM_OK;
+}
+
+int pm_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
 int64_t pm_ctx_launch_count(pm_ctx* ctx) { return ctx ? ctx->launches : 0; }
 void pm_ctx_reset_launch_count(pm_ctx* ctx) { if (ctx) ctx->launches = 0; }
 float pm_ctx_last_kernel_ms(pm_ctx* ctx) { return ctx ? ctx->last_kernel_ms : 0.f; }

@@ -379,13 +379,13 @@ int pm_emit_photons_keyed(pm_ctx* ctx, const pm_scene* scene, const pm_light* li
                    photon_stride, out, out_keys, capacity, count, n_paths, n_segments);
 }
 
-int pm_emit_photons_counted(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, int n_lights, int64_t casted,
-                            int max_depth, int caustics_mode, uint64_t seed, int rng_mode, int64_t first_photon,
-                            int64_t photon_stride, pm_photon40* out_dev, uint8_t* path_counts_dev, int64_t capacity,
-                            int64_t* count, int64_t* n_paths, int64_t* n_segments) {
+int pm_emit_photons_counted(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, const pm_light_shape* shapes,
+                            int n_lights, int64_t casted, int max_depth, int caustics_mode, uint64_t seed, int rng_mode,
+                            int64_t first_photon, int64_t photon_stride, pm_photon40* out_dev, uint8_t* path_counts_dev,
+                            int64_t capacity, int64_t* count, int64_t* n_paths, int64_t* n_segments) {
   PM_REQUIRE(path_counts_dev, "path_counts is NULL");
   PM_REQUIRE(capacity == 0 || pm::is_device_ptr(out_dev), "out must be device memory");
-  return emit_impl(ctx, scene, lights, nullptr, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
+  return emit_impl(ctx, scene, lights, shapes, n_lights, casted, max_depth, caustics_mode, seed, rng_mode, first_photon,
                    photon_stride, out_dev, nullptr, capacity, count, n_paths, n_segments, path_counts_dev);
 }
 

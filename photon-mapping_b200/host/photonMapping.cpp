@@ -2,8 +2,10 @@
 // Same inputs (config.toml keys [data] / [photon-mapper], the glb scene, lights.txt, <model>.mtl) and the
 // same outputs (two photon text files); the device work goes through libpmhot's C ABI instead of OWL.
 //
-//   photonMapping [config.toml] [--dump-scene] [--counter-rng SEED]
+//   photonMapping [config.toml] [--dump-scene] [--counter-rng SEED] [--rank R --world G --comm-file PATH [--device D]]
 // Without arguments the config is read from ../config.toml like the reference (common/src/configLoader.h:6).
+// With --world G (one process per GPU, pm_ranks.hpp) rank R traces launch indices R, R + G, ... of every light, the
+// shards meet in ONE exchange (pm_exchange_photons over NCCL) and rank 0 writes the same files a single process writes.
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -11,6 +13,7 @@
 
 #include "pm_assets.hpp"
 #include "pm_config.hpp"
+#include "pm_ranks.hpp"
 
 #define LOG(message) std::cout << "\033[1;37m#pm.host: " << message << "\033[0m" << std::endl
 #define LOG_OK(message) std::cout << "\033[1;32m#pm.host: " << message << "\033[0m" << std::endl
@@ -25,7 +28,9 @@ int main(int argc, char** argv) {
     bool dump = false;
     int rng_mode = PM_RNG_LCG_PARITY;
     uint64_t seed = 0;
+    pmh::Ranks ranks;
     for (int i = 1; i < argc; i++) {
+      if (ranks.parse(argc, argv, i)) continue;
       if (!strcmp(argv[i], "--dump-scene")) dump = true;
       else if (!strcmp(argv[i], "--counter-rng") && i + 1 < argc) { rng_mode = PM_RNG_COUNTER; seed = strtoull(argv[++i], nullptr, 10); }
       else config_path = argv[i];
@@ -60,7 +65,8 @@ int main(int argc, char** argv) {
 
     pm_ctx* ctx = nullptr;
     pm_scene* scene = nullptr;
-    check(pm_ctx_create(0, &ctx));
+    check(pm_ctx_create(ranks.pick_device(), &ctx));
+    ranks.connect(ctx);
     check(pm_scene_create(ctx, world.verts.data(), (int)(world.verts.size() / 3), world.tris.data(), (int)(world.tris.size() / 3),
                           world.tri_mesh.data(), world.mats.data(), (int)world.mats.size(), &scene));
     LOG_OK("Geometry uploaded, LBVH built");
@@ -69,19 +75,51 @@ int main(int argc, char** argv) {
     struct Pass { const char* what; long long casted; int caustics; const std::string* file; };
     const Pass passes[2] = {{"global", casted_diffuse, 0, &photons_filename}, {"caustic", casted_caustics, 1, &caustics_photons_filename}};
     for (const Pass& p : passes) {
-      std::vector<pm_photon40> photons((size_t)std::max<long long>(p.casted, 0) * (size_t)std::max(max_depth, 1));
+      const int64_t capacity = (int64_t)std::max<long long>(p.casted, 0) * (int64_t)std::max(max_depth, 1);
+      std::vector<pm_photon40> photons;
       int64_t count = 0, paths = 0, segments = 0;
       const auto t0 = std::chrono::steady_clock::now();
-      check(pm_emit_photons_shaped(ctx, scene, world.light_sources.data(), world.light_shapes.data(), (int)world.light_sources.size(),
-                                   p.casted, max_depth, p.caustics, seed, rng_mode, 0, 1, photons.data(), nullptr,
-                                   (int64_t)photons.size(), &count, &paths, &segments));
+      if (ranks.world == 1) {
+        photons.resize((size_t)capacity);
+        check(pm_emit_photons_shaped(ctx, scene, world.light_sources.data(), world.light_shapes.data(), (int)world.light_sources.size(),
+                                     p.casted, max_depth, p.caustics, seed, rng_mode, 0, 1, photons.data(), nullptr, capacity, &count,
+                                     &paths, &segments));
+      } else {
+        // this rank's launch indices -> device shard + one count byte per path -> the exchange -> all photons, in the
+        // single-process order, as 44-byte records on every rank; rank 0 turns them back into the file's 40-byte records
+        const int64_t cap_local = capacity / ranks.world + (int64_t)max_depth * ((int64_t)world.light_sources.size() + 1);
+        const int64_t paths_max = p.casted / ranks.world + (int64_t)world.light_sources.size() + 16;
+        pmh::DevBuf shard(ctx, cap_local * (int64_t)sizeof(pm_photon40)), counts(ctx, paths_max), all(ctx, capacity * (int64_t)sizeof(pm_photon44));
+        int64_t stored = 0;
+        check(pm_emit_photons_counted(ctx, scene, world.light_sources.data(), world.light_shapes.data(), (int)world.light_sources.size(),
+                                      p.casted, max_depth, p.caustics, seed, rng_mode, ranks.rank, ranks.world, shard.as<pm_photon40>(),
+                                      counts.as<uint8_t>(), cap_local, &stored, &paths, &segments));
+        float coll_ms = 0.f;
+        check(pm_exchange_photons(ctx, ranks.comm, world.light_sources.data(), (int)world.light_sources.size(), p.casted,
+                                  shard.as<pm_photon40>(), stored, counts.as<uint8_t>(), 1.0f, all.as<pm_photon44>(), capacity, &count,
+                                  &coll_ms));
+        if (ranks.rank == 0) {
+          std::vector<pm_photon44> rec((size_t)count);
+          check(pm_dev_copy(ctx, rec.data(), all.p, count * (int64_t)sizeof(pm_photon44)));
+          photons.resize((size_t)count);
+          for (int64_t i = 0; i < count; i++) {
+            pm_photon40& q = photons[(size_t)i];
+            memcpy(q.pos, rec[(size_t)i].pos, 12); memcpy(q.dir, rec[(size_t)i].dir, 12); memcpy(q.color, rec[(size_t)i].color, 12);
+            q.power = 0;
+          }
+        }
+      }
       const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-      LOG_OK(p.what << " pass: " << paths << " paths, " << segments << " segments, " << count << " photons stored in " << ms
+      LOG_OK(p.what << " pass" << (ranks.world > 1 ? " (rank " + std::to_string(ranks.rank) + " of " + std::to_string(ranks.world) + ")" : std::string())
+                    << ": " << paths << " paths, " << segments << " segments, " << count << " photons stored in " << ms
                     << " ms (device " << pm_ctx_last_kernel_ms(ctx) << " ms)");
-      const bool bin = p.file->size() > 4 && p.file->compare(p.file->size() - 4, 4, ".bin") == 0;  // lossless hand-off
-      check(bin ? pm_photons_write_bin(p.file->c_str(), photons.data(), count) : pm_photons_write_text(p.file->c_str(), photons.data(), count));
-      LOG_OK("Wrote " << *p.file);
+      if (ranks.rank == 0) {
+        const bool bin = p.file->size() > 4 && p.file->compare(p.file->size() - 4, 4, ".bin") == 0;  // lossless hand-off
+        check(bin ? pm_photons_write_bin(p.file->c_str(), photons.data(), count) : pm_photons_write_text(p.file->c_str(), photons.data(), count));
+        LOG_OK("Wrote " << *p.file);
+      }
     }
+    ranks.close();
     pm_scene_destroy(scene);
     pm_ctx_destroy(ctx);
     return 0;

@@ -3,17 +3,22 @@
 // files written by photonMapping; builds the two photon maps (≙ cukd::buildTree ×2, hostCode.cu:93-98),
 // renders through libpmhot (≙ owlRayGenLaunch2D, :231-237) and writes the PNG (:239-240).
 //
-//   rayTracer [config.toml]
+//   rayTracer [config.toml] [--rank R --world G --comm-file PATH [--device D]]
+// With --world G (one process per GPU, pm_ranks.hpp) every rank reads the photon files, the global map is built with
+// pm_map_build_sharded (same tree, levels below log2(G) split over the ranks), rank R renders pixels
+// [R*W*H/G, (R+1)*W*H/G) and the disjoint ranges meet in one all-reduce; rank 0 writes the PNG.
 #include <chrono>
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <iostream>
+#include <memory>
 
 #include "pm_assets.hpp"
 #include "pm_config.hpp"
 #include "pm_png.hpp"
+#include "pm_ranks.hpp"
 
 #define LOG(message) std::cout << "\033[1;37m#pm.host: " << message << "\033[0m" << std::endl
 #define LOG_OK(message) std::cout << "\033[1;32m#pm.host: " << message << "\033[0m" << std::endl
@@ -74,7 +79,12 @@ static std::vector<pm_photon40> read_photons(const std::string& path) {
 
 int main(int argc, char** argv) {
   try {
-    const std::string config_path = argc > 1 ? argv[1] : "../config.toml";
+    std::string config_path = "../config.toml";
+    pmh::Ranks ranks;
+    for (int i = 1; i < argc; i++) {
+      if (ranks.parse(argc, argv, i)) continue;
+      config_path = argv[i];
+    }
     LOG("Loading Config file...");
     const pmh::Config cfg = pmh::Config::load(config_path);
     const std::string global_file = cfg.str("data", "photons_file");
@@ -93,7 +103,8 @@ int main(int argc, char** argv) {
     pmh::World world = pmh::import_scene(model_path);
     pm_ctx* ctx = nullptr;
     pm_scene* scene = nullptr;
-    check(pm_ctx_create(0, &ctx));
+    check(pm_ctx_create(ranks.pick_device(), &ctx));
+    ranks.connect(ctx);
     check(pm_scene_create(ctx, world.verts.data(), (int)(world.verts.size() / 3), world.tris.data(), (int)(world.tris.size() / 3),
                           world.tri_mesh.data(), world.mats.data(), (int)world.mats.size(), &scene));
 
@@ -104,9 +115,16 @@ int main(int argc, char** argv) {
     check(pm_photons_to_maps(ctx, g40.data(), (int64_t)g40.size(), c40.data(), (int64_t)c40.size(), g44.data(), c44.data()));
     pm_map *gmap = nullptr, *cmap = nullptr;
     float gb[6], cb[6];
+    std::unique_ptr<pmh::DevBuf> g_dev, fb_dev;
     const auto t0 = std::chrono::steady_clock::now();
-    check(pm_map_build(ctx, g44.data(), (int64_t)g44.size(), gb, &gmap));
-    check(pm_map_build(ctx, c44.data(), (int64_t)c44.size(), cb, &cmap));
+    if (ranks.world == 1 || g44.empty()) {
+      check(pm_map_build(ctx, g44.data(), (int64_t)g44.size(), gb, &gmap));
+    } else {
+      g_dev.reset(new pmh::DevBuf(ctx, (int64_t)(g44.size() * sizeof(pm_photon44))));
+      check(pm_dev_copy(ctx, g_dev->p, g44.data(), (int64_t)(g44.size() * sizeof(pm_photon44))));
+      check(pm_map_build_sharded(ctx, ranks.comm, g_dev->as<pm_photon44>(), (int64_t)g44.size(), gb, &gmap));
+    }
+    check(pm_map_build(ctx, c44.data(), (int64_t)c44.size(), cb, &cmap));  // the caustic map is small: built whole
     const auto t1 = std::chrono::steady_clock::now();
     printf("Photon maps built in %.3f ms\n", std::chrono::duration<double, std::milli>(t1 - t0).count());
 
@@ -116,13 +134,26 @@ int main(int argc, char** argv) {
     std::vector<uint32_t> fb((size_t)W * H, 0u);
     LOG("Launching...");
     const auto t2 = std::chrono::steady_clock::now();
-    check(pm_render(ctx, scene, world.light_sources.data(), (int)world.light_sources.size(), gmap, cmap, &cam, W, H, spp, depth, sky3,
-                    0, (int64_t)W * H, fb.data()));
+    const int64_t npx = (int64_t)W * H;
+    if (ranks.world == 1) {
+      check(pm_render(ctx, scene, world.light_sources.data(), (int)world.light_sources.size(), gmap, cmap, &cam, W, H, spp, depth, sky3,
+                      0, npx, fb.data()));
+    } else {
+      fb_dev.reset(new pmh::DevBuf(ctx, npx * (int64_t)sizeof(uint32_t)));  // zero-filled
+      const int64_t b = ranks.rank * npx / ranks.world, e = (ranks.rank + 1) * npx / ranks.world;
+      check(pm_render(ctx, scene, world.light_sources.data(), (int)world.light_sources.size(), gmap, cmap, &cam, W, H, spp, depth, sky3,
+                      b, e, fb_dev->as<uint32_t>()));
+      check(pm_comm_allreduce_sum(ctx, ranks.comm, fb_dev->p, npx, PM_DTYPE_I32));  // disjoint ranges: the sum is a merge
+      check(pm_dev_copy(ctx, fb.data(), fb_dev->p, npx * (int64_t)sizeof(uint32_t)));
+    }
     const auto t3 = std::chrono::steady_clock::now();
     printf("Rendered in %.3f ms (gather kernels %.3f ms)\n", std::chrono::duration<double, std::milli>(t3 - t2).count(),
            pm_ctx_last_kernel_ms(ctx));
-    if (!pmh::write_png_rgba8(output, fb.data(), W, H)) throw std::runtime_error("cannot write " + output);
-    LOG_OK("Written rendered frame buffer to file " << output);
+    if (ranks.rank == 0) {
+      if (!pmh::write_png_rgba8(output, fb.data(), W, H)) throw std::runtime_error("cannot write " + output);
+      LOG_OK("Written rendered frame buffer to file " << output);
+    }
+    ranks.close();
     pm_map_destroy(gmap);
     pm_map_destroy(cmap);
     pm_scene_destroy(scene);

@@ -89,7 +89,7 @@ def run_c4(pkg, ctx, comm, rank, world, casted_total=64_000_000, W=1920, H=1080,
         cnt, npaths, nseg, total, coll_ms = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_float(0)
 
         def emit():
-            pkg._check(L.pm_emit_photons_counted(ctx.handle, scene.handle, lights.ctypes.data, len(lights), casted_total, depth, 0, 1,
+            pkg._check(L.pm_emit_photons_counted(ctx.handle, scene.handle, lights.ctypes.data, None, len(lights), casted_total, depth, 0, 1,
                                                  pkg.RNG_COUNTER, rank, world, shard.data_ptr(), pcnt.data_ptr(), cap_local,
                                                  ctypes.byref(cnt), ctypes.byref(npaths), ctypes.byref(nseg)))
 

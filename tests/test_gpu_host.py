@@ -61,3 +61,39 @@ def test_two_pass_workflow_matches_python_host(pkg, ctx, tmp_path):
         want = scene.view_photons(photons, (80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87, W, H)
         assert np.array_equal(read_png_rgba8(path), want)
     assert (read_png_rgba8(png + ".viewer.png") != 0xFF000000).sum() > 500
+
+
+def test_two_rank_hosts_write_the_single_process_files(tmp_path):
+    """Multi-process mode of the C++ hosts (pm_ranks.hpp): two ranks on two GPUs — sharded emission, the sort-free
+    NCCL exchange, the sharded map build, pixel ranges merged by one all-reduce — produce byte-identical photon files
+    and the identical PNG of the single-process run. Needs two GPUs (skipped on the driver's one-GPU test box;
+    run with `gpurun --gpus 2`, record in profiles/)."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    sc0 = load_scene("cornell_box")
+    glb = write_scene_files(str(tmp_path), sc0, "box")
+    W, H = 160, 96
+    out = {}
+    for tag, world in (("one", 1), ("two", 2)):
+        d = tmp_path / tag
+        d.mkdir()
+        cfg = str(d / "config.toml")
+        gfile, cfile, png = str(d / "global.bin"), str(d / "caustic.txt"), str(d / "result.png")
+        write_config(cfg, glb, gfile, cfile, png, W=W, H=H, spp=1, depth=1, max_depth=6, casted=(60001, 20000))
+        for exe in ("photonMapping", "rayTracer"):
+            procs = []
+            for r in range(world):
+                cmd = [os.path.join(HOST_DIR, exe), cfg]
+                if world > 1:
+                    cmd += ["--rank", str(r), "--world", str(world), "--comm-file", str(d / f"{exe}.id"), "--device", str(r)]
+                procs.append(subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+            for p in procs:
+                o, _ = p.communicate(timeout=300)
+                assert p.returncode == 0, o
+        out[tag] = (open(gfile, "rb").read(), open(cfile, "rb").read(), read_png_rgba8(png))
+    assert len(out["one"][0]) > 1_000_000
+    assert out["one"][0] == out["two"][0]  # binary global photon file
+    assert out["one"][1] == out["two"][1]  # text caustic photon file
+    assert np.array_equal(out["one"][2], out["two"][2]) and (out["one"][2][1:] != 0).any()

@@ -100,7 +100,7 @@ def test_sortfree_exchange_places_shards_in_single_gpu_order(pkg, ctx, world, ca
     total_local = 0
     for r in range(world):
         cnt, npaths, nseg = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int64(0)
-        pkg._check(L.pm_emit_photons_counted(ctx.handle, scene.handle, lights.ctypes.data, len(lights), casted, depth,
+        pkg._check(L.pm_emit_photons_counted(ctx.handle, scene.handle, lights.ctypes.data, None, len(lights), casted, depth,
                                              1 if caustics else 0, 3, pkg.RNG_COUNTER, r, world, shards[r].data_ptr(),
                                              counts_all[r].data_ptr(), cap_r, ctypes.byref(cnt), ctypes.byref(npaths),
                                              ctypes.byref(nseg)))
