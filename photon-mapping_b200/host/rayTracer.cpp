@@ -156,6 +156,8 @@ int main(int argc, char** argv) {
     ranks.close();
     pm_map_destroy(gmap);
     pm_map_destroy(cmap);
+    fb_dev.reset();  // device buffers go before their context
+    g_dev.reset();
     pm_scene_destroy(scene);
     pm_ctx_destroy(ctx);
     return 0;
