@@ -150,202 +150,6 @@ k_walk(const EmitParams P, unsigned long long* __restrict__ next_path, pm_photon
   if (lane == 0 && my_segments) atomicAdd(segments, my_segments);
 }
 
-/* ---- k_walk_q: the same walk as a per-warp wavefront ------------------------------------------------
- * k_walk keeps one path per lane: a lane whose ray has finished waits until enough others have, then the warp runs
- * the closest-hit / scatter code for the few finished lanes and refills them — ncu: 12 of 32 lanes active per
- * instruction, the shading maths (a third of all instructions) at 12.6. Here every warp owns kWalkSlots path
- * records in shared memory and three rings of slot numbers (ready to trace, traced, free):
- *   - a lane whose ray has finished writes the hit into its path's slot, appends the slot to the "traced" ring and
- *     takes the next ready ray at once — the traversal loop runs with (almost) all lanes;
- *   - closest-hit, roulette, scatter and the photon store run only when 32 traced paths have queued up: 32 lanes;
- *   - emission fills free slots 32 paths at a time: 32 lanes.
- * Ring positions are handed out by ballots (the warp is the only user of its rings: no atomics). Every path keeps
- * its own RNG state and its own slot range in the output buffer, so the stored photons and their order are those of
- * k_walk (and of the oracle), whatever the order of processing. */
-constexpr int kWalkSlots = 128;            /* paths in flight per warp; ring capacity (power of two) */
-constexpr int kWalkWarps = 4;
-
-struct __align__(16) WalkWarp {
-  float org[3][kWalkSlots], dir[3][kWalkSlots], col[3][kWalkSlots];
-  uint32_t rng[3][kWalkSlots];             /* LCG state | counter key lo, key hi, counter */
-  int local[kWalkSlots];                   /* path index inside the batch */
-  int hit_slot[kWalkSlots];                /* triangle slot the finished segment hit, -1: miss */
-  float hit_t[kWalkSlots];
-  uint8_t depth[kWalkSlots], stored[kWalkSlots];
-  uint8_t ready[kWalkSlots], traced[kWalkSlots], freeq[kWalkSlots];
-};
-
-__global__ void __launch_bounds__(kWalkWarps * 32)
-k_walk_q(const EmitParams P, unsigned long long* __restrict__ next_path, pm_photon40* __restrict__ slots,
-         int* __restrict__ counts, unsigned long long* __restrict__ segments) {
-  __shared__ WalkWarp sw[kWalkWarps];
-  constexpr int kMask = kWalkSlots - 1;
-  const unsigned lane = threadIdx.x & 31u;
-  const unsigned ltm = (1u << lane) - 1u;
-  WalkWarp& w = sw[__shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0)];
-  for (int s = lane; s < kWalkSlots; s += 32) w.freeq[s] = (uint8_t)s;
-  int rq_h = 0, rq_n = 0, hq_h = 0, hq_n = 0, fq_h = 0, fq_n = kWalkSlots; /* warp-uniform ring heads and fills */
-  bool exhausted = false;                                                  /* no path ids left in this batch */
-  bool has_ray = false;
-  int myslot = 0;
-  vec3 org = v3(0, 0, 0), dir = v3(0, 0, 1);
-  TraceState st;
-  st.node = kNoChild; st.sp = 0;
-  unsigned long long my_segments = 0;
-  __syncwarp();
-  while (true) {
-    const unsigned idle = __ballot_sync(0xffffffffu, !has_ray);
-    const int n_idle = __popc(idle);
-    /* produce ready rays until the idle lanes can be filled (or nothing can be produced) */
-    while (rq_n < n_idle) {
-      /* full batches first: 32 traced paths to shade, else 32 free slots to fill; partial ones only when stuck */
-      const bool can_emit = !exhausted && fq_n > 0;
-      const bool full_emit = !exhausted && fq_n >= 32;
-      if (hq_n >= 32 || (hq_n > 0 && !full_emit)) {
-        /* ---- closest hit + scatter for up to 32 traced paths (deviceCode.cu:74-136, 25-52) ---- */
-        const int cnt = min(hq_n, 32);
-        bool cont = false, end = false;
-        int slot = 0;
-        if ((int)lane < cnt) {
-          slot = w.traced[(hq_h + lane) & kMask];
-          const vec3 o = v3(w.org[0][slot], w.org[1][slot], w.org[2][slot]);
-          const vec3 d = v3(w.dir[0][slot], w.dir[1][slot], w.dir[2][slot]);
-          const vec3 color = v3(w.col[0][slot], w.col[1][slot], w.col[2][slot]);
-          Rng rng;
-          rng.mode = P.rng_mode; rng.lcg.state = w.rng[0][slot];
-          rng.cr.key = (uint64_t)w.rng[0][slot] | ((uint64_t)w.rng[1][slot] << 32); rng.cr.ctr = w.rng[2][slot];
-          int depth = w.depth[slot], stored = w.stored[slot];
-          const int local = w.local[slot];
-          const int hslot = w.hit_slot[slot];
-          int ev = EV_MISS;
-          vec3 s_org = o, s_dir = d, s_col = color;
-          if (hslot >= 0) {
-            const pm_material m = P.sc.mats[slot_mesh(P.sc, hslot)];
-            const float diffuseProb = m.diffuse;
-            const float specularProb = m.specular + diffuseProb;
-            const float transmissionProb = m.transmission + specularProb;
-            const float r = rng.next();
-            if (r < diffuseProb) ev = EV_DIFFUSE;
-            else if (r < specularProb) ev = EV_SPECULAR;
-            else if (r < transmissionProb) ev = EV_REFRACT;
-            else ev = EV_ABSORBED;
-            if (ev != EV_ABSORBED) {
-              s_org = o + w.hit_t[slot] * d;
-              const vec3 n = slot_normal(P.sc, hslot);
-              if (ev == EV_DIFFUSE) s_dir = cosineSampleHemisphere(n, rng);
-              else if (ev == EV_SPECULAR) s_dir = reflect(d, n);
-              else s_dir = refract3(d, n, m.refraction_idx);
-              s_col = v3(m.albedo) * color;
-            }
-          }
-          if (ev == EV_DIFFUSE && depth > 0) {
-            store40(slots + (size_t)local * P.slots_per_path + stored, s_org, s_dir, color);
-            stored++;
-          }
-          cont = P.caustics ? ((ev & (EV_SPECULAR | EV_REFRACT)) != 0) : (ev == EV_DIFFUSE);
-          depth++;
-          if (!cont || depth >= P.max_depth) {
-            counts[local] = stored;
-            cont = false; end = true;
-          } else {
-            w.org[0][slot] = s_org.x; w.org[1][slot] = s_org.y; w.org[2][slot] = s_org.z;
-            w.dir[0][slot] = s_dir.x; w.dir[1][slot] = s_dir.y; w.dir[2][slot] = s_dir.z;
-            w.col[0][slot] = s_col.x; w.col[1][slot] = s_col.y; w.col[2][slot] = s_col.z;
-            if (P.rng_mode == PM_RNG_LCG_PARITY) w.rng[0][slot] = rng.lcg.state;
-            else w.rng[2][slot] = rng.cr.ctr;
-            w.depth[slot] = (uint8_t)depth; w.stored[slot] = (uint8_t)stored;
-          }
-        }
-        const unsigned cb = __ballot_sync(0xffffffffu, cont), eb = __ballot_sync(0xffffffffu, end);
-        if (cont) w.ready[(rq_h + rq_n + __popc(cb & ltm)) & kMask] = (uint8_t)slot;
-        if (end) w.freeq[(fq_h + fq_n + __popc(eb & ltm)) & kMask] = (uint8_t)slot;
-        rq_n += __popc(cb); fq_n += __popc(eb);
-        hq_h += cnt; hq_n -= cnt;
-        __syncwarp();
-      } else if (can_emit) {
-        /* ---- pointLightRayGen for up to 32 new paths (deviceCode.cu:54-72) ---- */
-        const int cnt = min(fq_n, 32);
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(next_path, (unsigned long long)cnt);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        const int64_t mine = (int64_t)base + lane;
-        const bool valid = (int)lane < cnt && mine < P.batch_count;
-        if ((int64_t)base + cnt >= P.batch_count) exhausted = true;
-        const unsigned vb = __ballot_sync(0xffffffffu, valid);
-        bool go = false;
-        int slot = 0;
-        if (valid) {
-          slot = w.freeq[(fq_h + __popc(vb & ltm)) & kMask];
-          const int64_t g = P.batch_begin + mine;
-          int l = 0;
-          while (l + 1 < P.n_lights && g >= P.light_first[l + 1]) l++;
-          const int64_t idx = P.first_photon + (g - P.light_first[l]) * P.photon_stride;
-          Rng rng;
-          rng.lcg.state = 0; rng.cr.key = 0; rng.cr.ctr = 0;
-          if (P.rng_mode == PM_RNG_LCG_PARITY) rng.init_lcg((uint32_t)idx, 0u); /* deviceCode.cu:59 */
-          else rng.init_counter(P.seed, ((uint64_t)((P.caustics ? P.n_lights : 0) + l) << 32) | (uint64_t)idx);
-          vec3 o = v3(P.light_pos[l]), d;
-          if (P.light_shape[l][3] > 0.f) sampleSquareLight(o, v3(P.light_shape[l]), P.light_shape[l][3], rng, &o, &d);
-          else d = randomPointInUnitSphere(rng); /* deviceCode.cu:64 */
-          w.local[slot] = (int)mine;
-          if (P.max_depth > 0) {
-            go = true;
-            w.org[0][slot] = o.x; w.org[1][slot] = o.y; w.org[2][slot] = o.z;
-            w.dir[0][slot] = d.x; w.dir[1][slot] = d.y; w.dir[2][slot] = d.z;
-            w.col[0][slot] = P.light_rgb[l][0]; w.col[1][slot] = P.light_rgb[l][1]; w.col[2][slot] = P.light_rgb[l][2];
-            if (P.rng_mode == PM_RNG_LCG_PARITY) w.rng[0][slot] = rng.lcg.state;
-            else { w.rng[0][slot] = (uint32_t)rng.cr.key; w.rng[1][slot] = (uint32_t)(rng.cr.key >> 32); w.rng[2][slot] = rng.cr.ctr; }
-            w.depth[slot] = 0; w.stored[slot] = 0;
-          } else {
-            counts[mine] = 0;
-          }
-        }
-        const unsigned gb = __ballot_sync(0xffffffffu, go);
-        if (go) w.ready[(rq_h + rq_n + __popc(gb & ltm)) & kMask] = (uint8_t)slot;
-        /* slots of paths that do not start (max_depth 0) go straight back to the free ring */
-        const unsigned nb = vb & ~gb;
-        const int nv = __popc(vb);
-        if (valid && !go) w.freeq[(fq_h + fq_n + __popc(nb & ltm)) & kMask] = (uint8_t)slot;
-        fq_h += nv; fq_n += __popc(nb) - nv;
-        rq_n += __popc(gb);
-        __syncwarp();
-      } else {
-        break;
-      }
-    }
-    /* idle lanes take the next ready rays */
-    if (rq_n > 0 && n_idle > 0) {
-      const int take = min(rq_n, n_idle);
-      const int r = __popc(idle & ltm);
-      if (!has_ray && r < take) {
-        myslot = w.ready[(rq_h + r) & kMask];
-        org = v3(w.org[0][myslot], w.org[1][myslot], w.org[2][myslot]);
-        dir = v3(w.dir[0][myslot], w.dir[1][myslot], w.dir[2][myslot]);
-        trace_begin(P.sc, st, dir, 1e30f);
-        has_ray = true;
-        my_segments++;
-      }
-      rq_h += take; rq_n -= take;
-    }
-    if (!__any_sync(0xffffffffu, has_ray)) break; /* nothing in flight and nothing left to produce */
-    /* traversal of the segments in flight; the warp leaves when fewer than min_lanes are still inside */
-    if (has_ray) trace_advance<false>(P.sc, st, org, dir, PMD_EPS, 1e30f, P.min_lanes);
-    const bool done = has_ray && st.node == kNoChild;
-    const unsigned db = __ballot_sync(0xffffffffu, done);
-    if (done) {
-      w.hit_slot[myslot] = st.best.prim >= 0 ? st.best.slot : -1;
-      w.hit_t[myslot] = st.best.t;
-      w.traced[(hq_h + hq_n + __popc(db & ltm)) & kMask] = (uint8_t)myslot;
-      has_ray = false;
-    }
-    hq_n += __popc(db);
-    __syncwarp();
-  }
-  /* one atomic per warp */
-  for (int o = 16; o > 0; o >>= 1) my_segments += __shfl_xor_sync(0xffffffffu, my_segments, o);
-  if (lane == 0 && my_segments) atomicAdd(segments, my_segments);
-}
-
 /* path p copies its counts[p] records to dst[offsets[p] - base ...) while below `limit` records */
 /* key of a stored photon: light << 56 | launch index << 8 | ordinal of the store on its path — sorting the
  * shards of several ranks by it restores the single-GPU output order */
@@ -489,10 +293,8 @@ static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights,
   ki.n_lights = n_lights;
   for (int l = 0; l <= n_lights; l++) ki.light_first[l] = P.light_first[l];
   ki.first_photon = first_photon; ki.photon_stride = photon_stride;
-  static const bool old_walk = getenv("PM_WALK_OLD") != nullptr; /* measurement knob: one path per lane */
   int blocks_per_sm = 0;
-  if (old_walk) PM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_walk, 128, 0));
-  else PM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_walk_q, kWalkWarps * 32, 0));
+  PM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_walk, 128, 0));
   if (blocks_per_sm < 1) blocks_per_sm = 1;
   int64_t written = 0; /* records produced so far (may exceed capacity) */
   float ms_total = 0.f;
@@ -503,8 +305,7 @@ static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights,
     int64_t grid = (int64_t)ctx->sm_count * blocks_per_sm;
     if (grid > pm::div_up(nb, 128)) grid = pm::div_up(nb, 128);
     PM_CUDA(cudaEventRecord(ctx->ev0, st));
-    if (old_walk) k_walk<<<(unsigned)grid, 128, 0, st>>>(P, ctrs, slots, counts, ctrs + 1);
-    else k_walk_q<<<(unsigned)grid, kWalkWarps * 32, 0, st>>>(P, ctrs, slots, counts, ctrs + 1);
+    k_walk<<<(unsigned)grid, 128, 0, st>>>(P, ctrs, slots, counts, ctrs + 1);
     PM_CUDA(cudaEventRecord(ctx->ev1, st));
     PM_CUDA(cudaGetLastError());
     {
