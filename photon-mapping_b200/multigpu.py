@@ -6,7 +6,9 @@ between stage 1 and stage 2:
            first_photon = r, photon_stride = G); scene and BVH are replicated;
   exchange all_gather of the per-rank counts, then all_gather of the padded 40-byte records and their
            64-bit keys; sorting by key restores exactly the single-GPU output order (light, launch index,
-           bounce), so the replicated photon map is bit-identical to the 1-GPU map;
+           bounce), so the replicated photon map is bit-identical to the 1-GPU map. (The library's own
+           exchange, pm_exchange_photons in csrc/pm_comm.cu, needs neither keys nor a sort: one count byte
+           per path and two prefix sums place every record; `place_by_counts` below states it in numpy.)
   stage 2  every rank builds the same map (replicated build);
   stage 3  pixels (or queries) shard by contiguous range, no communication; framebuffers are summed
            (disjoint ranges, zero elsewhere) or gathered on rank 0.
@@ -44,6 +46,43 @@ def merge_shards(records: list[np.ndarray], keys: list[np.ndarray]) -> tuple[np.
     key = np.concatenate(keys) if keys else np.zeros(0, np.uint64)
     order = np.argsort(key, kind="stable")
     return rec[order], key[order]
+
+
+def exchange_layout(sizes: list[int], world: int):
+    """The path layout of a sharded emission, as pm_exchange_photons lays it out (csrc/pm_comm.cu make_layout/locate):
+    global path g = light_base[l] + i belongs to rank i % world and is that rank's local path lf[rank][l] + i // world.
+    Returns (rank_of[g], local_of[g], paths_per_rank)."""
+    rank_of, local_of = [], []
+    lf = [0] * world
+    for n in sizes:
+        i = np.arange(int(n), dtype=np.int64)
+        r = i % world
+        rank_of.append(r)
+        local_of.append(np.asarray(lf, np.int64)[r] + i // world)
+        for k in range(world):
+            lf[k] += (n - k + world - 1) // world if n > k else 0
+    cat = lambda a: np.concatenate(a) if a else np.zeros(0, np.int64)
+    return cat(rank_of), cat(local_of), lf
+
+
+def place_by_counts(counts: list[np.ndarray], records: list[np.ndarray], sizes: list[int]) -> np.ndarray:
+    """Sort-free merge of per-rank shards (numpy statement of pm_comm.cu exchange_place): `counts[r]` holds one byte per
+    path rank r traced (photons stored on it), `records[r]` that rank's records in its own emission order. Two
+    prefix sums (global path order, per-rank order) give every path's source and destination offsets; the result is
+    the single-GPU record order without any key."""
+    world = len(counts)
+    rank_of, local_of, per_rank = exchange_layout(sizes, world)
+    for r in range(world):
+        assert len(counts[r]) == per_rank[r], "count bytes do not match the launch layout"
+    c = np.array([counts[r][p] for r, p in zip(rank_of, local_of)], np.int64) if len(rank_of) else np.zeros(0, np.int64)
+    goff = np.concatenate([[0], np.cumsum(c)])
+    roff = [np.concatenate([[0], np.cumsum(counts[r].astype(np.int64))]) for r in range(world)]
+    width = records[0].shape[1] if records and records[0].ndim == 2 else PHOTON40_BYTES
+    out = np.zeros((int(goff[-1]), width), np.uint8)
+    for g in np.nonzero(c)[0]:
+        r, p = int(rank_of[g]), int(local_of[g])
+        out[goff[g]:goff[g + 1]] = records[r][roff[r][p]:roff[r][p + 1]]
+    return out
 
 
 def allgather_photons(local_records, local_keys, group=None, device=None):

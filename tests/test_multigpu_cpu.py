@@ -34,6 +34,27 @@ def fake_emit(sizes, first, stride):
     return np.stack(rec), np.array(keys, np.uint64)
 
 
+def fake_counts(sizes, first, stride):
+    """One count byte per path of the same fake emission, in this rank's emission order (pm_emit_photons_counted)."""
+    return np.array([(i * 2654435761 + l * 97) % 4 for l, n in enumerate(sizes) for i in range(first, n, stride)], np.uint8)
+
+
+def test_sort_free_placement_equals_key_merge():
+    """pm_exchange_photons' layout arithmetic (csrc/pm_comm.cu), stated in numpy: count bytes + two prefix sums give the
+    same array as the keyed merge, for ragged lights (fewer paths than ranks, empty lights) and any world size."""
+    mg = graft.load_package_module("multigpu")
+    for sizes in ([40, 13, 27], [0, 5, 0], [1], [3, 2, 1, 0, 9], []):
+        full_rec, _ = fake_emit(sizes, 0, 1)
+        for world in (1, 2, 3, 5, 8):
+            shards = [fake_emit(sizes, r, world)[0] for r in range(world)]
+            counts = [fake_counts(sizes, r, world) for r in range(world)]
+            assert [len(c) for c in counts] == [mg.rank_path_count(sizes, r, world) for r in range(world)]
+            got = mg.place_by_counts(counts, shards, sizes)
+            assert np.array_equal(got, full_rec.reshape(-1, 40))
+    with pytest.raises(AssertionError):
+        mg.place_by_counts([np.zeros(3, np.uint8)], [np.zeros((0, 40), np.uint8)], [4])
+
+
 def test_shard_arithmetic():
     mg = graft.load_package_module("multigpu")
     assert [mg.shard_range(10, r, 4) for r in range(4)] == [(0, 3), (3, 6), (6, 8), (8, 10)]
@@ -75,6 +96,21 @@ def _worker(rank, world, port, sizes, out_dir):
     # the tensor-resident exchange (what tools/c4_run.py runs over NCCL) gives the same array
     x_rec, x_keys, counts = mg.exchange_photons(torch.from_numpy(rec.copy()), torch.from_numpy(keys.view(np.int64).copy()))
     assert torch.equal(x_rec, all_rec.reshape(-1, 40)) and torch.equal(x_keys, all_keys) and counts[rank] == len(keys)
+    # the library's sort-free exchange, same collectives over gloo: padded count rows and record rows, then placement
+    cnt = fake_counts(sizes, rank, world)
+    pmax = max(mg.rank_path_count(sizes, r, world) for r in range(world))
+    row = torch.zeros(pmax, dtype=torch.uint8)
+    row[: len(cnt)] = torch.from_numpy(cnt.copy())
+    rows = [torch.zeros_like(row) for _ in range(world)]
+    dist.all_gather(rows, row)
+    stored = [int(r.sum()) for r in rows]
+    pad = torch.zeros((max(stored), 40), dtype=torch.uint8)
+    pad[: len(rec)] = torch.from_numpy(rec.copy())
+    pads = [torch.zeros_like(pad) for _ in range(world)]
+    dist.all_gather(pads, pad)
+    placed = mg.place_by_counts([rows[r][: mg.rank_path_count(sizes, r, world)].numpy() for r in range(world)],
+                                [pads[r][: stored[r]].numpy() for r in range(world)], sizes)
+    assert np.array_equal(placed, all_rec.numpy().reshape(-1, 40))
     # progressive mode: one sum of (flux.rgb, count) per pass over disjoint photon shards
     ppm = graft.load_package_module("ppm")
     rng = np.random.default_rng(100 + rank)
