@@ -765,11 +765,23 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
  * thousands of photons per ball on blocks of 15..20 cells a side: both used to fall to the per-thread kd-tree
  * range kernel below, which now only sees balls that no block of (2 kMaxHRadius + 1)^3 cells covers. */
 constexpr int kMaxHRadius = 48;
+constexpr int kThreadMaxH = 6;
+constexpr int kRadiusSamples = 2048;
+constexpr int kRadiusDenseMean = 600; /* mean candidates per sampled hit point above which the warp kernel is faster */
+struct RadiusPick { int candidates, lit, heavy; };
+__device__ __forceinline__ bool radius_dense(const RadiusPick* pick) {
+  return pick->candidates > kRadiusDenseMean * max(pick->lit, 1);
+}
+
 __global__ void __launch_bounds__(kWarps * 32)
 k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
-              const float* __restrict__ radius2, const int* __restrict__ order, int nq, int max_h, float* __restrict__ out_flux,
+              const float* __restrict__ radius2, const int* __restrict__ order, int nq_host, const int* __restrict__ heavy_list,
+              const RadiusPick* __restrict__ pick, int max_h, float* __restrict__ out_flux,
               int32_t* __restrict__ out_count, int* __restrict__ fb_list, int* __restrict__ fb_count) {
   __shared__ WarpScratch scratch[kWarps];
+  /* after the per-thread kernel: either the whole list (dense call, that kernel did nothing) or what it left behind */
+  int nq = nq_host;
+  if (pick && !radius_dense(pick)) { order = heavy_list; nq = pick->heavy; }
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u, le_not0 = (lt | (1u << lane)) & ~1u;
   const int wid = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); /* warp-uniform to the compiler */
@@ -908,6 +920,104 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
     }
     __syncwarp();
   }
+}
+
+/* ---- the same gather, one THREAD per hit point -----------------------------------------------------
+ * With up to a few hundred photons per ball (C5 on eight ranks: 350 per lit hit point at the first pass, 90 later)
+ * a warp per hit point spends most of its instructions on block set-up, scans and reductions. Here every thread
+ * walks the ball-trimmed rows of its own hit point (same row bounds as k_grid_radius, so the same candidates);
+ * neighbouring hit points of the sorted list share their rows through L1. Measured on the C5 hit points (B200,
+ * candidates = photons in the trimmed rows, per lit hit point): 1.47 vs 2.93 ms at 125 candidates, 3.96 vs 5.68 ms
+ * at 500, level at 1200 (7.8 vs 8.3 ms), and behind from there on — 9.5 vs 8.0 ms at 900 candidates of a 14 M-photon
+ * shard, 31 vs 28 ms at 3200 of 29 M (less row sharing between neighbours as the balls shrink against the pixel
+ * footprint). So a sample of the hit points decides per call (SAMPLE pass: mean number of candidates; 2048 threads),
+ * both kernels are launched and the one that is not wanted returns at once. A hit point whose block is wider than
+ * 2 * kThreadMaxH + 1 cells is appended to heavy_list and left to the warp kernel. */
+template <bool SAMPLE>
+__global__ void __launch_bounds__(256)
+k_grid_radius_thread(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
+                     const float* __restrict__ radius2, const int* __restrict__ order, int nq, int stride,
+                     float* __restrict__ out_flux, int32_t* __restrict__ out_count, int* __restrict__ heavy_list,
+                     RadiusPick* __restrict__ pick) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (SAMPLE) t *= stride;
+  if (t >= nq) return;
+  if (!SAMPLE && radius_dense(pick)) return; /* the warp kernel takes the whole list */
+  const int qi = order ? order[t] : t;
+  const float f = brdf[qi], R2 = radius2[qi];
+  float sr = 0.f, sg = 0.f, sb = 0.f;
+  int cnt = 0, scanned = 0;
+  bool heavy = false;
+  const bool lit = f > 0.f && R2 > 0.f;
+  if (lit) {
+    const float qx = q[(size_t)qi * 3 + 0], qy = q[(size_t)qi * 3 + 1], qz = q[(size_t)qi * 3 + 2];
+    const float fx = (qx - g.lo[0]) * g.inv_cell, fy = (qy - g.lo[1]) * g.inv_cell, fz = (qz - g.lo[2]) * g.inv_cell;
+    const int cx = min(max(__float2int_rd(fx), 0), g.nx - 1), cy = min(max(__float2int_rd(fy), 0), g.ny - 1),
+              cz = min(max(__float2int_rd(fz), 0), g.nz - 1);
+    int h = max(__float2int_ru(sqrtf(R2) * g.inv_cell), 1);
+    int x0 = 0, x1 = 0, y0 = 0, y1 = 0, z0 = 0, z1 = 0;
+    bool covered = false;
+    for (; h <= kThreadMaxH; h++) { /* smallest block whose guaranteed radius covers the ball (as in k_grid_radius) */
+      x0 = max(cx - h, 0); x1 = min(cx + h, g.nx - 1);
+      y0 = max(cy - h, 0); y1 = min(cy + h, g.ny - 1);
+      z0 = max(cz - h, 0); z1 = min(cz + h, g.nz - 1);
+      float Gc = INFINITY;
+      if (x0 > 0) Gc = fminf(Gc, fx - (float)x0);
+      if (x1 < g.nx - 1) Gc = fminf(Gc, (float)(x1 + 1) - fx);
+      if (y0 > 0) Gc = fminf(Gc, fy - (float)y0);
+      if (y1 < g.ny - 1) Gc = fminf(Gc, (float)(y1 + 1) - fy);
+      if (z0 > 0) Gc = fminf(Gc, fz - (float)z0);
+      if (z1 < g.nz - 1) Gc = fminf(Gc, (float)(z1 + 1) - fz);
+      const float G = Gc * g.cell - g.margin;
+      if (G > 0.f && !(G * G < R2)) { covered = true; break; }
+    }
+    heavy = !covered;
+    for (int rz = z0; rz <= z1 && !heavy; rz++) {
+      const float zlo = g.lo[2] + (float)rz * g.cell;
+      const float dz = fmaxf(fmaxf(zlo - qz, qz - (zlo + g.cell)) - g.margin, 0.f);
+      for (int ry = y0; ry <= y1; ry++) {
+        const float ylo = g.lo[1] + (float)ry * g.cell;
+        const float dy = fmaxf(fmaxf(ylo - qy, qy - (ylo + g.cell)) - g.margin, 0.f);
+        const float dyz2 = dy * dy + dz * dz;
+        if (!(dyz2 < R2)) continue;
+        const float t2 = R2 - dyz2;
+        const float w = (t2 < 1e30f ? t2 * rsqrtf(t2) * 1.0001f : INFINITY) + g.margin;
+        const int xa = max(cell_idx(qx - w, g.lo[0], g.inv_cell, g.nx), x0);
+        const int xb = min(cell_idx(qx + w, g.lo[0], g.inv_cell, g.nx), x1);
+        if (xa > xb) continue;
+        const size_t base = ((size_t)rz * g.ny + ry) * g.nx;
+        const int st = (int)__ldg(g.cell_start + base + xa), en = (int)__ldg(g.cell_start + base + xb + 1);
+        if (SAMPLE) { scanned += en - st; continue; }
+        for (int j = st; j < en; j++) {
+          const float4 p = __ldg(g.pts + j);
+          const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+          if (d2 < R2) {
+            const float4 c = __ldg(color4 + __float_as_int(p.w));
+            sr = __fadd_rn(sr, __fmul_rn(c.w, c.x));
+            sg = __fadd_rn(sg, __fmul_rn(c.w, c.y));
+            sb = __fadd_rn(sb, __fmul_rn(c.w, c.z));
+            cnt++;
+          }
+        }
+      }
+    }
+  }
+  if (SAMPLE) {
+    if (lit) {
+      atomicAdd(&pick->candidates, heavy ? 4 * kRadiusDenseMean : min(scanned, 64 * kRadiusDenseMean));
+      atomicAdd(&pick->lit, 1);
+    }
+    return;
+  }
+  if (heavy) {
+    heavy_list[atomicAdd(&pick->heavy, 1)] = qi;
+    return;
+  }
+  const float fpos = f > 0.f ? f : 0.f;
+  out_flux[(size_t)qi * 3 + 0] = __fmul_rn(fpos, sr);
+  out_flux[(size_t)qi * 3 + 1] = __fmul_rn(fpos, sg);
+  out_flux[(size_t)qi * 3 + 2] = __fmul_rn(fpos, sb);
+  out_count[qi] = cnt;
 }
 
 /* kd-tree range query, one thread per hit point: the fallback of k_grid_radius and the only path of maps
@@ -1222,8 +1332,20 @@ int radius_query(pm_ctx* ctx, const pm_map* map, const float* q, const float* br
     /* a cells-only map has no tree to fall back on: its blocks may grow to the whole grid (then every side is
      * clipped and the block covers any ball), so nothing is ever handed over */
     const int max_h = map->cells_only ? std::max(map->gdim[0], std::max(map->gdim[1], map->gdim[2])) : kMaxHRadius;
-    k_grid_radius<<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, max_h, out_flux,
-                                                                  out_count, fb_list, fb_count);
+    /* a sample of the hit points decides between one thread and one warp per hit point (see k_grid_radius_thread) */
+    int* heavy_list = nullptr;
+    RadiusPick* pick = nullptr;
+    PM_CHECK(ctx->get_scratch(pm::S_FAST1, (size_t)nq, &heavy_list));
+    PM_CHECK(ctx->get_scratch(pm::S_FAST2, (size_t)1, &pick));
+    PM_CUDA(cudaMemsetAsync(pick, 0, sizeof(RadiusPick), ctx->stream));
+    const int stride = std::max(1, nq / kRadiusSamples);
+    k_grid_radius_thread<true><<<(unsigned)div_up(div_up(nq, stride), 256), 256, 0, ctx->stream>>>(
+        g, map->color4, q, brdf, radius2, order, nq, stride, nullptr, nullptr, nullptr, pick);
+    k_grid_radius_thread<false><<<(unsigned)div_up(nq, 256), 256, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, 1,
+                                                                                    out_flux, out_count, heavy_list, pick);
+    k_grid_radius<<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, heavy_list, pick, max_h,
+                                                                  out_flux, out_count, fb_list, fb_count);
+    ctx->launches += 2;
     if (map->cells_only) { ctx->launches++; PM_CUDA(cudaGetLastError()); return PM_OK; }
     if (kd_grid > ctx->sm_count * 2) kd_grid = ctx->sm_count * 2;
     k_kd_radius<<<(unsigned)kd_grid, 128, 0, ctx->stream>>>(map->nodes4, map->color4, (int)map->n, q, brdf, radius2, nq, fb_list,

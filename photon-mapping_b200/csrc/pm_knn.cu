@@ -482,6 +482,7 @@ int pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const flo
   PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT0, out_flux, sizeof(float) * 3 * (size_t)nq, &of));
   PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT1, out_count, sizeof(int32_t) * (size_t)nq, &oc));
   ctx->fb_count_dev = nullptr;
+  ctx->ho_count_dev = nullptr;
   if (!map || map->n < 1) {
     PM_CUDA(cudaMemsetAsync(of.dev, 0, sizeof(float) * 3 * (size_t)nq, ctx->stream));
     PM_CUDA(cudaMemsetAsync(oc.dev, 0, sizeof(int32_t) * (size_t)nq, ctx->stream));

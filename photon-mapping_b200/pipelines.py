@@ -192,9 +192,10 @@ def run_c5(pkg, ctx, comm, rank, world, W=3840, H=2160, passes=8, per_pass=15_62
         n = cnt.value
         lap()
         lit = N[sample] > 0
-        r_med = float(torch.sqrt(torch.median(r2[sample][lit]) if bool(lit.any()) else r2[0]).item())
+        # cell = a quarter of the 90th-percentile radius: blocks of at most 9 cells a side for nine hit points in ten
+        r_med = float(torch.sqrt(torch.quantile(r2[sample][lit], 0.9) if bool(lit.any()) else r2[0]).item())
         pkg._check(L.pm_photons_to_maps(ctx.handle, d40.data_ptr(), n, None, 0, g44.data_ptr(), None))
-        pmap = pkg.PhotonMap.build_cells(ctx, g44[:n], 0.2 * r_med)
+        pmap = pkg.PhotonMap.build_cells(ctx, g44[:n], 0.25 * r_med)
         lap()
         pmap.gather_radius(pos, brdf, r2, out_flux=flux, out_count=count)
         gk = ctx.last_kernel_ms

@@ -99,7 +99,7 @@ def progressive_render(pkg, ctx, scene, tri_mesh, mats, lights, camera, width: i
 
 def progressive_render_device(pkg, ctx, scene, tri_mesh, mats, lights, camera, width: int, height: int, passes: int,
                               photons_per_pass: int, r0: float, alpha: float = 0.7, max_depth: int = 8, seed: int = 1,
-                              group=None, stats: list | None = None, cells: bool = False, cell_fraction: float = 0.2):
+                              group=None, stats: list | None = None, cells: bool = False, cell_fraction: float = 0.25):
     """`progressive_render` with everything resident in HBM: hit points, per-pixel state, the pass's photons and its
     map never leave the device (the host loop above moves every pass's photons through numpy, ~80 B per photon over
     PCIe). Same arithmetic: the emission, record conversion, build and `pm_gather_radius` calls are the same C-ABI
@@ -107,7 +107,8 @@ def progressive_render_device(pkg, ctx, scene, tri_mesh, mats, lights, camera, w
     element), so N, r² and tau equal the host loop's bit for bit on one GPU. Multi-GPU: photons of a pass sharded
     by launch index, one NCCL all-reduce (sum) of (flux.rgb, count) per pass — 16 B per pixel.
     `stats`: optional list that receives one dict of per-stage milliseconds per pass.
-    `cells`: build a cells-only map per pass (pm_map_build_cells, cell = `cell_fraction` of the median radius of the lit pixels)
+    `cells`: build a cells-only map per pass (pm_map_build_cells, cell = `cell_fraction` of the 90th-percentile radius of the lit pixels:
+    blocks of at most 9 cells a side for nine hit points in ten)
     instead of the kd-tree map — the fixed-radius gather never touches the tree. Counts, hence N and r², are the
     same integers either way; flux sums differ in float addition order (photons are visited in another order)."""
     import ctypes
@@ -159,7 +160,7 @@ def progressive_render_device(pkg, ctx, scene, tri_mesh, mats, lights, camera, w
             pkg._check(L.pm_photons_to_maps(ctx.handle, d40.data_ptr(), n, None, 0, g44.data_ptr(), None))
             if cells:
                 lit = N > 0
-                r_med = float(torch.sqrt(torch.median(r2[lit]) if bool(lit.any()) else r2[0]).item())
+                r_med = float(torch.sqrt(torch.quantile(r2[lit][::61], 0.9) if bool(lit.any()) else r2[0]).item())
                 pmap = pkg.PhotonMap.build_cells(ctx, g44[:n], cell_fraction * r_med)
             else:
                 pmap = pkg.PhotonMap.build(ctx, g44[:n])

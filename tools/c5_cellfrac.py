@@ -29,9 +29,10 @@ pkg._check(L.pm_emit_photons(ctx.handle, scene.handle, lights.ctypes.data, len(l
                              d40.data_ptr(), cap, ctypes.byref(cnt), ctypes.byref(npaths), ctypes.byref(nseg)))
 n = cnt.value
 pkg._check(L.pm_photons_to_maps(ctx.handle, d40.data_ptr(), n, None, 0, g44.data_ptr(), None))
+fracs = [float(x) for x in os.environ.get("C5_FRACS", "0.15,0.2,0.3,0.4,0.5,0.7,1.0").split(",")]
 for r in (0.5, 0.35, 0.25):
     r2 = torch.full((npx,), r * r, dtype=torch.float32, device=dev)
-    for frac in (0.15, 0.2, 0.3, 0.4, 0.5, 0.7, 1.0):
+    for frac in fracs:
         ms = []
         for it in range(3):
             torch.cuda.synchronize(); t0 = time.perf_counter()
@@ -42,4 +43,4 @@ for r in (0.5, 0.35, 0.25):
             ms.append((1e3 * (t1 - t0), 1e3 * (t2 - t1), ctx.last_kernel_ms))
             pmap.close()
         b = min(ms[1:], key=lambda x: x[0] + x[1])
-        print(f"ranks {ranks} photons {n} radius {r} cell_frac {frac}: map {b[0]:.2f} ms gather {b[1]:.2f} ms (kernels {b[2]:.2f}) mean count {float(count.float().mean()):.1f}", flush=True)
+        print(f"ranks {ranks} photons {n} radius {r} cell_frac {frac}: map {b[0]:.2f} ms gather {b[1]:.2f} ms (kernels {b[2]:.2f}) heavy {ctx.last_handover_count} mean count {float(count.float().mean()):.1f}", flush=True)

@@ -57,10 +57,10 @@ def run(w, h, n_pass, n_photons, radius, sharded, stats=None):
     cam = pkg.make_camera((80.0, 30.0, 0.0), (10.0, 20.0, 0.0), (0.0, 1.0, 0.0), 0.87, w, h)
     if sharded or world == 1:
         return ppm.progressive_render_device(pkg, ctx, scene, z["tri_mesh"], mats, lights, cam, w, h, n_pass, n_photons, radius, alpha,
-                                             depth, seed=1, stats=stats, cells=cells, cell_fraction=float(os.environ.get('PM_PPM_CELL_FRAC', '0.2')))
+                                             depth, seed=1, stats=stats, cells=cells, cell_fraction=float(os.environ.get('PM_PPM_CELL_FRAC', '0.25')))
     # unsharded on this rank although a process group exists: a one-rank group of our own
     return ppm.progressive_render_device(pkg, ctx, scene, z["tri_mesh"], mats, lights, cam, w, h, n_pass, n_photons, radius, alpha,
-                                         depth, seed=1, stats=stats, group=solo, cells=cells, cell_fraction=float(os.environ.get('PM_PPM_CELL_FRAC', '0.2')))
+                                         depth, seed=1, stats=stats, group=solo, cells=cells, cell_fraction=float(os.environ.get('PM_PPM_CELL_FRAC', '0.25')))
 
 
 if world > 1:
