@@ -764,6 +764,14 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
  * (its rows are long: every step is a coalesced 512-byte read). Early passes of a progressive render hold
  * thousands of photons per ball on blocks of 15..20 cells a side: both used to fall to the per-thread kd-tree
  * range kernel below, which now only sees balls that no block of (2 kMaxHRadius + 1)^3 cells covers. */
+/* flux += power * colour of one accepted photon; PREMUL: the product was formed when the cells-only map was built */
+template <bool PREMUL>
+__device__ __forceinline__ void add_flux(const float4 c, float& sr, float& sg, float& sb) {
+  sr = __fadd_rn(sr, PREMUL ? c.x : __fmul_rn(c.w, c.x));
+  sg = __fadd_rn(sg, PREMUL ? c.y : __fmul_rn(c.w, c.y));
+  sb = __fadd_rn(sb, PREMUL ? c.z : __fmul_rn(c.w, c.z));
+}
+
 constexpr int kMaxHRadius = 48;
 constexpr int kThreadMaxH = 6;
 constexpr int kRadiusSamples = 2048;
@@ -773,6 +781,7 @@ __device__ __forceinline__ bool radius_dense(const RadiusPick* pick) {
   return pick->candidates > kRadiusDenseMean * max(pick->lit, 1);
 }
 
+template <bool PREMUL>
 __global__ void __launch_bounds__(kWarps * 32)
 k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
               const float* __restrict__ radius2, const int* __restrict__ order, int nq_host, const int* __restrict__ heavy_list,
@@ -862,9 +871,7 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
               const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
               if (d2 < R2) {
                 const float4 c = __ldg(color4 + __float_as_int(p.w));
-                sr = __fadd_rn(sr, __fmul_rn(c.w, c.x));
-                sg = __fadd_rn(sg, __fmul_rn(c.w, c.y));
-                sb = __fadd_rn(sb, __fmul_rn(c.w, c.z));
+                add_flux<PREMUL>(c, sr, sg, sb);
                 cnt++;
               }
             }
@@ -892,9 +899,7 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
           const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
           if (j < mc && d2 < R2) {
             const float4 c = __ldg(color4 + __float_as_int(p.w));
-            sr = __fadd_rn(sr, __fmul_rn(c.w, c.x));
-            sg = __fadd_rn(sg, __fmul_rn(c.w, c.y));
-            sb = __fadd_rn(sb, __fmul_rn(c.w, c.z));
+            add_flux<PREMUL>(c, sr, sg, sb);
             cnt++;
           }
         }
@@ -930,17 +935,19 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
  * candidates = photons in the trimmed rows, per lit hit point): 1.47 vs 2.93 ms at 125 candidates, 3.96 vs 5.68 ms
  * at 500, level at 1200 (7.8 vs 8.3 ms), and behind from there on — 9.5 vs 8.0 ms at 900 candidates of a 14 M-photon
  * shard, 31 vs 28 ms at 3200 of 29 M (less row sharing between neighbours as the balls shrink against the pixel
- * footprint). So a sample of the hit points decides per call (SAMPLE pass: mean number of candidates; 2048 threads),
+ * footprint). So a sample of the hit points decides per call (SAMPLE pass: mean number of candidates, 2048 warps),
  * both kernels are launched and the one that is not wanted returns at once. A hit point whose block is wider than
  * 2 * kThreadMaxH + 1 cells is appended to heavy_list and left to the warp kernel. */
-template <bool SAMPLE>
+template <bool SAMPLE, bool PREMUL>
 __global__ void __launch_bounds__(256)
 k_grid_radius_thread(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
                      const float* __restrict__ radius2, const int* __restrict__ order, int nq, int stride,
                      float* __restrict__ out_flux, int32_t* __restrict__ out_count, int* __restrict__ heavy_list,
                      RadiusPick* __restrict__ pick) {
+  /* SAMPLE: one warp per sampled hit point (its rows are dealt to the lanes), every stride-th of the list */
   int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (SAMPLE) t *= stride;
+  const int row_first = SAMPLE ? (int)(threadIdx.x & 31) : 0, row_step = SAMPLE ? 32 : 1;
+  if (SAMPLE) t = (t >> 5) * stride;
   if (t >= nq) return;
   if (!SAMPLE && radius_dense(pick)) return; /* the warp kernel takes the whole list */
   const int qi = order ? order[t] : t;
@@ -972,38 +979,36 @@ k_grid_radius_thread(const GridView g, const float4* __restrict__ color4, const 
       if (G > 0.f && !(G * G < R2)) { covered = true; break; }
     }
     heavy = !covered;
-    for (int rz = z0; rz <= z1 && !heavy; rz++) {
-      const float zlo = g.lo[2] + (float)rz * g.cell;
+    const int ny_r = y1 - y0 + 1, nrows = heavy ? 0 : ny_r * (z1 - z0 + 1);
+    for (int row = row_first; row < nrows; row += row_step) {
+      const int rzo = row / ny_r;
+      const int ry = y0 + row - rzo * ny_r, rz = z0 + rzo;
+      const float zlo = g.lo[2] + (float)rz * g.cell, ylo = g.lo[1] + (float)ry * g.cell;
       const float dz = fmaxf(fmaxf(zlo - qz, qz - (zlo + g.cell)) - g.margin, 0.f);
-      for (int ry = y0; ry <= y1; ry++) {
-        const float ylo = g.lo[1] + (float)ry * g.cell;
-        const float dy = fmaxf(fmaxf(ylo - qy, qy - (ylo + g.cell)) - g.margin, 0.f);
-        const float dyz2 = dy * dy + dz * dz;
-        if (!(dyz2 < R2)) continue;
-        const float t2 = R2 - dyz2;
-        const float w = (t2 < 1e30f ? t2 * rsqrtf(t2) * 1.0001f : INFINITY) + g.margin;
-        const int xa = max(cell_idx(qx - w, g.lo[0], g.inv_cell, g.nx), x0);
-        const int xb = min(cell_idx(qx + w, g.lo[0], g.inv_cell, g.nx), x1);
-        if (xa > xb) continue;
-        const size_t base = ((size_t)rz * g.ny + ry) * g.nx;
-        const int st = (int)__ldg(g.cell_start + base + xa), en = (int)__ldg(g.cell_start + base + xb + 1);
-        if (SAMPLE) { scanned += en - st; continue; }
-        for (int j = st; j < en; j++) {
-          const float4 p = __ldg(g.pts + j);
-          const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
-          if (d2 < R2) {
-            const float4 c = __ldg(color4 + __float_as_int(p.w));
-            sr = __fadd_rn(sr, __fmul_rn(c.w, c.x));
-            sg = __fadd_rn(sg, __fmul_rn(c.w, c.y));
-            sb = __fadd_rn(sb, __fmul_rn(c.w, c.z));
-            cnt++;
-          }
+      const float dy = fmaxf(fmaxf(ylo - qy, qy - (ylo + g.cell)) - g.margin, 0.f);
+      const float dyz2 = dy * dy + dz * dz;
+      if (!(dyz2 < R2)) continue;
+      const float t2 = R2 - dyz2;
+      const float w = (t2 < 1e30f ? t2 * rsqrtf(t2) * 1.0001f : INFINITY) + g.margin;
+      const int xa = max(cell_idx(qx - w, g.lo[0], g.inv_cell, g.nx), x0);
+      const int xb = min(cell_idx(qx + w, g.lo[0], g.inv_cell, g.nx), x1);
+      if (xa > xb) continue;
+      const size_t base = ((size_t)rz * g.ny + ry) * g.nx;
+      const int st = (int)__ldg(g.cell_start + base + xa), en = (int)__ldg(g.cell_start + base + xb + 1);
+      if (SAMPLE) { scanned += en - st; continue; }
+      for (int j = st; j < en; j++) {
+        const float4 p = __ldg(g.pts + j);
+        const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
+        if (d2 < R2) {
+          add_flux<PREMUL>(__ldg(color4 + __float_as_int(p.w)), sr, sg, sb);
+          cnt++;
         }
       }
     }
   }
-  if (SAMPLE) {
-    if (lit) {
+  if (SAMPLE) { /* warp-uniform: lit and heavy depend on the hit point only */
+    scanned = __reduce_add_sync(0xffffffffu, scanned);
+    if (lit && (threadIdx.x & 31) == 0) {
       atomicAdd(&pick->candidates, heavy ? 4 * kRadiusDenseMean : min(scanned, 64 * kRadiusDenseMean));
       atomicAdd(&pick->lit, 1);
     }
@@ -1131,12 +1136,14 @@ namespace pm {
 
 /* cells-only maps: colours follow the cell order of grid_pts and the id a record carries becomes its own position,
  * so the colour of a candidate sits next to its position (input order is the order photons were traced in: every
- * colour fetch would be a DRAM sector of its own) */
+ * colour fetch would be a DRAM sector of its own). The colours are stored multiplied by the power (PREMUL kernels). */
 __global__ void k_cells_reorder(int n, float4* __restrict__ pts, const float4* __restrict__ color_in, float4* __restrict__ color_out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   float4 p = pts[i];
-  color_out[i] = __ldg(color_in + __float_as_int(p.w));
+  const float4 c = __ldg(color_in + __float_as_int(p.w));
+  /* power * colour is formed here once (same products, same rounding as in the gather loop of a full map) */
+  color_out[i] = make_float4(__fmul_rn(c.w, c.x), __fmul_rn(c.w, c.y), __fmul_rn(c.w, c.z), c.w);
   p.w = __int_as_float(i);
   pts[i] = p;
 }
@@ -1339,12 +1346,22 @@ int radius_query(pm_ctx* ctx, const pm_map* map, const float* q, const float* br
     PM_CHECK(ctx->get_scratch(pm::S_FAST2, (size_t)1, &pick));
     PM_CUDA(cudaMemsetAsync(pick, 0, sizeof(RadiusPick), ctx->stream));
     const int stride = std::max(1, nq / kRadiusSamples);
-    k_grid_radius_thread<true><<<(unsigned)div_up(div_up(nq, stride), 256), 256, 0, ctx->stream>>>(
-        g, map->color4, q, brdf, radius2, order, nq, stride, nullptr, nullptr, nullptr, pick);
-    k_grid_radius_thread<false><<<(unsigned)div_up(nq, 256), 256, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, 1,
-                                                                                    out_flux, out_count, heavy_list, pick);
-    k_grid_radius<<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, heavy_list, pick, max_h,
-                                                                  out_flux, out_count, fb_list, fb_count);
+    const unsigned sgrid = (unsigned)div_up(div_up(nq, stride) * 32, 256), tgrid = (unsigned)div_up(nq, 256);
+    if (map->cells_only) {
+      k_grid_radius_thread<true, true><<<sgrid, 256, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, stride, nullptr,
+                                                                       nullptr, nullptr, pick);
+      k_grid_radius_thread<false, true><<<tgrid, 256, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, 1, out_flux,
+                                                                        out_count, heavy_list, pick);
+      k_grid_radius<true><<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, heavy_list, pick,
+                                                                          max_h, out_flux, out_count, fb_list, fb_count);
+    } else {
+      k_grid_radius_thread<true, false><<<sgrid, 256, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, stride, nullptr,
+                                                                        nullptr, nullptr, pick);
+      k_grid_radius_thread<false, false><<<tgrid, 256, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, 1, out_flux,
+                                                                         out_count, heavy_list, pick);
+      k_grid_radius<false><<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, heavy_list, pick,
+                                                                           max_h, out_flux, out_count, fb_list, fb_count);
+    }
     ctx->launches += 2;
     if (map->cells_only) { ctx->launches++; PM_CUDA(cudaGetLastError()); return PM_OK; }
     if (kd_grid > ctx->sm_count * 2) kd_grid = ctx->sm_count * 2;
