@@ -28,6 +28,7 @@
 #include <cub/cub.cuh>
 #include <algorithm>
 #include <cfloat>
+#include <climits>
 #include <cmath>
 #include "pm_knn.cuh"
 
@@ -756,14 +757,6 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
   }
 }
 
-/* ---- fixed-radius gather (progressive photon mapping pass; SURVEY appendix B — no reference code) ------
- * Per hit point: flux = brdf * sum(power * colour) over the nodes with dist² < radius², count = their number.
- * Same candidate enumeration as k_grid_query (ball-trimmed rows of the smallest block that covers the ball),
- * no selection. Rows are taken 32 at a time (one per lane); a chunk of rows with at most kMaxScan candidates is
- * flattened into one index space so that short rows still fill the warp, a denser chunk is streamed row by row
- * (its rows are long: every step is a coalesced 512-byte read). Early passes of a progressive render hold
- * thousands of photons per ball on blocks of 15..20 cells a side: both used to fall to the per-thread kd-tree
- * range kernel below, which now only sees balls that no block of (2 kMaxHRadius + 1)^3 cells covers. */
 /* flux += power * colour of one accepted photon; PREMUL: the product was formed when the cells-only map was built */
 template <bool PREMUL>
 __device__ __forceinline__ void add_flux(const float4 c, float& sr, float& sg, float& sb) {
@@ -775,12 +768,22 @@ __device__ __forceinline__ void add_flux(const float4 c, float& sr, float& sg, f
 constexpr int kMaxHRadius = 48;
 constexpr int kThreadMaxH = 6;
 constexpr int kRadiusSamples = 2048;
-constexpr int kRadiusDenseMean = 600; /* mean candidates per sampled hit point above which the warp kernel is faster */
+constexpr int kRadiusDenseMean = 300; /* mean candidates per sampled hit point from which the group kernel is faster */
 struct RadiusPick { int candidates, lit, heavy; };
 __device__ __forceinline__ bool radius_dense(const RadiusPick* pick) {
   return pick->candidates > kRadiusDenseMean * max(pick->lit, 1);
 }
 
+/* ---- fixed-radius gather (progressive photon mapping pass; SURVEY appendix B — no reference code) ------
+ * Per hit point: flux = brdf * sum(power * colour) over the nodes with dist² < radius², count = their number.
+ * Same candidate enumeration as k_grid_query (ball-trimmed rows of the smallest block that covers the ball),
+ * no selection. Rows are taken 32 at a time (one per lane); a chunk of rows with at most kMaxScan candidates is
+ * flattened into one index space so that short rows still fill the warp, a denser chunk is streamed row by row
+ * (its rows are long: every step is a coalesced 512-byte read). Early passes of a progressive render hold
+ * thousands of photons per ball on blocks of 15..20 cells a side: both used to fall to the per-thread kd-tree
+ * range kernel below, which now only sees balls that no block of (2 kMaxHRadius + 1)^3 cells covers.
+ * Since the per-group and per-thread kernels below exist, this one takes what they leave behind (heavy_list:
+ * groups that are not compact, blocks too wide for a thread), or the whole list when called without a pick. */
 template <bool PREMUL>
 __global__ void __launch_bounds__(kWarps * 32)
 k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
@@ -788,9 +791,9 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
               const RadiusPick* __restrict__ pick, int max_h, float* __restrict__ out_flux,
               int32_t* __restrict__ out_count, int* __restrict__ fb_list, int* __restrict__ fb_count) {
   __shared__ WarpScratch scratch[kWarps];
-  /* after the per-thread kernel: either the whole list (dense call, that kernel did nothing) or what it left behind */
+  /* after the per-thread / per-group kernels: only what they left behind */
   int nq = nq_host;
-  if (pick && !radius_dense(pick)) { order = heavy_list; nq = pick->heavy; }
+  if (pick) { order = heavy_list; nq = pick->heavy; }
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u, le_not0 = (lt | (1u << lane)) & ~1u;
   const int wid = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); /* warp-uniform to the compiler */
@@ -927,17 +930,208 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
   }
 }
 
+/* ---- the same gather, one warp per GROUP of kGroup neighbouring hit points ------------------------------
+ * Dense balls (thousands of photons each): neighbouring hit points of the sorted list — neighbouring pixels — see
+ * almost the same photons, yet one warp per hit point pulls every candidate through L1 once per hit point (ncu on
+ * the C5 frame, 2800 photons per ball: 12.5 TB/s between L2 and L1, long-scoreboard 16.8 stalls per issue, and 37
+ * instructions per 32 (hit point, candidate) pairs, most of them row bookkeeping). Here a warp walks the trimmed
+ * rows of the UNION of kGroup blocks once and tests every candidate against the kGroup balls held in registers:
+ * one load and one round of bookkeeping per kGroup tests. Same candidates and more (a superset of every member's
+ * rows), same distance arithmetic and comparison: counts are unchanged. A group that is not compact (its union
+ * block holds more than twice the cells of its largest member's: a scanline or bin boundary in the order), or
+ * that has a member no block covers, is appended to heavy_list for k_grid_radius. */
+constexpr int kGroup = 4;
+struct __align__(16) GroupScratch {
+  uint2 words[kWords];
+  int run_off[32];
+};
+
+template <bool PREMUL>
+__global__ void __launch_bounds__(kWarps * 32, 4)
+k_grid_radius_group(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
+                    const float* __restrict__ radius2, const int* __restrict__ order, int nq, int max_h, float* __restrict__ out_flux,
+                    int32_t* __restrict__ out_count, int* __restrict__ heavy_list, RadiusPick* __restrict__ pick) {
+  __shared__ GroupScratch scratch[kWarps];
+  if (!radius_dense(pick)) return; /* the per-thread kernel has taken the list */
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u, le_not0 = (lt | (1u << lane)) & ~1u;
+  const int wid = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); /* warp-uniform to the compiler */
+  GroupScratch& ws = scratch[wid];
+  const int ngroups = (nq + kGroup - 1) / kGroup;
+  for (int t = blockIdx.x * kWarps + wid; t < ngroups; t += gridDim.x * kWarps) {
+    /* lanes 0 .. kGroup-1 own one member each: block and cover test as in k_grid_radius */
+    const int my = t * kGroup + lane;
+    const bool have = lane < kGroup && my < nq;
+    const int qi_l = have ? (order ? order[my] : my) : -1;
+    const float f_l = have ? brdf[qi_l] : 0.f, R2_l = have ? radius2[qi_l] : 0.f;
+    const bool lit_l = f_l > 0.f && R2_l > 0.f;
+    float qx_l = 0.f, qy_l = 0.f, qz_l = 0.f;
+    int x0 = INT_MAX, x1 = INT_MIN, y0 = INT_MAX, y1 = INT_MIN, z0 = INT_MAX, z1 = INT_MIN, vol_l = 0;
+    bool covered = true;
+    if (lit_l) {
+      qx_l = q[(size_t)qi_l * 3 + 0]; qy_l = q[(size_t)qi_l * 3 + 1]; qz_l = q[(size_t)qi_l * 3 + 2];
+      const float fx = (qx_l - g.lo[0]) * g.inv_cell, fy = (qy_l - g.lo[1]) * g.inv_cell, fz = (qz_l - g.lo[2]) * g.inv_cell;
+      const int cx = min(max(__float2int_rd(fx), 0), g.nx - 1), cy = min(max(__float2int_rd(fy), 0), g.ny - 1),
+                cz = min(max(__float2int_rd(fz), 0), g.nz - 1);
+      covered = false;
+      for (int h = min(max(__float2int_ru(sqrtf(R2_l) * g.inv_cell), 1), max_h); h <= max_h; h++) {
+        x0 = max(cx - h, 0); x1 = min(cx + h, g.nx - 1);
+        y0 = max(cy - h, 0); y1 = min(cy + h, g.ny - 1);
+        z0 = max(cz - h, 0); z1 = min(cz + h, g.nz - 1);
+        float Gc = INFINITY;
+        if (x0 > 0) Gc = fminf(Gc, fx - (float)x0);
+        if (x1 < g.nx - 1) Gc = fminf(Gc, (float)(x1 + 1) - fx);
+        if (y0 > 0) Gc = fminf(Gc, fy - (float)y0);
+        if (y1 < g.ny - 1) Gc = fminf(Gc, (float)(y1 + 1) - fy);
+        if (z0 > 0) Gc = fminf(Gc, fz - (float)z0);
+        if (z1 < g.nz - 1) Gc = fminf(Gc, (float)(z1 + 1) - fz);
+        const float G = Gc * g.cell - g.margin;
+        if (G > 0.f && !(G * G < R2_l)) { covered = true; break; }
+      }
+      /* cells of the member's block, saturated (a cells-only map's block may be the whole grid) */
+      vol_l = (int)fminf((float)(x1 - x0 + 1) * (float)(y1 - y0 + 1) * (float)(z1 - z0 + 1), 1e9f);
+      if (!covered) { x0 = y0 = z0 = INT_MAX; x1 = y1 = z1 = INT_MIN; }
+    }
+    const unsigned litmask = __ballot_sync(0xffffffffu, lit_l);
+    if (litmask == 0u) { /* nothing but misses */
+      if (have) {
+        out_flux[(size_t)qi_l * 3 + 0] = 0.f; out_flux[(size_t)qi_l * 3 + 1] = 0.f; out_flux[(size_t)qi_l * 3 + 2] = 0.f;
+        out_count[qi_l] = 0;
+      }
+      continue;
+    }
+    const int X0 = __reduce_min_sync(0xffffffffu, x0), X1 = __reduce_max_sync(0xffffffffu, x1);
+    const int Y0 = __reduce_min_sync(0xffffffffu, y0), Y1 = __reduce_max_sync(0xffffffffu, y1);
+    const int Z0 = __reduce_min_sync(0xffffffffu, z0), Z1 = __reduce_max_sync(0xffffffffu, z1);
+    const int vmax = __reduce_max_sync(0xffffffffu, vol_l);
+    const float volU = (float)(X1 - X0 + 1) * (float)(Y1 - Y0 + 1) * (float)(Z1 - Z0 + 1);
+    if (__any_sync(0xffffffffu, lit_l && !covered) || volU > 2.f * (float)vmax) {
+      if (have) heavy_list[atomicAdd(&pick->heavy, 1)] = qi_l;
+      continue;
+    }
+    float qx[kGroup], qy[kGroup], qz[kGroup], R2[kGroup], sr[kGroup], sg[kGroup], sb[kGroup];
+    int cnt[kGroup];
+#pragma unroll
+    for (int m = 0; m < kGroup; m++) {
+      qx[m] = __shfl_sync(0xffffffffu, qx_l, m); qy[m] = __shfl_sync(0xffffffffu, qy_l, m); qz[m] = __shfl_sync(0xffffffffu, qz_l, m);
+      const float r2m = __shfl_sync(0xffffffffu, R2_l, m);
+      R2[m] = (litmask >> m) & 1u ? r2m : -1.f; /* a miss accepts nothing */
+      sr[m] = sg[m] = sb[m] = 0.f; cnt[m] = 0;
+    }
+    auto test = [&](const float4 p, const bool valid) {
+      bool ps[kGroup], any = false;
+#pragma unroll
+      for (int m = 0; m < kGroup; m++) {
+        ps[m] = valid && pmk::dist2(p.x, p.y, p.z, qx[m], qy[m], qz[m]) < R2[m];
+        any = any || ps[m];
+      }
+      if (any) {
+        const float4 c = __ldg(color4 + __float_as_int(p.w));
+#pragma unroll
+        for (int m = 0; m < kGroup; m++)
+          if (ps[m]) { add_flux<PREMUL>(c, sr[m], sg[m], sb[m]); cnt[m]++; }
+      }
+    };
+    const int ny_r = Y1 - Y0 + 1, nrows = ny_r * (Z1 - Z0 + 1);
+    for (int r0 = 0; r0 < nrows; r0 += 32) {
+      const int row = r0 + lane;
+      int len = 0, st = 0;
+      if (row < nrows) {
+        const int rzo = row / ny_r;
+        const int ry = Y0 + row - rzo * ny_r, rz = Z0 + rzo;
+        const float ylo = g.lo[1] + (float)ry * g.cell, zlo = g.lo[2] + (float)rz * g.cell;
+        int xa = INT_MAX, xb = INT_MIN;
+#pragma unroll
+        for (int m = 0; m < kGroup; m++) { /* the row's x range: union of the members' trimmed ranges */
+          const float dy = fmaxf(fmaxf(ylo - qy[m], qy[m] - (ylo + g.cell)) - g.margin, 0.f);
+          const float dz = fmaxf(fmaxf(zlo - qz[m], qz[m] - (zlo + g.cell)) - g.margin, 0.f);
+          const float dyz2 = dy * dy + dz * dz;
+          if (dyz2 < R2[m]) {
+            const float t2 = R2[m] - dyz2;
+            const float w = (t2 < 1e30f ? t2 * rsqrtf(t2) * 1.0001f : INFINITY) + g.margin;
+            xa = min(xa, max(cell_idx(qx[m] - w, g.lo[0], g.inv_cell, g.nx), X0));
+            xb = max(xb, min(cell_idx(qx[m] + w, g.lo[0], g.inv_cell, g.nx), X1));
+          }
+        }
+        if (xa <= xb) {
+          const size_t base = ((size_t)rz * g.ny + ry) * g.nx;
+          st = (int)__ldg(g.cell_start + base + xa);
+          len = (int)__ldg(g.cell_start + base + xb + 1) - st;
+        }
+      }
+      int incl = len;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      const int mc = __shfl_sync(0xffffffffu, incl, 31);
+      if (mc == 0) continue;
+      if (mc > kMaxScan) { /* dense chunk: row by row (long rows: every step is a coalesced 512-byte read) */
+        unsigned rows_left = __ballot_sync(0xffffffffu, len > 0);
+        while (rows_left) {
+          const int r = __ffs(rows_left) - 1;
+          rows_left &= rows_left - 1;
+          const int rs = __shfl_sync(0xffffffffu, st, r), rl = __shfl_sync(0xffffffffu, len, r);
+          for (int j = lane; j < rl; j += 32) test(__ldg(g.pts + (rs + j)), true);
+        }
+        continue;
+      }
+      const int P = incl - len;
+      __syncwarp();
+      ws.words[lane] = make_uint2(0u, 0u);
+      __syncwarp();
+      const unsigned nonempty = __ballot_sync(0xffffffffu, len > 0);
+      if (len > 0) {
+        const int d = __popc(nonempty & lt);
+        atomicOr(&ws.words[P >> 5].x, 1u << (P & 31));
+        ws.run_off[d] = st - P;
+        for (int i = (P + 31) >> 5; i * 32 < P + len; i++) ws.words[i].y = (unsigned)d;
+      }
+      __syncwarp();
+      for (int i = 0; i * 32 < mc; i++) {
+        const int j = i * 32 + lane;
+        const uint2 w = ws.words[i];
+        const int run = (int)w.y + __popc(w.x & le_not0);
+        test(__ldg(g.pts + (ws.run_off[run] + min(j, mc - 1))), j < mc);
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < kGroup; m++) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        sr[m] = __fadd_rn(sr[m], __shfl_xor_sync(0xffffffffu, sr[m], o));
+        sg[m] = __fadd_rn(sg[m], __shfl_xor_sync(0xffffffffu, sg[m], o));
+        sb[m] = __fadd_rn(sb[m], __shfl_xor_sync(0xffffffffu, sb[m], o));
+      }
+      cnt[m] = __reduce_add_sync(0xffffffffu, cnt[m]);
+    }
+    /* lane m writes member m */
+    float wr = 0.f, wg = 0.f, wb = 0.f;
+    int wc = 0;
+#pragma unroll
+    for (int m = 0; m < kGroup; m++)
+      if (lane == m) { wr = sr[m]; wg = sg[m]; wb = sb[m]; wc = cnt[m]; }
+    if (have) {
+      out_flux[(size_t)qi_l * 3 + 0] = lit_l ? __fmul_rn(f_l, wr) : 0.f;
+      out_flux[(size_t)qi_l * 3 + 1] = lit_l ? __fmul_rn(f_l, wg) : 0.f;
+      out_flux[(size_t)qi_l * 3 + 2] = lit_l ? __fmul_rn(f_l, wb) : 0.f;
+      out_count[qi_l] = lit_l ? wc : 0;
+    }
+    __syncwarp();
+  }
+}
+
 /* ---- the same gather, one THREAD per hit point -----------------------------------------------------
- * With up to a few hundred photons per ball (C5 on eight ranks: 350 per lit hit point at the first pass, 90 later)
- * a warp per hit point spends most of its instructions on block set-up, scans and reductions. Here every thread
- * walks the ball-trimmed rows of its own hit point (same row bounds as k_grid_radius, so the same candidates);
+ * With up to a couple of hundred photons per ball (C5 on eight ranks after the first passes: 90 per lit hit point)
+ * even a warp per group spends most of its instructions on set-up, scans and reductions. Here every thread walks
+ * the ball-trimmed rows of its own hit point (same row bounds as k_grid_radius, so the same candidates);
  * neighbouring hit points of the sorted list share their rows through L1. Measured on the C5 hit points (B200,
- * candidates = photons in the trimmed rows, per lit hit point): 1.47 vs 2.93 ms at 125 candidates, 3.96 vs 5.68 ms
- * at 500, level at 1200 (7.8 vs 8.3 ms), and behind from there on — 9.5 vs 8.0 ms at 900 candidates of a 14 M-photon
- * shard, 31 vs 28 ms at 3200 of 29 M (less row sharing between neighbours as the balls shrink against the pixel
- * footprint). So a sample of the hit points decides per call (SAMPLE pass: mean number of candidates, 2048 warps),
- * both kernels are launched and the one that is not wanted returns at once. A hit point whose block is wider than
- * 2 * kThreadMaxH + 1 cells is appended to heavy_list and left to the warp kernel. */
+ * candidates = photons in the trimmed rows, per lit hit point; group kernel second): 1.45 vs 1.87 ms at 170
+ * candidates, 2.28 vs 2.36 at 265, 2.47 vs 2.48 at 300, then behind: 3.90 vs 3.49 at 500, 5.4 vs 3.7 at 540 of a
+ * 14 M-photon shard. So a sample of the hit points decides per call (SAMPLE pass: mean number of candidates, 2048
+ * warps, kRadiusDenseMean), both kernels are launched and the one that is not wanted returns at once. A hit point
+ * whose block is wider than 2 * kThreadMaxH + 1 cells is appended to heavy_list and left to k_grid_radius. */
 template <bool SAMPLE, bool PREMUL>
 __global__ void __launch_bounds__(256)
 k_grid_radius_thread(const GridView g, const float4* __restrict__ color4, const float* __restrict__ q, const float* __restrict__ brdf,
@@ -995,8 +1189,8 @@ k_grid_radius_thread(const GridView g, const float4* __restrict__ color4, const 
       if (xa > xb) continue;
       const size_t base = ((size_t)rz * g.ny + ry) * g.nx;
       const int st = (int)__ldg(g.cell_start + base + xa), en = (int)__ldg(g.cell_start + base + xb + 1);
-      if (SAMPLE) { scanned += en - st; continue; }
-      for (int j = st; j < en; j++) {
+      if (SAMPLE) scanned += en - st;
+      else for (int j = st; j < en; j++) {
         const float4 p = __ldg(g.pts + j);
         const float d2 = pmk::dist2(p.x, p.y, p.z, qx, qy, qz);
         if (d2 < R2) {
@@ -1345,13 +1539,17 @@ int radius_query(pm_ctx* ctx, const pm_map* map, const float* q, const float* br
     PM_CHECK(ctx->get_scratch(pm::S_FAST1, (size_t)nq, &heavy_list));
     PM_CHECK(ctx->get_scratch(pm::S_FAST2, (size_t)1, &pick));
     PM_CUDA(cudaMemsetAsync(pick, 0, sizeof(RadiusPick), ctx->stream));
+    ctx->ho_count_dev = &pick->heavy; /* reported as the call's hand-over count */
     const int stride = std::max(1, nq / kRadiusSamples);
     const unsigned sgrid = (unsigned)div_up(div_up(nq, stride) * 32, 256), tgrid = (unsigned)div_up(nq, 256);
+    const unsigned ggrid = (unsigned)std::min<int64_t>(div_up(div_up(nq, kGroup), kWarps), cap);
     if (map->cells_only) {
       k_grid_radius_thread<true, true><<<sgrid, 256, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, stride, nullptr,
                                                                        nullptr, nullptr, pick);
       k_grid_radius_thread<false, true><<<tgrid, 256, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, 1, out_flux,
                                                                         out_count, heavy_list, pick);
+      k_grid_radius_group<true><<<ggrid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, max_h, out_flux,
+                                                                       out_count, heavy_list, pick);
       k_grid_radius<true><<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, heavy_list, pick,
                                                                           max_h, out_flux, out_count, fb_list, fb_count);
     } else {
@@ -1359,10 +1557,12 @@ int radius_query(pm_ctx* ctx, const pm_map* map, const float* q, const float* br
                                                                         nullptr, nullptr, pick);
       k_grid_radius_thread<false, false><<<tgrid, 256, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, 1, out_flux,
                                                                          out_count, heavy_list, pick);
+      k_grid_radius_group<false><<<ggrid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, max_h, out_flux,
+                                                                        out_count, heavy_list, pick);
       k_grid_radius<false><<<(unsigned)grid, kWarps * 32, 0, ctx->stream>>>(g, map->color4, q, brdf, radius2, order, nq, heavy_list, pick,
                                                                            max_h, out_flux, out_count, fb_list, fb_count);
     }
-    ctx->launches += 2;
+    ctx->launches += 3;
     if (map->cells_only) { ctx->launches++; PM_CUDA(cudaGetLastError()); return PM_OK; }
     if (kd_grid > ctx->sm_count * 2) kd_grid = ctx->sm_count * 2;
     k_kd_radius<<<(unsigned)kd_grid, 128, 0, ctx->stream>>>(map->nodes4, map->color4, (int)map->n, q, brdf, radius2, nq, fb_list,
