@@ -768,7 +768,7 @@ __device__ __forceinline__ void add_flux(const float4 c, float& sr, float& sg, f
 constexpr int kMaxHRadius = 48;
 constexpr int kThreadMaxH = 6;
 constexpr int kRadiusSamples = 2048;
-constexpr int kRadiusDenseMean = 300; /* mean candidates per sampled hit point from which the group kernel is faster */
+constexpr int kRadiusDenseMean = 200; /* mean candidates per sampled hit point from which the group kernel is faster */
 struct RadiusPick { int candidates, lit, heavy; };
 __device__ __forceinline__ bool radius_dense(const RadiusPick* pick) {
   return pick->candidates > kRadiusDenseMean * max(pick->lit, 1);
@@ -939,7 +939,8 @@ k_grid_radius(const GridView g, const float4* __restrict__ color4, const float* 
  * one load and one round of bookkeeping per kGroup tests. Same candidates and more (a superset of every member's
  * rows), same distance arithmetic and comparison: counts are unchanged. A group that is not compact (its union
  * block holds more than twice the cells of its largest member's: a scanline or bin boundary in the order), or
- * that has a member no block covers, is appended to heavy_list for k_grid_radius. */
+ * that has a member no block covers, is appended to heavy_list for k_grid_radius (1 .. 4 % of the C5 hit points).
+ * C5 frame, one GPU, 29 M photons, 2800 per ball: 13.0 ms against 27.8 ms for one warp per hit point. */
 constexpr int kGroup = 4;
 struct __align__(16) GroupScratch {
   uint2 words[kWords];
@@ -1018,15 +1019,20 @@ k_grid_radius_group(const GridView g, const float4* __restrict__ color4, const f
       R2[m] = (litmask >> m) & 1u ? r2m : -1.f; /* a miss accepts nothing */
       sr[m] = sg[m] = sb[m] = 0.f; cnt[m] = 0;
     }
-    auto test = [&](const float4 p, const bool valid) {
+    /* candidate at position `at` of the cell-ordered arrays. In a cells-only map (PREMUL) the colour sits at the
+     * same position, so both loads are issued together; in a full map the colour is looked up by node id. */
+    auto test = [&](const int at, const bool valid) {
+      const float4 p = __ldg(g.pts + at);
+      float4 c;
+      if (PREMUL) c = __ldg(color4 + at);
       bool ps[kGroup], any = false;
 #pragma unroll
       for (int m = 0; m < kGroup; m++) {
         ps[m] = valid && pmk::dist2(p.x, p.y, p.z, qx[m], qy[m], qz[m]) < R2[m];
         any = any || ps[m];
       }
-      if (any) {
-        const float4 c = __ldg(color4 + __float_as_int(p.w));
+      if (PREMUL || any) {
+        if (!PREMUL) c = __ldg(color4 + __float_as_int(p.w));
 #pragma unroll
         for (int m = 0; m < kGroup; m++)
           if (ps[m]) { add_flux<PREMUL>(c, sr[m], sg[m], sb[m]); cnt[m]++; }
@@ -1073,7 +1079,8 @@ k_grid_radius_group(const GridView g, const float4* __restrict__ color4, const f
           const int r = __ffs(rows_left) - 1;
           rows_left &= rows_left - 1;
           const int rs = __shfl_sync(0xffffffffu, st, r), rl = __shfl_sync(0xffffffffu, len, r);
-          for (int j = lane; j < rl; j += 32) test(__ldg(g.pts + (rs + j)), true);
+#pragma unroll 4
+          for (int j = lane; j < rl; j += 32) test(rs + j, true);
         }
         continue;
       }
@@ -1089,11 +1096,12 @@ k_grid_radius_group(const GridView g, const float4* __restrict__ color4, const f
         for (int i = (P + 31) >> 5; i * 32 < P + len; i++) ws.words[i].y = (unsigned)d;
       }
       __syncwarp();
+#pragma unroll 2
       for (int i = 0; i * 32 < mc; i++) {
         const int j = i * 32 + lane;
         const uint2 w = ws.words[i];
         const int run = (int)w.y + __popc(w.x & le_not0);
-        test(__ldg(g.pts + (ws.run_off[run] + min(j, mc - 1))), j < mc);
+        test(ws.run_off[run] + min(j, mc - 1), j < mc);
       }
     }
 #pragma unroll
@@ -1127,8 +1135,8 @@ k_grid_radius_group(const GridView g, const float4* __restrict__ color4, const f
  * even a warp per group spends most of its instructions on set-up, scans and reductions. Here every thread walks
  * the ball-trimmed rows of its own hit point (same row bounds as k_grid_radius, so the same candidates);
  * neighbouring hit points of the sorted list share their rows through L1. Measured on the C5 hit points (B200,
- * candidates = photons in the trimmed rows, per lit hit point; group kernel second): 1.45 vs 1.87 ms at 170
- * candidates, 2.28 vs 2.36 at 265, 2.47 vs 2.48 at 300, then behind: 3.90 vs 3.49 at 500, 5.4 vs 3.7 at 540 of a
+ * candidates = photons in the trimmed rows, per lit hit point; group kernel second): 1.45 vs 1.6 ms at 170
+ * candidates, then behind: 2.29 vs 2.09 at 265, 2.49 vs 2.13 at 300, 3.90 vs 3.04 at 500, 5.4 vs 3.2 at 540 of a
  * 14 M-photon shard. So a sample of the hit points decides per call (SAMPLE pass: mean number of candidates, 2048
  * warps, kRadiusDenseMean), both kernels are launched and the one that is not wanted returns at once. A hit point
  * whose block is wider than 2 * kThreadMaxH + 1 cells is appended to heavy_list and left to k_grid_radius. */
