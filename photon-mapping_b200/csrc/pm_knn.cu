@@ -14,6 +14,7 @@
  * pm_grid.cu (uniform grid, one warp per query) and pm_kdwarp.cu (warp-cooperative kd-tree walk).
  */
 #include <cfloat>
+#include <cub/cub.cuh>
 #include "pm_knn.cuh"
 
 namespace {
@@ -39,9 +40,7 @@ struct Box6 { float lo[3]; float inv[3]; };
  * scatter (the atomic's return value is the slot inside the bin). The order inside a bin is whatever the atomics
  * hand out; results do not depend on it. */
 constexpr int kQBitsMax = 7;
-constexpr int kQBinsMax = (1 << (3 * kQBitsMax)) + 1;
 constexpr int kScanTile = 2048;                       /* counters per CTA of the scan: 256 threads x 8 */
-constexpr int kScanTilesMax = (kQBinsMax + kScanTile - 1) / kScanTile;
 
 __device__ __forceinline__ uint32_t bin_of(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int i,
                                            const Box6& box, int bits) {
@@ -194,6 +193,44 @@ int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float
   PM_CUDA(cudaGetLastError());
   *perm_out = perm;
   if (sq_out) *sq_out = sq;
+  return PM_OK;
+}
+
+/* The same Morton-bin order, but STABLE (input order inside a bin): a radix sort of (bin, index) pairs over the bits
+ * in use. pm_gather_radius needs it: its group kernel sums a hit point's flux in an order that depends on which
+ * neighbours share its warp, so the order of the list has to be a function of the input alone for the result to be
+ * reproducible bit for bit — and input order inside a bin is raster order, which is what makes neighbours neighbours. */
+__global__ void k_qbin_codes(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int nq, Box6 box, int bits,
+                             uint32_t* __restrict__ codes, int* __restrict__ iota) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  codes[i] = bin_of(q, skip_if_not_positive, i, box, bits);
+  iota[i] = i;
+}
+
+int sort_queries_stable(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float* brdf_dev, int nq, int** perm_out) {
+  uint32_t *codes, *codes_sorted; int *iota, *perm;
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)nq, &codes));
+  PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)nq, &codes_sorted));
+  PM_CHECK(ctx->get_scratch(pm::S_VALS0, (size_t)nq, &iota));
+  PM_CHECK(ctx->get_scratch(pm::S_PERM, (size_t)nq, &perm));
+  int bits = 4;
+  while (bits < kQBitsMax && ((int64_t)1 << (3 * bits)) * 4 < nq) bits++;
+  Box6 box;
+  for (int d = 0; d < 3; d++) {
+    box.lo[d] = map->bounds[d];
+    const float w = map->bounds[3 + d] - map->bounds[d];
+    box.inv[d] = w > 0.f ? (float)(1 << bits) / w : 0.f;
+  }
+  k_qbin_codes<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, bits, codes, iota);
+  size_t tb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, codes, codes_sorted, iota, perm, nq, 0, 3 * bits + 1, ctx->stream);
+  void* tmp = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_CUB, tb, &tmp));
+  PM_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, codes, codes_sorted, iota, perm, nq, 0, 3 * bits + 1, ctx->stream));
+  ctx->launches += 1 + (3 * bits + 1 + 7) / 8 + 2;
+  PM_CUDA(cudaGetLastError());
+  *perm_out = perm;
   return PM_OK;
 }
 
@@ -488,7 +525,7 @@ int pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const flo
     PM_CUDA(cudaMemsetAsync(oc.dev, 0, sizeof(int32_t) * (size_t)nq, ctx->stream));
   } else {
     int* perm = nullptr;
-    PM_CHECK(sort_queries(ctx, map, (const float*)h_dev, (const float*)b_dev, (int)nq, &perm, nullptr));
+    PM_CHECK(sort_queries_stable(ctx, map, (const float*)h_dev, (const float*)b_dev, (int)nq, &perm));
     int *fb_list = nullptr, *fb_count = nullptr;
     PM_CHECK(ctx->get_scratch(pm::S_MISC1, (size_t)nq, &fb_list));
     PM_CHECK(ctx->get_scratch(pm::S_MISC2, (size_t)4, &fb_count));
