@@ -260,6 +260,17 @@ int  pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* br
  * out_count[i] = their number. Hit points with brdf <= 0 or radius2 <= 0 yield zeros. Host or device pointers. */
 int  pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, const float* radius2,
                       int64_t nq, float* out_flux, int32_t* out_count);
+/* A progressive render gathers at the SAME hit points every pass. pm_gather_radius orders the hit points spatially
+ * on every call (a stable sort by Morton bin: neighbouring pixels end up in one warp); pm_hit_order_create does it
+ * once — bins inside the bounding box of the hit points with brdf > 0 — and pm_gather_radius_ordered reuses the
+ * order, with any map and any radii, as long as hit/brdf/nq are the arrays the order was made from. Same results as
+ * pm_gather_radius up to the summation order of the flux (counts are identical); the same order gives the same
+ * bits on every call. Host or device pointers. */
+typedef struct pm_hit_order pm_hit_order;
+int  pm_hit_order_create(pm_ctx* ctx, const float* hit, const float* brdf, int64_t nq, pm_hit_order** out);
+void pm_hit_order_destroy(pm_hit_order* order);
+int  pm_gather_radius_ordered(pm_ctx* ctx, const pm_map* map, const pm_hit_order* order, const float* hit,
+                              const float* brdf, const float* radius2, int64_t nq, float* out_flux, int32_t* out_count);
 
 /* render (≙ simpleRayGen launch): fb is W*H RGBA8, rows as the reference writes them
  * (row H - py; row 0 stays 0, the reference's out-of-bounds row H is not written).

@@ -108,6 +108,9 @@ _SIGNATURES = {
     "pm_knn": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "pm_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p]),
     "pm_gather_radius": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "pm_hit_order_create": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "pm_hit_order_destroy": (None, [c_void_p]),
+    "pm_gather_radius_ordered": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "pm_view_photons": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int,
                                 c_void_p]),
     "pm_view_matrix": (None, [c_void_p, c_void_p, c_void_p, c_float, c_int, c_int, c_void_p]),
@@ -408,8 +411,32 @@ class PhotonMap:
         return out_rgb
 
 
-def _gather_radius(self, hit, brdf, radius2, out_flux=None, out_count=None):
-    """pm_gather_radius: (flux[nq,3], count[nq]) for per-point squared radii (one progressive pass)."""
+class HitOrder:
+    """pm_hit_order: the spatial order of a fixed set of hit points, made once and reused by every progressive pass
+    (`PhotonMap.gather_radius(..., order=...)` with the same hit / brdf arrays)."""
+
+    def __init__(self, ctx: "Context", hit, brdf):
+        self.ctx, self.nq = ctx, _count(hit, 12)
+        h = c_void_p()
+        ctx.after_torch(hit, brdf)
+        _check(lib().pm_hit_order_create(ctx.handle, _ptr(hit), _ptr(brdf), self.nq, ctypes.byref(h)))
+        self.handle = h
+
+    def close(self) -> None:
+        if getattr(self, "handle", None):
+            lib().pm_hit_order_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _gather_radius(self, hit, brdf, radius2, out_flux=None, out_count=None, order: "HitOrder | None" = None):
+    """pm_gather_radius / pm_gather_radius_ordered: (flux[nq,3], count[nq]) for per-point squared radii (one
+    progressive pass)."""
     nq = _count(hit, 12)
     if isinstance(hit, np.ndarray):
         out_flux = np.empty((nq, 3), np.float32) if out_flux is None else out_flux
@@ -420,8 +447,12 @@ def _gather_radius(self, hit, brdf, radius2, out_flux=None, out_count=None):
         out_flux = torch.empty((nq, 3), dtype=torch.float32, device=hit.device) if out_flux is None else out_flux
         out_count = torch.empty(nq, dtype=torch.int32, device=hit.device) if out_count is None else out_count
     self.ctx.after_torch(hit, brdf, radius2, out_flux)
-    _check(lib().pm_gather_radius(self.ctx.handle, self.handle, _ptr(hit), _ptr(brdf), _ptr(radius2), nq, _ptr(out_flux),
-                                  _ptr(out_count)))
+    if order is not None:
+        _check(lib().pm_gather_radius_ordered(self.ctx.handle, self.handle, order.handle, _ptr(hit), _ptr(brdf), _ptr(radius2), nq,
+                                              _ptr(out_flux), _ptr(out_count)))
+    else:
+        _check(lib().pm_gather_radius(self.ctx.handle, self.handle, _ptr(hit), _ptr(brdf), _ptr(radius2), nq, _ptr(out_flux),
+                                      _ptr(out_count)))
     return out_flux, out_count
 
 

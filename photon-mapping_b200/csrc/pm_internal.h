@@ -115,6 +115,13 @@ int stage_out_finish(pm_ctx* ctx, const OutStage& st);
 
 }  // namespace pm
 
+/* pm_hit_order_create: a stable spatial order of a fixed set of hit points, reused by every progressive pass */
+struct pm_hit_order {
+  int device = 0;
+  int64_t nq = 0;
+  int* perm = nullptr; /* device, nq indices */
+};
+
 /* the photon map: tree-ordered AoS records (what the reference hands to its kernels) plus the
  * query-side SoA copies this library traverses */
 struct pm_map {

@@ -208,7 +208,8 @@ __global__ void k_qbin_codes(const float* __restrict__ q, const float* __restric
   iota[i] = i;
 }
 
-int sort_queries_stable(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float* brdf_dev, int nq, int** perm_out) {
+int sort_queries_stable(pm_ctx* ctx, const float* bounds /* lo[3], hi[3] */, const float* q_dev, const float* brdf_dev, int nq,
+                        int** perm_out) {
   uint32_t *codes, *codes_sorted; int *iota, *perm;
   PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)nq, &codes));
   PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)nq, &codes_sorted));
@@ -218,8 +219,8 @@ int sort_queries_stable(pm_ctx* ctx, const pm_map* map, const float* q_dev, cons
   while (bits < kQBitsMax && ((int64_t)1 << (3 * bits)) * 4 < nq) bits++;
   Box6 box;
   for (int d = 0; d < 3; d++) {
-    box.lo[d] = map->bounds[d];
-    const float w = map->bounds[3 + d] - map->bounds[d];
+    box.lo[d] = bounds[d];
+    const float w = bounds[3 + d] - bounds[d];
     box.inv[d] = w > 0.f ? (float)(1 << bits) / w : 0.f;
   }
   k_qbin_codes<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, bits, codes, iota);
@@ -232,6 +233,30 @@ int sort_queries_stable(pm_ctx* ctx, const pm_map* map, const float* q_dev, cons
   PM_CUDA(cudaGetLastError());
   *perm_out = perm;
   return PM_OK;
+}
+
+/* bounding box of the hit points that will be evaluated (brdf > 0): ordered-integer min / max */
+__device__ __forceinline__ uint32_t ordered_bits(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__global__ void k_hit_bounds(const float* __restrict__ q, const float* __restrict__ brdf, int nq, uint32_t* __restrict__ out /* lo[3], hi[3] */) {
+  uint32_t lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nq; i += gridDim.x * blockDim.x) {
+    if (!(brdf[i] > 0.f)) continue;
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+      const float v = q[(size_t)i * 3 + d];
+      if (v != v) continue;
+      const uint32_t k = ordered_bits(v);
+      lo[d] = min(lo[d], k); hi[d] = max(hi[d], k);
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    const uint32_t l = __reduce_min_sync(0xffffffffu, lo[d]), h = __reduce_max_sync(0xffffffffu, hi[d]);
+    if ((threadIdx.x & 31) == 0) { atomicMin(out + d, l); atomicMax(out + 3 + d, h); }
+  }
 }
 
 __global__ void k_fill_empty(int64_t total, int32_t* ids, float* d2, float cutoff2) {
@@ -504,8 +529,8 @@ int pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brd
 }
 
 /* fixed-radius gather: one progressive-photon-mapping pass over a set of hit points */
-int pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, const float* radius2, int64_t nq,
-                     float* out_flux, int32_t* out_count) {
+static int gather_radius_impl(pm_ctx* ctx, const pm_map* map, const pm_hit_order* order, const float* hit, const float* brdf,
+                              const float* radius2, int64_t nq, float* out_flux, int32_t* out_count) {
   PM_REQUIRE(ctx, "ctx is NULL");
   PM_REQUIRE(nq >= 0 && nq < ((int64_t)1 << 31), "nq out of range");
   if (nq == 0) return PM_OK;
@@ -525,7 +550,8 @@ int pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const flo
     PM_CUDA(cudaMemsetAsync(oc.dev, 0, sizeof(int32_t) * (size_t)nq, ctx->stream));
   } else {
     int* perm = nullptr;
-    PM_CHECK(sort_queries_stable(ctx, map, (const float*)h_dev, (const float*)b_dev, (int)nq, &perm));
+    if (order) perm = order->perm;
+    else PM_CHECK(sort_queries_stable(ctx, map->bounds, (const float*)h_dev, (const float*)b_dev, (int)nq, &perm));
     int *fb_list = nullptr, *fb_count = nullptr;
     PM_CHECK(ctx->get_scratch(pm::S_MISC1, (size_t)nq, &fb_list));
     PM_CHECK(ctx->get_scratch(pm::S_MISC2, (size_t)4, &fb_count));
@@ -540,6 +566,65 @@ int pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const flo
   PM_CHECK(pm::stage_out_finish(ctx, oc));
   PM_CHECK(finish_stats(ctx, map));
   return PM_OK;
+}
+
+int pm_gather_radius(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, const float* radius2, int64_t nq,
+                     float* out_flux, int32_t* out_count) {
+  return gather_radius_impl(ctx, map, nullptr, hit, brdf, radius2, nq, out_flux, out_count);
+}
+
+int pm_hit_order_create(pm_ctx* ctx, const float* hit, const float* brdf, int64_t nq, pm_hit_order** out) {
+  PM_REQUIRE(ctx && out, "ctx/out is NULL");
+  *out = nullptr;
+  PM_REQUIRE(nq >= 0 && nq < ((int64_t)1 << 31), "nq out of range");
+  if (nq == 0) return PM_OK;
+  PM_REQUIRE(hit && brdf, "hit/brdf is NULL");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  const void *h_dev = nullptr, *b_dev = nullptr;
+  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN0, hit, sizeof(float) * 3 * (size_t)nq, &h_dev));
+  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN1, brdf, sizeof(float) * (size_t)nq, &b_dev));
+  uint32_t* bb = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_MISC3, (size_t)8, &bb));
+  const uint32_t init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+  PM_CUDA(cudaMemcpyAsync(bb, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+  k_hit_bounds<<<(unsigned)std::min<int64_t>(pm::div_up(nq, 256), (int64_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+      (const float*)h_dev, (const float*)b_dev, (int)nq, bb);
+  uint32_t got[6];
+  PM_CUDA(cudaMemcpyAsync(got, bb, sizeof got, cudaMemcpyDeviceToHost, ctx->stream));
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  float bounds[6];
+  for (int d = 0; d < 6; d++) {
+    const uint32_t k = got[d], u = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+    memcpy(&bounds[d], &u, 4);
+  }
+  if (got[0] > got[3]) for (int d = 0; d < 6; d++) bounds[d] = 0.f; /* no hit point is lit: any order will do */
+  int* perm = nullptr;
+  PM_CHECK(sort_queries_stable(ctx, bounds, (const float*)h_dev, (const float*)b_dev, (int)nq, &perm));
+  pm_hit_order* o = new pm_hit_order();
+  o->device = ctx->device; o->nq = nq;
+  if (pm::map_alloc(&o->perm, sizeof(int) * (size_t)nq, ctx->stream) != cudaSuccess) {
+    cudaGetLastError(); delete o; pm::set_error("pm_hit_order_create: out of device memory"); return PM_ERR_NOMEM;
+  }
+  PM_CUDA(cudaMemcpyAsync(o->perm, perm, sizeof(int) * (size_t)nq, cudaMemcpyDeviceToDevice, ctx->stream));
+  PM_CUDA(cudaStreamSynchronize(ctx->stream));
+  ctx->launches++;
+  *out = o;
+  return PM_OK;
+}
+
+void pm_hit_order_destroy(pm_hit_order* order) {
+  if (!order) return;
+  cudaSetDevice(order->device);
+  cudaDeviceSynchronize();
+  pm::map_free(order->perm);
+  delete order;
+}
+
+int pm_gather_radius_ordered(pm_ctx* ctx, const pm_map* map, const pm_hit_order* order, const float* hit, const float* brdf,
+                             const float* radius2, int64_t nq, float* out_flux, int32_t* out_count) {
+  PM_REQUIRE(order || nq == 0, "order is NULL");
+  PM_REQUIRE(!order || (order->nq == nq && ctx && order->device == ctx->device), "order was made for another set of hit points (size or device)");
+  return gather_radius_impl(ctx, map, order, hit, brdf, radius2, nq, out_flux, out_count);
 }
 
 }  // extern "C"

@@ -171,6 +171,7 @@ def run_c5(pkg, ctx, comm, rank, world, W=3840, H=2160, passes=8, per_pass=15_62
     cap = (per_pass // world + len(lights) + 1) * depth
     d40 = torch.empty((cap, 40), dtype=torch.uint8, device=dev)
     g44 = torch.empty((cap, 44), dtype=torch.uint8, device=dev)
+    order = pkg.HitOrder(ctx, pos, brdf)  # the hit points never move: pm_hit_order_create once, reused by every pass
     sample = slice(0, npx, 61)  # the cell size is a speed knob only: a strided sample of the radii is enough
     stats = []
     t_all0 = None
@@ -197,7 +198,7 @@ def run_c5(pkg, ctx, comm, rank, world, W=3840, H=2160, passes=8, per_pass=15_62
         pkg._check(L.pm_photons_to_maps(ctx.handle, d40.data_ptr(), n, None, 0, g44.data_ptr(), None))
         pmap = pkg.PhotonMap.build_cells(ctx, g44[:n], 0.25 * r_med)
         lap()
-        pmap.gather_radius(pos, brdf, r2, out_flux=flux, out_count=count)
+        pmap.gather_radius(pos, brdf, r2, out_flux=flux, out_count=count, order=order)
         gk = ctx.last_kernel_ms
         pmap.close()
         lap()
@@ -209,11 +210,12 @@ def run_c5(pkg, ctx, comm, rank, world, W=3840, H=2160, passes=8, per_pass=15_62
                           "gather_kernels_ms": gk, "update_ms": 1e3 * (t[4] - t[3]), "allreduce_ms": coll_ms.value, "stored": n})
     torch.cuda.synchronize()
     loop_ms = clk.max_over_ranks(1e3 * (time.perf_counter() - t_all0))
+    order.close()
     mean = lambda k: clk.max_over_ranks(float(np.mean([s[k] for s in stats])))
     lit_px = int((N > 0).sum().item())
     res = {"workload": f"C5-like: Cornell box, {W}x{H} hit points, {passes} passes x {per_pass} cast photons (fixed total: strong "
                        f"scaling), r0 {r0}, alpha {alpha}, max_depth {depth}; per pass: sharded emission -> cells-only map of the shard "
-                       "-> pm_gather_radius over all hit points -> pm_ppm_update (all-reduce of 16 B per hit point + update kernel)",
+                       "-> pm_gather_radius_ordered over all hit points (one pm_hit_order for the run) -> pm_ppm_update (all-reduce of 16 B per hit point + update kernel)",
            "ranks": world, "passes": passes, "loop_ms": loop_ms, "pass_ms": loop_ms / passes,
            "cast_photons_per_s": passes * per_pass / (loop_ms * 1e-3), "emit_ms": mean("emit_ms"), "map_ms": mean("map_ms"),
            "gather_ms": mean("gather_ms"), "gather_kernels_ms": mean("gather_kernels_ms"), "update_ms": mean("update_ms"),

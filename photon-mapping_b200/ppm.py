@@ -78,6 +78,7 @@ def progressive_render(pkg, ctx, scene, tri_mesh, mats, lights, camera, width: i
     r2 = np.full(npx, np.float32(r0) * np.float32(r0), np.float32)
     tau = np.zeros((npx, 3), np.float32)
     emitted = 0
+    order = pkg.HitOrder(ctx, pos, brdf)  # the hit points never move: their spatial order is made once
     for p in range(passes):
         g40, n, paths, _ = scene.emit_photons(lights, photons_per_pass, max_depth, False, seed=seed + p,
                                               rng_mode=pkg.RNG_COUNTER, first_photon=rank, photon_stride=world,
@@ -86,13 +87,14 @@ def progressive_render(pkg, ctx, scene, tri_mesh, mats, lights, camera, width: i
         g44, _ = pkg.photons_to_maps(ctx, g40, np.zeros(0, pkg.PHOTON40))
         pmap = pkg.PhotonMap.build(ctx, g44) if len(g44) else None
         if pmap is not None:
-            flux, count = pmap.gather_radius(pos, brdf, r2)
+            flux, count = pmap.gather_radius(pos, brdf, r2, order=order)
             pmap.close()
         else:
             flux, count = np.zeros((npx, 3), np.float32), np.zeros(npx, np.int32)
         if world > 1:
             flux, count = _allreduce(flux, count, group, device)
         ppm_update(N, r2, tau, flux, count, alpha)
+    order.close()
     radiance = (tau / (np.float32(np.pi) * r2[:, None] * np.float32(max(emitted, 1)))).astype(np.float32) * albedo
     return dict(radiance=radiance.reshape(height, width, 3), r2=r2, N=N, tau=tau, emitted=emitted)
 
@@ -141,6 +143,7 @@ def progressive_render_device(pkg, ctx, scene, tri_mesh, mats, lights, camera, w
     a32 = torch.tensor(alpha, dtype=torch.float32, device=dev)
     tiny, one = torch.tensor(1e-30, dtype=torch.float32, device=dev), torch.tensor(1.0, dtype=torch.float32, device=dev)
     emitted = 0
+    order = pkg.HitOrder(ctx, pos, brdf)  # the hit points never move: their spatial order is made once
     torch.cuda.synchronize()
     for p in range(passes):
         t = [time.perf_counter()]
@@ -165,7 +168,7 @@ def progressive_render_device(pkg, ctx, scene, tri_mesh, mats, lights, camera, w
             else:
                 pmap = pkg.PhotonMap.build(ctx, g44[:n])
             lap()
-            pmap.gather_radius(pos, brdf, r2, out_flux=flux, out_count=count)
+            pmap.gather_radius(pos, brdf, r2, out_flux=flux, out_count=count, order=order)
             gk_ms, fallbacks = ctx.last_kernel_ms, ctx.last_fallback_count
             pmap.close()
         else:
