@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(kLocalThreads)
 k_finish_subtrees(int level_first, int j0, int level_count, int n, const int* __restrict__ ord0, const int* __restrict__ ord1,
                   const int* __restrict__ ord2, const float* __restrict__ cx, const float* __restrict__ cy,
                   const float* __restrict__ cz, const float* __restrict__ box_cur, const int* __restrict__ begin_cur,
-                  int* __restrict__ local_of, int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
+                  int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   LocalSmem& sm = *reinterpret_cast<LocalSmem*>(smem_raw);
   using Scan = cub::BlockScan<uint64_t, kLocalThreads>;
@@ -317,21 +317,37 @@ k_finish_subtrees(int level_first, int j0, int level_count, int n, const int* __
   const int m = (int)subtree_size(s0, n);
   const int tid = threadIdx.x;
 
+  /* element id -> local index (its position in list 0) for the other two lists: an open-addressing table in shared
+   * memory, keys in the scan buffer and values in the second list buffer, neither of which is in use yet (2048
+   * slots for at most 1023 keys). It replaces a 4-byte scatter to and two 4-byte gathers from a global array per
+   * element, each a DRAM sector of its own. */
+  int* hkeys = reinterpret_cast<int*>(sm.scanv);
+  uint16_t* hvals = &sm.lst[1][0][0];
+  constexpr int kHashBits = 11, kHashSlots = 1 << kHashBits;
+  static_assert(sizeof(sm.scanv) >= kHashSlots * sizeof(int) && sizeof(sm.lst[1]) >= kHashSlots * sizeof(uint16_t), "hash table space");
+  for (int i = tid; i < kHashSlots; i += kLocalThreads) hkeys[i] = -1;
+  if (tid < 6) sm.box_even[0][tid] = box_cur[(size_t)j * 6 + tid];
+  if (tid == 0) sm.seg_begin[0][0] = 0;
+  __syncthreads();
   for (int i = tid; i < m; i += kLocalThreads) {
     const int e = ord0[begin0 + i];
     sm.gid[i] = e;
     sm.c[0][i] = cx[e]; sm.c[1][i] = cy[e]; sm.c[2][i] = cz[e];
     sm.lst[0][0][i] = (uint16_t)i;
     sm.segid[i] = 0;
-    local_of[e] = i;
+    uint32_t h = ((uint32_t)e * 2654435761u) >> (32 - kHashBits);
+    while (atomicCAS(&hkeys[h], -1, e) != -1) h = (h + 1) & (kHashSlots - 1);
+    hvals[h] = (uint16_t)i;
   }
-  if (tid < 6) sm.box_even[0][tid] = box_cur[(size_t)j * 6 + tid];
-  if (tid == 0) sm.seg_begin[0][0] = 0;
-  __threadfence_block();
   __syncthreads();
   for (int i = tid; i < m; i += kLocalThreads) {
-    sm.lst[0][1][i] = (uint16_t)local_of[ord1[begin0 + i]];
-    sm.lst[0][2][i] = (uint16_t)local_of[ord2[begin0 + i]];
+#pragma unroll
+    for (int d = 1; d < 3; d++) {
+      const int e = (d == 1 ? ord1 : ord2)[begin0 + i];
+      uint32_t h = ((uint32_t)e * 2654435761u) >> (32 - kHashBits);
+      while (hkeys[h] != e) h = (h + 1) & (kHashSlots - 1);
+      sm.lst[0][d][i] = hvals[h];
+    }
   }
   __syncthreads();
 
@@ -527,13 +543,12 @@ static int build_nodes(pm_ctx* ctx, const pm_photon44* src, int n, int rank, int
   const int max_width = (n + 1) / 2 + 1;
   const unsigned ntiles = (unsigned)pm::div_up(n, kTile);
   const size_t status_words = (size_t)num_levels * ntiles + 64; /* per-level tile status words, then the tickets */
-  float* box[2]; int* begin[2]; int *seg[2], *elem_of_node, *local_of; uint8_t* dim_of_node; SegRec* seg_rec;
+  float* box[2]; int* begin[2]; int *seg[2], *elem_of_node; uint8_t* dim_of_node; SegRec* seg_rec;
   unsigned long long* status;
   PM_CHECK(ctx->get_scratch(pm::S_BUILD6, (size_t)max_width * 6, &box[0]));
   PM_CHECK(ctx->get_scratch(pm::S_BUILD7, (size_t)max_width * 6, &box[1]));
   PM_CHECK(ctx->get_scratch(pm::S_BUILD8, (size_t)max_width, &begin[0]));
   PM_CHECK(ctx->get_scratch(pm::S_BUILD9, (size_t)max_width, &begin[1]));
-  PM_CHECK(ctx->get_scratch(pm::S_BUILD10, (size_t)n, &local_of));
   PM_CHECK(ctx->get_scratch(pm::S_BUILD11, (size_t)n * 2, &seg[0]));
   seg[1] = seg[0] + n;
   PM_CHECK(ctx->get_scratch(pm::S_BUILD12, (size_t)n, &elem_of_node));
@@ -583,7 +598,7 @@ static int build_nodes(pm_ctx* ctx, const pm_photon44* src, int n, int rank, int
       if (j1 > j0)
         k_finish_subtrees<<<(unsigned)(j1 - j0), kLocalThreads, sizeof(LocalSmem), st>>>(
             level_first, j0, j1, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
-            local_of, elem_of_node, dim_of_node);
+            elem_of_node, dim_of_node);
       ctx->launches++;
       break;
     }
