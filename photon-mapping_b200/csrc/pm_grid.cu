@@ -1363,12 +1363,9 @@ int cells_reorder(pm_ctx* ctx, pm_map* m) {
   return PM_OK;
 }
 
-/* candidates expected inside the first radius: a k + b (tuning knobs PM_FAST_EK_A / PM_FAST_EK_B, read once) */
-static float fast_expected_count(int k) {
-  static const float a = getenv("PM_FAST_EK_A") ? (float)atof(getenv("PM_FAST_EK_A")) : 1.25f;
-  static const float b = getenv("PM_FAST_EK_B") ? (float)atof(getenv("PM_FAST_EK_B")) : 10.f;
-  return a * (float)k + b;
-}
+/* candidates expected inside the first radius: 1.25 k + 10. Swept on C2 (B200, ms per 1 M-query step): 1.1 k + 10
+ * 0.806, 1.25 k + 10 0.797, 1.25 k + 20 0.803, 1.4 k + 10 0.822, 1.5 k + 16 0.827 — flat around the choice. */
+static float fast_expected_count(int k) { return 1.25f * (float)k + 10.f; }
 
 int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
   const bool given = cell_size > 0.f; /* cells-only map: the caller names the cell, nothing is sampled (there is no tree) */
