@@ -249,6 +249,21 @@ int64_t pm_map_size(const pm_map* map);
 int  pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int k,
             float cutoff_radius, int32_t* out_ids, float* out_dist2, float* out_r2);
 
+/* pm_knn for callers that cannot allocate. NO COUNTERPART IN THE REFERENCE: added
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). Same results as
+ * pm_knn, but the call allocates nothing — no cudaMalloc / cudaFree / pool allocation, no staging: the kernels'
+ * scratch (query order, bin counters, hand-over lists) is a file-scope device array of the library, 12 MiB,
+ * that every GPU which loads the library holds until the process exits. Consequences:
+ *   - queries_dev and every output must be DEVICE memory (host pointers: PM_ERR_INVALID);
+ *   - nq <= PM_KNN_STATIC_MAX_QUERIES, else PM_ERR_CAPACITY (split the batch, or call pm_knn);
+ *   - all calls on a device share the one array: calls that overlap on the GPU (two contexts, two threads) race —
+ *     serialise them. The array keeps the last call's contents; each call clears what it needs at zero itself.
+ * Synchronous on return like pm_knn. The first call on a device looks the array's address up (cudaGetSymbolAddress)
+ * and, like any first launch, loads the kernels: make one call before a region that must not allocate. */
+#define PM_KNN_STATIC_MAX_QUERIES 262144
+int  pm_knn_static(pm_ctx* ctx, const pm_map* map, const float* queries_dev, int64_t nq, int k,
+                   float cutoff_radius, int32_t* out_ids_dev, float* out_dist2_dev, float* out_r2_dev);
+
 /* fused kNN + radiance estimate (≙ gatherPhotons, ray-tracer/cuda/shading.h:93-121).
  * hit: 3*nq, brdf: nq, out_rgb: 3*nq. */
 int  pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, int64_t nq,

@@ -40,6 +40,7 @@ RNG_LCG_PARITY = 0
 RNG_COUNTER = 1
 
 SUPPORTED_K = (8, 16, 32, 50, 64)
+KNN_STATIC_MAX_QUERIES = 262144  # PM_KNN_STATIC_MAX_QUERIES
 
 # every exported symbol of include/pmhot.h: name -> (restype, argtypes)
 _SIGNATURES = {
@@ -106,6 +107,7 @@ _SIGNATURES = {
     "pm_map_destroy": (None, [c_void_p]),
     "pm_map_size": (c_int64, [c_void_p]),
     "pm_knn": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p, c_void_p, c_void_p]),
+    "pm_knn_static": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "pm_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p]),
     "pm_gather_radius": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "pm_hit_order_create": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
@@ -395,6 +397,13 @@ class PhotonMap:
         _check(lib().pm_knn(self.ctx.handle, self.handle, _ptr(queries), nq, k, cutoff, _ptr(out_ids), _ptr(out_dist2),
                             _ptr(out_r2)))
         return out_ids, out_dist2, out_r2
+
+    def knn_static(self, queries, k: int, cutoff: float, out_ids, out_dist2=None, out_r2=None) -> None:
+        """pm_knn_static: pm_knn on CUDA tensors the caller owns, with the library's resident scratch array — the call
+        allocates nothing (no reference counterpart; see pmhot.h). At most KNN_STATIC_MAX_QUERIES queries."""
+        self.ctx.after_torch(queries, out_ids)
+        _check(lib().pm_knn_static(self.ctx.handle, self.handle, _ptr(queries), _count(queries, 12), k, cutoff, _ptr(out_ids),
+                                   _ptr(out_dist2), _ptr(out_r2)))
 
     def gather(self, hit, brdf, k: int = 50, cutoff: float = 100.0, out_rgb=None):
         """≙ gatherPhotons (ray-tracer/cuda/shading.h:93-121). Returns rgb[nq,3]."""

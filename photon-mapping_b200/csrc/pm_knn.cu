@@ -628,3 +628,137 @@ int pm_gather_radius_ordered(pm_ctx* ctx, const pm_map* map, const pm_hit_order*
 }
 
 }  // extern "C"
+
+/* ---- pm_knn_static: pm_knn without any device-memory allocation -----------------------------------------------
+ * No counterpart in the reference; added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). The scratch the query
+ * kernels need — Morton codes, permutation, ordered queries, bin counters, the hand-over lists of k_knn_fast and
+ * k_grid_query — lives in ONE file-scope device array instead of the context's growable cudaMalloc'ed slots.
+ * Every GPU that loads the library holds the array (12.0 MiB) until the process exits. All calls share it: two
+ * calls that overlap on the GPU (two contexts, two host threads) race. Nothing in it has to survive a call; what
+ * must start at zero (bin counters, scan states, list counters) is cleared by the same memsets pm_knn issues. */
+namespace {
+
+constexpr int64_t kStaticMaxQueries = PM_KNN_STATIC_MAX_QUERIES;
+
+/* sort_queries' counter-block size for a batch of nq queries (the same arithmetic, restated for the layout) */
+constexpr size_t static_hist_bytes(int64_t nq) {
+  int bits = 4;
+  while (bits < kQBitsMax && ((int64_t)1 << (3 * bits)) * 4 < nq) bits++;
+  const size_t bins = ((size_t)1 << (3 * bits)) + 1, tiles = (bins + kScanTile - 1) / kScanTile;
+  return ((bins + 3) & ~(size_t)3) * 4 + tiles * 8 + 16;
+}
+constexpr size_t align256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+/* slot -> (offset, bytes) inside the array: exactly the slots run_queries / sort_queries / grid_query ask for */
+struct StaticSlot { int slot; size_t bytes; };
+constexpr StaticSlot kStaticSlots[] = {
+    {pm::S_KEYS0, align256((size_t)kStaticMaxQueries * sizeof(uint32_t))},   /* Morton bin per query */
+    {pm::S_PERM, align256((size_t)kStaticMaxQueries * sizeof(int))},         /* processing order */
+    {pm::S_VALS1, align256((size_t)kStaticMaxQueries * sizeof(float4))},     /* queries in that order */
+    /* bin counters + scan states; x 4: sort_queries asks for that many uint32_t, not bytes */
+    {pm::S_KEYS1, align256(static_hist_bytes(kStaticMaxQueries) * sizeof(uint32_t))},
+    {pm::S_MISC1, align256((size_t)kStaticMaxQueries * sizeof(int))},        /* kd-tree hand-over list */
+    {pm::S_MISC2, 256},                                                      /* ... its counter */
+    {pm::S_FAST1, align256((size_t)kStaticMaxQueries * sizeof(int))},        /* fast-path hand-over list */
+    {pm::S_FAST2, 256},                                                      /* ... its counter */
+};
+constexpr size_t static_total() {
+  size_t t = 0;
+  for (const StaticSlot& s : kStaticSlots) t += s.bytes;
+  return t;
+}
+constexpr size_t kStaticBytes = static_total();
+static_assert(kStaticBytes <= ((size_t)13 << 20), "pm_knn_static: the resident scratch is meant to stay modest");
+
+/* In HOST code this name is only the host-side stand-in of the symbol, not a device address: the address the kernels
+ * get comes from cudaGetSymbolAddress (static_scratch_base). */
+static __device__ __align__(256) unsigned char g_knn_static_scratch[kStaticBytes];
+
+constexpr int kStaticMaxDevices = 64;
+unsigned char* g_static_base[kStaticMaxDevices] = {};
+
+/* device address of the array on the CURRENT device (the caller has made ctx->device current), looked up once per
+ * device */
+int static_scratch_base(int device, unsigned char** out) {
+  if (device < 0 || device >= kStaticMaxDevices) { pm::set_error("pm_knn_static: device %d out of range", device); return PM_ERR_INVALID; }
+  unsigned char* p = __atomic_load_n(&g_static_base[device], __ATOMIC_ACQUIRE);
+  if (!p) {
+    void* sym = nullptr;
+    PM_CUDA(cudaGetSymbolAddress(&sym, g_knn_static_scratch));
+    if (!sym) { pm::set_error("pm_knn_static: cudaGetSymbolAddress returned NULL"); return PM_ERR_CUDA; }
+    p = static_cast<unsigned char*>(sym);
+    __atomic_store_n(&g_static_base[device], p, __ATOMIC_RELEASE); /* every thread computes the same value */
+  }
+  *out = p;
+  return PM_OK;
+}
+
+/* Swaps the context's scratch table for one whose slots point into the static array, for the duration of one call.
+ * A slot the array has no room for is marked (non-NULL pointer, capacity 0) so that pm_ctx::get_scratch fails on it
+ * (it would have to cudaFree an address cudaMalloc never returned) instead of allocating behind the caller's back. */
+struct StaticScratchScope {
+  pm_ctx* ctx;
+  pm::Scratch saved[pm::S_COUNT];
+  StaticScratchScope(pm_ctx* c, unsigned char* base) : ctx(c) {
+    for (int i = 0; i < pm::S_COUNT; i++) {
+      saved[i] = c->scratch[i];
+      c->scratch[i].ptr = base;
+      c->scratch[i].cap = 0;
+    }
+    size_t off = 0;
+    for (const StaticSlot& s : kStaticSlots) {
+      c->scratch[s.slot].ptr = base + off;
+      c->scratch[s.slot].cap = s.bytes;
+      off += s.bytes;
+    }
+  }
+  ~StaticScratchScope() {
+    for (int i = 0; i < pm::S_COUNT; i++) ctx->scratch[i] = saved[i];
+  }
+};
+
+}  // namespace
+
+extern "C" int pm_knn_static(pm_ctx* ctx, const pm_map* map, const float* queries_dev, int64_t nq, int k, float cutoff_radius,
+                             int32_t* out_ids_dev, float* out_dist2_dev, float* out_r2_dev) {
+  PM_REQUIRE(ctx, "ctx is NULL");
+  PM_REQUIRE(!map || !map->cells_only, "this map was built by pm_map_build_cells (no kd-tree): fixed-radius gathers only");
+  PM_REQUIRE(k == 8 || k == 16 || k == 32 || k == 50 || k == 64, "k must be one of 8, 16, 32, 50, 64");
+  PM_REQUIRE(nq >= 0, "nq is negative");
+  if (nq > kStaticMaxQueries) {
+    pm::set_error("pm_knn_static: nq = %lld exceeds PM_KNN_STATIC_MAX_QUERIES = %lld (the resident scratch array is sized for "
+                  "that; split the batch or call pm_knn)", (long long)nq, (long long)kStaticMaxQueries);
+    return PM_ERR_CAPACITY;
+  }
+  if (nq == 0) return PM_OK;
+  PM_REQUIRE(queries_dev && out_ids_dev, "queries/out_ids is NULL");
+  PM_CUDA(cudaSetDevice(ctx->device));
+  /* host buffers would need a staging allocation: refused */
+  PM_REQUIRE(pm::is_device_ptr(queries_dev) && pm::is_device_ptr(out_ids_dev) && (!out_dist2_dev || pm::is_device_ptr(out_dist2_dev)) &&
+                 (!out_r2_dev || pm::is_device_ptr(out_r2_dev)),
+             "queries and outputs must be device memory (this entry point allocates nothing, so it cannot stage host buffers)");
+  PM_REQUIRE(!map || map->device == ctx->device, "the map lives on another device");
+  const float cutoff2 = cutoff_radius * cutoff_radius;
+  if (!map || map->n < 1) {
+    k_fill_empty<<<(unsigned)pm::div_up(nq * k, 256), 256, 0, ctx->stream>>>(nq * k, out_ids_dev, out_dist2_dev, cutoff2);
+    if (out_r2_dev) k_fill_f<<<(unsigned)pm::div_up(nq, 256), 256, 0, ctx->stream>>>(nq, out_r2_dev, cutoff2);
+    ctx->launches += 2;
+    PM_CUDA(cudaGetLastError());
+    ctx->fb_count_dev = nullptr;
+    ctx->ho_count_dev = nullptr;
+    return finish_stats(ctx, map);
+  }
+  unsigned char* base = nullptr;
+  PM_CHECK(static_scratch_base(ctx->device, &base));
+  int r;
+  {
+    StaticScratchScope scope(ctx, base);
+    pmk::QueryIO io;
+    io.q = queries_dev; io.nq = (int)nq; io.k = k; io.cutoff2 = cutoff2;
+    io.ids = out_ids_dev; io.d2 = out_dist2_dev; io.r2 = out_r2_dev;
+    r = run_queries(ctx, map, io, false, true);
+  }
+  if (r != PM_OK) { cudaStreamSynchronize(ctx->stream); return r; }
+  return finish_stats(ctx, map);
+}
