@@ -130,6 +130,11 @@ void pm_ctx_destroy(pm_ctx* ctx) {
     cudaStreamDestroy(ctx->copy_stream);
     for (int i = 0; i < 2; i++) { cudaEventDestroy(ctx->ev_kernel[i]); cudaEventDestroy(ctx->ev_copy[i]); }
   }
+  if (ctx->in_stream) {
+    cudaStreamSynchronize(ctx->in_stream);
+    cudaStreamDestroy(ctx->in_stream);
+    cudaEventDestroy(ctx->ev_in);
+  }
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaEventDestroy(ctx->ev_order);

@@ -81,6 +81,8 @@ struct pm_ctx {
   /* second stream + events for the chunked host-buffer pipeline of pm_knn (created on first use) */
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_kernel[2] = {nullptr, nullptr}, ev_copy[2] = {nullptr, nullptr};
+  cudaStream_t in_stream = nullptr; /* host queries of that pipeline: the other PCIe direction */
+  cudaEvent_t ev_in = nullptr;
   int64_t launches = 0;
   float last_kernel_ms = 0.f;
   int64_t last_fallbacks = 0;      /* queries of the last pm_knn / pm_gather answered by the kd-tree kernel */

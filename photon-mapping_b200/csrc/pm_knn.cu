@@ -366,11 +366,15 @@ int finish_stats(pm_ctx* ctx, const pm_map* map) {
 
 /* pm_knn with HOST output buffers: the batch is cut into chunks so that the device-to-host copy of
  * chunk c (PCIe, the slow part: k * 8 bytes per query) overlaps the kernels of chunk c + 1. Outputs are
- * staged in two alternating device buffers; a chunk's kernels wait for the copy that last used its buffer. */
-constexpr int64_t kPipeChunk = 131072;
+ * staged in two alternating device buffers; a chunk's kernels wait for the copy that last used its buffer.
+ * The first chunks are small (16 Ki queries, doubling up to kPipeChunk): the result copies — which bound the call —
+ * start after ~0.05 ms instead of after a full chunk. Host QUERIES travel the same way: only the first chunk's
+ * queries are copied ahead of its kernels, the rest follow on a third stream (the other PCIe direction) while chunk 0
+ * is being answered. */
+constexpr int64_t kPipeChunk = 131072, kPipeFirstChunk = 16384;
 
-int knn_pipelined(pm_ctx* ctx, const pm_map* map, const float* q_dev, int64_t nq, int k, float cutoff2, int32_t* out_ids,
-                  float* out_d2, float* out_r2) {
+int knn_pipelined(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float* q_host, int64_t nq, int k, float cutoff2,
+                  int32_t* out_ids, float* out_d2, float* out_r2) {
   if (!ctx->copy_stream) {
     PM_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
     for (int i = 0; i < 2; i++) {
@@ -378,15 +382,32 @@ int knn_pipelined(pm_ctx* ctx, const pm_map* map, const float* q_dev, int64_t nq
       PM_CUDA(cudaEventCreateWithFlags(&ctx->ev_copy[i], cudaEventDisableTiming));
     }
   }
+  if (q_host && !ctx->in_stream) {
+    PM_CUDA(cudaStreamCreateWithFlags(&ctx->in_stream, cudaStreamNonBlocking));
+    PM_CUDA(cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming));
+  }
   int32_t* s_ids = nullptr; float *s_d2 = nullptr, *s_r2 = nullptr;
   PM_CHECK(ctx->get_scratch(pm::S_STAGE_OUT0, (size_t)(2 * kPipeChunk * k), &s_ids));
   if (out_d2) PM_CHECK(ctx->get_scratch(pm::S_STAGE_OUT1, (size_t)(2 * kPipeChunk * k), &s_d2));
   if (out_r2) PM_CHECK(ctx->get_scratch(pm::S_STAGE_OUT2, (size_t)(2 * kPipeChunk), &s_r2));
   PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   int c = 0;
-  for (int64_t b = 0; b < nq; b += kPipeChunk, c++) {
-    const int64_t cnt = nq - b < kPipeChunk ? nq - b : kPipeChunk;
+  int64_t size = kPipeFirstChunk;
+  for (int64_t b = 0; b < nq; b += size, size = std::min<int64_t>(2 * size, kPipeChunk), c++) {
+    const int64_t cnt = std::min<int64_t>(nq - b, size);
     const int buf = c & 1;
+    if (q_host) {
+      float* qd = const_cast<float*>(q_dev);
+      if (c == 0) {
+        PM_CUDA(cudaMemcpyAsync(qd, q_host, sizeof(float) * 3 * (size_t)cnt, cudaMemcpyHostToDevice, ctx->stream));
+        if (cnt < nq) {
+          PM_CUDA(cudaMemcpyAsync(qd + 3 * cnt, q_host + 3 * cnt, sizeof(float) * 3 * (size_t)(nq - cnt), cudaMemcpyHostToDevice, ctx->in_stream));
+          PM_CUDA(cudaEventRecord(ctx->ev_in, ctx->in_stream));
+        }
+      } else if (c == 1) {
+        PM_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_in, 0));
+      }
+    }
     if (c >= 2) PM_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_copy[buf], 0));
     pmk::QueryIO io;
     io.q = q_dev + 3 * b; io.nq = (int)cnt; io.k = k; io.cutoff2 = cutoff2;
@@ -480,13 +501,20 @@ int pm_knn(pm_ctx* ctx, const pm_map* map, const float* queries, int64_t nq, int
   PM_CUDA(cudaSetDevice(ctx->device));
   const float cutoff2 = cutoff_radius * cutoff_radius;
   const void* q_dev = nullptr;
-  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN0, queries, sizeof(float) * 3 * (size_t)nq, &q_dev));
   if (map && map->n >= 1 && nq >= 2 * kPipeChunk && !pm::is_device_ptr(out_ids) && !pm::is_device_ptr(out_dist2) &&
       !pm::is_device_ptr(out_r2)) {
-    PM_CHECK(knn_pipelined(ctx, map, (const float*)q_dev, nq, k, cutoff2, out_ids, out_dist2, out_r2));
+    const float* q_host = nullptr;
+    if (pm::is_device_ptr(queries)) q_dev = queries;
+    else { /* host queries are copied chunk-wise by the pipeline itself */
+      float* d = nullptr;
+      PM_CHECK(ctx->get_scratch(pm::S_STAGE_IN0, (size_t)nq * 3, &d));
+      q_dev = d; q_host = queries;
+    }
+    PM_CHECK(knn_pipelined(ctx, map, (const float*)q_dev, q_host, nq, k, cutoff2, out_ids, out_dist2, out_r2));
     PM_CHECK(finish_stats(ctx, map));
     return PM_OK;
   }
+  PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN0, queries, sizeof(float) * 3 * (size_t)nq, &q_dev));
   pm::OutStage o_ids, o_d2, o_r2;
   PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT0, out_ids, sizeof(int32_t) * (size_t)k * nq, &o_ids));
   PM_CHECK(pm::stage_out(ctx, pm::S_STAGE_OUT1, out_dist2, sizeof(float) * (size_t)k * nq, &o_d2));
