@@ -472,7 +472,7 @@ constexpr int kFastMaxScan = kFastWords * 32; /* retry on a 7- or 9-cell-wide bl
 constexpr int kFastPairs = 6;                 /* steps taken two at a time by the unrolled part of the scan (a 5x5x5 block needs ~8) */
 constexpr int kFastMaxH = 4;                  /* widest block of the fast path: 9x9 rows (3 rounds) */
 constexpr int kFastAttempts = 6;
-constexpr int kFastProbes = 8;                /* interpolated counting probes per query ... */
+constexpr int kFastProbes = 10;               /* interpolated counting probes per query ... */
 constexpr int kFastBisect = 28;               /* ... then bisection steps, before it is handed over */
 
 struct __align__(16) FastScratch {
@@ -669,31 +669,38 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
     {
       float Tlo = 0.f, Thi = R2, T = n == k ? R2 : R2 * fp.win[n]; /* every candidate has dist² < R2 */
       int clo = 0, chi = n;
-      /* up to kFastProbes interpolated probes (3.5 on average), then plain bisection of what is left of the bracket: the
-       * interpolation stalls now and then (regula falsi: one end of the bracket stops moving), and handing such a query
-       * to k_grid_query costs a kernel of its own — 1 590 of 1 M queries and 29 us on C2. Only a real tie at the k-th
-       * place (no float between the bracket's ends) still leaves here without a threshold. */
 #pragma unroll 1
-      for (int it = 0; it < kFastProbes + kFastBisect; it++) {
+      for (int it = 0; it < kFastProbes; it++) {
         const uint32_t tb = __float_as_uint(T);
         int c = (kv[0].x <= tb) + (kv[1].x <= tb) + (kv[2].x <= tb) + (kv[3].x <= tb); /* an unused slot is +inf */
         c = __reduce_add_sync(0xffffffffu, c);
-        if (c == k) {
-          uint32_t m = 0u;
-#pragma unroll
-          for (int s = 0; s < kSlots; s++) m = max(m, kv[s].x <= tb ? kv[s].x : 0u);
-          tau = __reduce_max_sync(0xffffffffu, m); /* the k-th smallest itself */
-          exact = true;
-          break;
-        }
+        if (c == k) { exact = true; break; }
         if (c < k) { Tlo = T; clo = c; } else { Thi = T; chi = c; }
-        if (it < kFastProbes) T = Tlo + (Thi - Tlo) * ((float)(k - clo) * rcp_approx((float)(chi - clo))); /* clo < k < chi */
-        else T = 0.5f * (Tlo + Thi);
-        if (!(T > Tlo && T < Thi)) {
-          if (it >= kFastProbes) break; /* no value left between the bracket's ends */
-          it = kFastProbes - 1; T = 0.5f * (Tlo + Thi); /* degenerate interpolation step: go on bisecting */
+        T = Tlo + (Thi - Tlo) * ((float)(k - clo) * rcp_approx((float)(chi - clo))); /* clo < k < chi */
+        if (!(T > Tlo && T < Thi)) break; /* degenerate step */
+      }
+      /* the interpolation stalls now and then (regula falsi: one end of the bracket stops moving) or steps onto an end
+       * of the bracket; what is left of the bracket is then bisected. Handing such a query to k_grid_query instead
+       * cost a kernel of its own: 1 590 of 1 M queries and 29 us on C2. Only a real tie at the k-th place (no float
+       * between the bracket's ends) still leaves here without a threshold. */
+      if (!exact) {
+#pragma unroll 1
+        for (int it = 0; it < kFastBisect; it++) {
+          T = 0.5f * (Tlo + Thi);
           if (!(T > Tlo && T < Thi)) break;
+          const uint32_t tb = __float_as_uint(T);
+          int c = (kv[0].x <= tb) + (kv[1].x <= tb) + (kv[2].x <= tb) + (kv[3].x <= tb);
+          c = __reduce_add_sync(0xffffffffu, c);
+          if (c == k) { exact = true; break; }
+          if (c < k) Tlo = T; else Thi = T;
         }
+      }
+      if (exact) { /* the k-th smallest itself */
+        const uint32_t tb = __float_as_uint(T);
+        uint32_t m = 0u;
+#pragma unroll
+        for (int s = 0; s < kSlots; s++) m = max(m, kv[s].x <= tb ? kv[s].x : 0u);
+        tau = __reduce_max_sync(0xffffffffu, m);
       }
     }
     if (!exact) { /* equal distances at the k-th place (the id order decides), or an odd distribution */
