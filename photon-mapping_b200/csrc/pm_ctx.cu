@@ -135,6 +135,7 @@ void pm_ctx_destroy(pm_ctx* ctx) {
     cudaStreamDestroy(ctx->in_stream);
     cudaEventDestroy(ctx->ev_in);
   }
+  for (cudaEvent_t e : ctx->pipe_events) cudaEventDestroy(e);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaEventDestroy(ctx->ev_order);

@@ -83,6 +83,7 @@ struct pm_ctx {
   cudaEvent_t ev_kernel[2] = {nullptr, nullptr}, ev_copy[2] = {nullptr, nullptr};
   cudaStream_t in_stream = nullptr; /* host queries of that pipeline: the other PCIe direction */
   cudaEvent_t ev_in = nullptr;
+  std::vector<cudaEvent_t> pipe_events; /* pm_gather's host-buffer pipeline: two per chunk */
   int64_t launches = 0;
   float last_kernel_ms = 0.f;
   int64_t last_fallbacks = 0;      /* queries of the last pm_knn / pm_gather answered by the kd-tree kernel */

@@ -471,6 +471,59 @@ int gather_device(pm_ctx* ctx, const pm_map* map, const float* hit_dev, const fl
 
 }  // namespace pm
 
+/* pm_gather with HOST buffers on both sides (16 B in, 12 B out per query): the three legs — queries in, kernels,
+ * colours out — run on three streams chunk by chunk, so the call costs about what its
+ * slowest leg costs instead of their sum. The staging buffers hold the whole batch: no buffer is reused inside a call. */
+/* few, large chunks: a chunk costs about ten launches on the host, and here the kernels are the slowest leg */
+constexpr int64_t kGatherFirstChunk = 65536, kGatherChunk = 262144;
+static int gather_pipelined(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brdf, int64_t nq, int k, float cutoff,
+                            float* out_rgb) {
+  if (!ctx->copy_stream) {
+    PM_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) {
+      PM_CUDA(cudaEventCreateWithFlags(&ctx->ev_kernel[i], cudaEventDisableTiming));
+      PM_CUDA(cudaEventCreateWithFlags(&ctx->ev_copy[i], cudaEventDisableTiming));
+    }
+  }
+  if (!ctx->in_stream) {
+    PM_CUDA(cudaStreamCreateWithFlags(&ctx->in_stream, cudaStreamNonBlocking));
+    PM_CUDA(cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming));
+  }
+  float *h_dev = nullptr, *b_dev = nullptr, *rgb_dev = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_STAGE_IN0, (size_t)nq * 3, &h_dev));
+  PM_CHECK(ctx->get_scratch(pm::S_STAGE_IN1, (size_t)nq, &b_dev));
+  PM_CHECK(ctx->get_scratch(pm::S_STAGE_OUT0, (size_t)nq * 3, &rgb_dev));
+  size_t chunks = 0;
+  for (int64_t b = 0, size = kGatherFirstChunk; b < nq; b += size, size = kGatherChunk) chunks++;
+  while (ctx->pipe_events.size() < 2 * chunks) {
+    cudaEvent_t e;
+    PM_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    ctx->pipe_events.push_back(e);
+  }
+  /* leg 1: every chunk's inputs, in order, on the input stream */
+  size_t c = 0;
+  for (int64_t b = 0, size = kGatherFirstChunk; b < nq; b += size, size = kGatherChunk, c++) {
+    const int64_t cnt = std::min<int64_t>(nq - b, size);
+    PM_CUDA(cudaMemcpyAsync(h_dev + 3 * b, hit + 3 * b, sizeof(float) * 3 * (size_t)cnt, cudaMemcpyHostToDevice, ctx->in_stream));
+    PM_CUDA(cudaMemcpyAsync(b_dev + b, brdf + b, sizeof(float) * (size_t)cnt, cudaMemcpyHostToDevice, ctx->in_stream));
+    PM_CUDA(cudaEventRecord(ctx->pipe_events[2 * c], ctx->in_stream));
+  }
+  /* legs 2 and 3 */
+  PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+  c = 0;
+  for (int64_t b = 0, size = kGatherFirstChunk; b < nq; b += size, size = kGatherChunk, c++) {
+    const int64_t cnt = std::min<int64_t>(nq - b, size);
+    PM_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->pipe_events[2 * c], 0));
+    PM_CHECK(pm::gather_device(ctx, map, h_dev + 3 * b, b_dev + b, cnt, k, cutoff, rgb_dev + 3 * b, false));
+    PM_CUDA(cudaEventRecord(ctx->pipe_events[2 * c + 1], ctx->stream));
+    PM_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->pipe_events[2 * c + 1], 0));
+    PM_CUDA(cudaMemcpyAsync(out_rgb + 3 * b, rgb_dev + 3 * b, sizeof(float) * 3 * (size_t)cnt, cudaMemcpyDeviceToHost, ctx->copy_stream));
+  }
+  PM_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  PM_CUDA(cudaStreamSynchronize(ctx->copy_stream));
+  return PM_OK;
+}
+
 extern "C" {
 
 int pm_selftest_math(pm_ctx* ctx, int64_t n, uint32_t seed, int64_t* mismatches, int64_t* accepted, int64_t* rejected) {
@@ -545,6 +598,11 @@ int pm_gather(pm_ctx* ctx, const pm_map* map, const float* hit, const float* brd
   if (nq == 0) return PM_OK;
   PM_REQUIRE(hit && brdf && out_rgb, "hit/brdf/out_rgb is NULL");
   PM_CUDA(cudaSetDevice(ctx->device));
+  if (map && map->n >= 1 && nq >= 2 * kPipeChunk && !pm::is_device_ptr(hit) && !pm::is_device_ptr(brdf) && !pm::is_device_ptr(out_rgb)) {
+    PM_CHECK(gather_pipelined(ctx, map, hit, brdf, nq, k, cutoff_radius, out_rgb));
+    PM_CHECK(finish_stats(ctx, map));
+    return PM_OK;
+  }
   const void *h_dev = nullptr, *b_dev = nullptr;
   PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN0, hit, sizeof(float) * 3 * (size_t)nq, &h_dev));
   PM_CHECK(pm::stage_in(ctx, pm::S_STAGE_IN1, brdf, sizeof(float) * (size_t)nq, &b_dev));
