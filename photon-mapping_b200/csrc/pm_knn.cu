@@ -55,16 +55,23 @@ __device__ __forceinline__ uint32_t bin_of(const float* __restrict__ q, const fl
   return code;
 }
 
-__global__ void k_qbin_count(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int nq, Box6 box, int bits,
-                             uint32_t* __restrict__ codes, uint32_t* __restrict__ hist) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool in = i < nq;
-  const uint32_t code = in ? bin_of(q, skip_if_not_positive, i, box, bits) : 0u;
-  if (in) codes[i] = code;
-  const bool last = in && code == 1u << (3 * bits);
-  const unsigned lb = __ballot_sync(0xffffffffu, last);
-  if (last) { if ((threadIdx.x & 31) == __ffs(lb) - 1) atomicAdd(hist + code, (uint32_t)__popc(lb)); }
-  else if (in) atomicAdd(hist + code, 1u);
+/* kQItems queries per thread (striped: coalesced): the atomics of a thread are independent, so several are in flight */
+constexpr int kQItems = 4;
+
+__global__ void __launch_bounds__(256)
+k_qbin_count(const float* __restrict__ q, const float* __restrict__ skip_if_not_positive, int nq, Box6 box, int bits,
+             uint32_t* __restrict__ codes, uint32_t* __restrict__ hist) {
+#pragma unroll
+  for (int it = 0; it < kQItems; it++) {
+    const int i = (blockIdx.x * kQItems + it) * blockDim.x + threadIdx.x;
+    const bool in = i < nq;
+    const uint32_t code = in ? bin_of(q, skip_if_not_positive, i, box, bits) : 0u;
+    if (in) codes[i] = code;
+    const bool last = in && code == 1u << (3 * bits);
+    const unsigned lb = __ballot_sync(0xffffffffu, last);
+    if (last) { if ((threadIdx.x & 31) == __ffs(lb) - 1) atomicAdd(hist + code, (uint32_t)__popc(lb)); }
+    else if (in) atomicAdd(hist + code, 1u);
+  }
 }
 
 /* in place: counts -> exclusive offsets. status[t] = flag << 32 | value with flag 1 = the tile's own sum, 2 = the
@@ -139,24 +146,35 @@ k_qbin_scan(uint32_t* __restrict__ hist, int nbins, unsigned long long* __restri
   }
 }
 
-__global__ void k_qbin_scatter(const float* __restrict__ q, const uint32_t* __restrict__ codes, int nq, int bits,
-                               uint32_t* __restrict__ cursor, int* __restrict__ perm, float4* __restrict__ sq) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool in = i < nq;
-  const uint32_t code = in ? codes[i] : 0u;
-  const bool last = in && code == 1u << (3 * bits);
-  const unsigned lb = __ballot_sync(0xffffffffu, last);
-  uint32_t pos = 0;
-  if (last) {
-    const int leader = __ffs(lb) - 1;
-    if ((threadIdx.x & 31) == leader) pos = atomicAdd(cursor + code, (uint32_t)__popc(lb));
-    pos = __shfl_sync(lb, pos, leader) + __popc(lb & ((1u << (threadIdx.x & 31)) - 1u));
-  } else if (in) {
-    pos = atomicAdd(cursor + code, 1u);
+__global__ void __launch_bounds__(256)
+k_qbin_scatter(const float* __restrict__ q, const uint32_t* __restrict__ codes, int nq, int bits,
+               uint32_t* __restrict__ cursor, int* __restrict__ perm, float4* __restrict__ sq) {
+  uint32_t pos[kQItems];
+  float qx[kQItems], qy[kQItems], qz[kQItems];
+#pragma unroll
+  for (int it = 0; it < kQItems; it++) {
+    const int i = (blockIdx.x * kQItems + it) * blockDim.x + threadIdx.x;
+    const bool in = i < nq;
+    const uint32_t code = in ? codes[i] : 0u;
+    const bool last = in && code == 1u << (3 * bits);
+    const unsigned lb = __ballot_sync(0xffffffffu, last);
+    pos[it] = 0u;
+    if (last) {
+      const int leader = __ffs(lb) - 1;
+      if ((threadIdx.x & 31) == leader) pos[it] = atomicAdd(cursor + code, (uint32_t)__popc(lb));
+      pos[it] = __shfl_sync(lb, pos[it], leader) + __popc(lb & ((1u << (threadIdx.x & 31)) - 1u));
+    } else if (in) {
+      pos[it] = atomicAdd(cursor + code, 1u);
+    }
+    if (in && sq) { qx[it] = q[(size_t)i * 3 + 0]; qy[it] = q[(size_t)i * 3 + 1]; qz[it] = q[(size_t)i * 3 + 2]; }
   }
-  if (in) {
-    perm[pos] = i;
-    if (sq) sq[pos] = make_float4(q[(size_t)i * 3 + 0], q[(size_t)i * 3 + 1], q[(size_t)i * 3 + 2], __int_as_float(i));
+#pragma unroll
+  for (int it = 0; it < kQItems; it++) {
+    const int i = (blockIdx.x * kQItems + it) * blockDim.x + threadIdx.x;
+    if (i < nq) {
+      if (perm) perm[pos[it]] = i;
+      if (sq) sq[pos[it]] = make_float4(qx[it], qy[it], qz[it], __int_as_float(i));
+    }
   }
 }
 
@@ -185,10 +203,11 @@ int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float
     const float w = map->bounds[3 + d] - map->bounds[d];
     box.inv[d] = w > 0.f ? (float)(1 << bits) / w : 0.f;
   }
-  const unsigned grid = (unsigned)pm::div_up(nq, 256);
+  const unsigned grid = (unsigned)pm::div_up(nq, 256 * kQItems);
   k_qbin_count<<<grid, 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, bits, codes, hist);
   k_qbin_scan<<<tiles, 256, 0, ctx->stream>>>(hist, bins, status, tile_counter);
-  k_qbin_scatter<<<grid, 256, 0, ctx->stream>>>(q_dev, codes, nq, bits, hist, perm, sq);
+  /* the fast path reads the ordered queries themselves (sq) and nothing else reads the permutation then */
+  k_qbin_scatter<<<grid, 256, 0, ctx->stream>>>(q_dev, codes, nq, bits, hist, sq ? nullptr : perm, sq);
   ctx->launches += 3;
   PM_CUDA(cudaGetLastError());
   *perm_out = perm;
@@ -331,7 +350,7 @@ int run_queries(pm_ctx* ctx, const pm_map* map, pmk::QueryIO io, bool gather, bo
   int* perm = nullptr;
   float4* sq = nullptr;
   PM_CHECK(sort_queries(ctx, map, io.q, gather ? io.brdf : nullptr, io.nq, &perm, map->fast_path ? &sq : nullptr));
-  io.order = perm;
+  io.order = sq ? nullptr : perm; /* with sq the permutation is not written (sort_queries) */
   io.sq = sq;
   ctx->fb_count_dev = nullptr;
   ctx->ho_count_dev = nullptr;
