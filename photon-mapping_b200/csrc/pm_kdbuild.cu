@@ -331,6 +331,7 @@ struct LocalSmem {
   uint64_t scanv[kLocalCap + 1];
   uint16_t lst[2][3][kLocalCap + 1];
   uint16_t segid[kLocalCap + 1];
+  uint8_t side_el[kLocalCap + 1];   /* side of every element on the current level: 0 left, 1 right, 2 pivot */
   float box_even[kLocalSegs / 2][6]; /* boxes of even local levels (<= 256 nodes at level 8) */
   float box_odd[kLocalSegs / 4][6];  /* odd local levels (<= 128 at level 7); level 9 keeps only its split axis */
   uint8_t last_dim[kLocalSegs];
@@ -445,6 +446,19 @@ k_finish_subtrees(int level_first, int j0, int level_count, int n, const int* __
      * order (ordered key, input index) against the pivot, which is the same decision */
     uint64_t f[kLocalItems], ex[kLocalItems];
     uint32_t sides[kLocalItems]; /* 2 bits per list, and the segment id above them */
+    /* the side of every ELEMENT, from its position in the list sorted along its segment's split axis (no key is
+     * compared: left of the pivot position = smaller in (coordinate, input index) order) ... */
+#pragma unroll
+    for (int it = 0; it < kLocalItems; it++) {
+      const int i = tid * kLocalItems + it;
+      if (i >= m) continue;
+      const uint16_t sg = sm.segid[i];
+      if (sg == kDead16) continue;
+      const int piv = sm.seg_pivot[sg];
+      sm.side_el[sm.lst[cur][sm.seg_dim[sg]][i]] = (uint8_t)(i < piv ? 0 : (i > piv ? 1 : 2));
+    }
+    __syncthreads();
+    /* ... which the other two lists look up by element */
 #pragma unroll
     for (int it = 0; it < kLocalItems; it++) {
       const int i = tid * kLocalItems + it;
@@ -453,20 +467,11 @@ k_finish_subtrees(int level_first, int j0, int level_count, int n, const int* __
       const uint16_t sg = sm.segid[i]; /* position i is only ever touched by this thread */
       if (sg == kDead16) continue;
       const int piv = sm.seg_pivot[sg], dim = sm.seg_dim[sg];
-      const int pe = sm.lst[cur][dim][piv];
-      const uint32_t pk = ordered_key(sm.c[dim][pe]);
-      const int pg = sm.gid[pe];
       sm.segid[i] = i < piv ? (uint16_t)(2 * sg) : (i > piv ? (uint16_t)(2 * sg + 1) : kDead16);
       uint32_t pack = (uint32_t)sg << 8;
 #pragma unroll
       for (int d = 0; d < 3; d++) {
-        uint32_t sd;
-        if (d == dim) sd = i < piv ? 0u : (i > piv ? 1u : 2u);
-        else {
-          const int el = sm.lst[cur][d][i];
-          const uint32_t k = ordered_key(sm.c[dim][el]);
-          sd = el == pe ? 2u : ((k < pk || (k == pk && sm.gid[el] < pg)) ? 0u : 1u);
-        }
+        const uint32_t sd = d == dim ? (i < piv ? 0u : (i > piv ? 1u : 2u)) : (uint32_t)sm.side_el[sm.lst[cur][d][i]];
         pack |= sd << (2 * d);
         if (sd < 2u) f[it] += 1ull << (20 * d + 10 * (int)sd);
       }
