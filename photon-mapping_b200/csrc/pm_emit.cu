@@ -54,8 +54,13 @@ __device__ __forceinline__ void store40(pm_photon40* dst, vec3 pos, vec3 dir, ve
 
 /* fewer traversing lanes than this: leave the traversal loop so that finished lanes can shade and pick up their
  * next segment (or a new path) instead of idling until the slowest ray of the warp is done */
+constexpr int kVoteMinTris = 4096;  /* scenes above this (the Morton-built hierarchies) walk with the vote-driven traversal */
 constexpr int kMinTraceLanes = 28; /* swept 0..31 on B200: 24-31 within 1 %, 0 (never leave) 8-25 % slower */
 
+/* WARP_VOTE: the vote-driven traversal of pm_scene.cuh (large scenes: twice the lanes per instruction on the
+ * 1 M-triangle room, 49 -> 43 ms per 16 M paths) instead of the free-running while-while loop (small scenes: the Cornell
+ * box walks 1.7x faster with it — its rays are a handful of steps long and the votes cost more than the idle lanes) */
+template <bool WARP_VOTE>
 __global__ void __launch_bounds__(128)
 k_walk(const EmitParams P, unsigned long long* __restrict__ next_path, pm_photon40* __restrict__ slots,
        int* __restrict__ counts, unsigned long long* __restrict__ segments) {
@@ -69,11 +74,11 @@ k_walk(const EmitParams P, unsigned long long* __restrict__ next_path, pm_photon
   unsigned long long my_segments = 0;
   bool exhausted = false;
   TraceState st;
-  st.node = kNoChild; st.sp = 0;
+  st.node = kNoChild; st.sp = 0; st.pend = 0;
   while (true) {
     /* 1. lanes whose traversal has finished: optixTrace returned -> triangleMeshClosestHit / miss
      *    (deviceCode.cu:74-136), then shootPhoton / shootCausticsPhoton (deviceCode.cu:25-52) */
-    if (active && st.node == kNoChild) {
+    if (active && st.node == kNoChild && st.pend == 0) {
       const Hit h = st.best;
       int ev = EV_MISS;
       vec3 s_org = org, s_dir = dir, s_col = color;
@@ -143,7 +148,8 @@ k_walk(const EmitParams P, unsigned long long* __restrict__ next_path, pm_photon
     }
     if (!__any_sync(0xffffffffu, active)) break;
     /* 3. traversal of the segments in flight (lanes without one have st.node == kNoChild and pass through) */
-    if (active) trace_advance<false>(P.sc, st, org, dir, PMD_EPS, 1e30f, P.min_lanes);
+    if (WARP_VOTE) trace_advance_warp<false>(P.sc, st, org, dir, PMD_EPS, 1e30f, P.min_lanes);
+    else if (active) trace_advance<false>(P.sc, st, org, dir, PMD_EPS, 1e30f, P.min_lanes);
   }
   /* one atomic per warp */
   for (int o = 16; o > 0; o >>= 1) my_segments += __shfl_xor_sync(0xffffffffu, my_segments, o);
@@ -260,7 +266,8 @@ static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights,
   P.max_depth = max_depth; P.caustics = caustics_mode ? 1 : 0; P.rng_mode = rng_mode; P.seed = seed;
   P.first_photon = first_photon; P.photon_stride = photon_stride;
   P.slots_per_path = max_depth > 1 ? max_depth - 1 : 1;
-  P.min_lanes = getenv("PM_WALK_MIN_LANES") ? atoi(getenv("PM_WALK_MIN_LANES")) : kMinTraceLanes;
+  P.min_lanes = kMinTraceLanes;
+  const bool vote = scene->nt > kVoteMinTris;
   if (n_paths) *n_paths = total_paths;
   if (total_paths == 0) return PM_OK;
   PM_REQUIRE(scene->nt == 0 || scene->mats, "scene has triangles but no materials");
@@ -294,7 +301,8 @@ static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights,
   for (int l = 0; l <= n_lights; l++) ki.light_first[l] = P.light_first[l];
   ki.first_photon = first_photon; ki.photon_stride = photon_stride;
   int blocks_per_sm = 0;
-  PM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_walk, 128, 0));
+  if (vote) PM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_walk<true>, 128, 0));
+  else PM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_walk<false>, 128, 0));
   if (blocks_per_sm < 1) blocks_per_sm = 1;
   int64_t written = 0; /* records produced so far (may exceed capacity) */
   float ms_total = 0.f;
@@ -305,7 +313,8 @@ static int emit_impl(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights,
     int64_t grid = (int64_t)ctx->sm_count * blocks_per_sm;
     if (grid > pm::div_up(nb, 128)) grid = pm::div_up(nb, 128);
     PM_CUDA(cudaEventRecord(ctx->ev0, st));
-    k_walk<<<(unsigned)grid, 128, 0, st>>>(P, ctrs, slots, counts, ctrs + 1);
+    if (vote) k_walk<true><<<(unsigned)grid, 128, 0, st>>>(P, ctrs, slots, counts, ctrs + 1);
+    else k_walk<false><<<(unsigned)grid, 128, 0, st>>>(P, ctrs, slots, counts, ctrs + 1);
     PM_CUDA(cudaEventRecord(ctx->ev1, st));
     PM_CUDA(cudaGetLastError());
     {

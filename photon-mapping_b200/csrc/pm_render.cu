@@ -186,15 +186,19 @@ k_vertex(Chunk c, SceneView sc, Lights L, float sky_r, float sky_g, float sky_b)
   }
 }
 
+/* WARP_VOTE: the final-gather rays of a large scene are traced with the vote-driven traversal (pm_scene.cuh): every
+ * lane of the warp stays until the trace is done, lanes without a ray included */
+template <bool WARP_VOTE>
 __global__ void __launch_bounds__(128)
 k_fg(Chunk c, SceneView sc) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= (int64_t)c.count * kFG) return;
-  if (!(c.gq_brdf[t] > 0.f)) return;
-  const int i = (int)(t / kFG);
-  const vec3 org = v3(c.cq_hit + 3 * (size_t)i);
-  const vec3 dir = v3(c.gq_hit + 3 * (size_t)t);
-  const Hit h = trace<false>(sc, org, dir, 3 * PMD_EPS, PMD_INFTY);
+  const bool valid = t < (int64_t)c.count * kFG && c.gq_brdf[t] > 0.f;
+  if (!WARP_VOTE && !valid) return;
+  const int i = valid ? (int)(t / kFG) : 0;
+  const vec3 org = valid ? v3(c.cq_hit + 3 * (size_t)i) : v3(0.f, 0.f, 0.f);
+  const vec3 dir = valid ? v3(c.gq_hit + 3 * (size_t)t) : v3(0.f, 0.f, 1.f);
+  const Hit h = WARP_VOTE ? trace_warp<false>(sc, valid, org, dir, 3 * PMD_EPS, PMD_INFTY) : trace<false>(sc, org, dir, 3 * PMD_EPS, PMD_INFTY);
+  if (!valid) return;
   if (h.prim < 0) { c.gq_brdf[t] = -1.f; return; } /* quirk iii: a missed sample contributes nothing */
   const pm_material m = sc.mats[slot_mesh(sc, h.slot)];
   if (!(m.diffuse > 0.f)) { c.gq_brdf[t] = -1.f; return; }
@@ -330,7 +334,8 @@ int pm_render_rgb(pm_ctx* ctx, const pm_scene* scene, const pm_light* lights, in
         ctx->launches++;
         for (int d = 0; d < depth; d++) {
           k_vertex<<<nb, 128, 0, st>>>(c, sv, L, sky[0], sky[1], sky[2]);
-          k_fg<<<(unsigned)pm::div_up((int64_t)c.count * kFG, 128), 128, 0, st>>>(c, sv);
+          if (scene->nt > 4096) k_fg<true><<<(unsigned)pm::div_up((int64_t)c.count * kFG, 128), 128, 0, st>>>(c, sv);
+          else k_fg<false><<<(unsigned)pm::div_up((int64_t)c.count * kFG, 128), 128, 0, st>>>(c, sv);
           ctx->launches += 2;
           PM_CUDA(cudaGetLastError());
           PM_CHECK(pm::gather_device(ctx, caustic_map, c.cq_hit, c.cq_brdf, c.count, kK, kCutoff, c.cq_out, false));

@@ -303,7 +303,7 @@ int pm_scene_create(pm_ctx* ctx, const float* verts_host, int nv, const int32_t*
     PM_SC(cudaMemcpyAsync(s->tris, rec, sizeof(float4) * 3, cudaMemcpyDeviceToDevice, st));
     k_single<<<1, 1, 0, st>>>(tri_box, pad, s->nodes);
     ctx->launches++;
-  } else if (nt <= kSahMaxTris && !getenv("PM_SCENE_LBVH")) {
+  } else if (nt <= kSahMaxTris) {
     std::vector<float> tbox((size_t)nt * 6);
     for (int i = 0; i < nt; i++)
       for (int d = 0; d < 3; d++) {
