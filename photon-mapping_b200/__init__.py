@@ -100,6 +100,7 @@ _SIGNATURES = {
                               POINTER(c_float)]),
     "pm_photons_to_maps": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "pm_map_build": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, POINTER(c_void_p)]),
+    "pm_test_build_carry_from": (None, [c_int64]),
     "pm_map_from_tree": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_void_p)]),
     "pm_map_build_shard": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "pm_map_build_finish": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, POINTER(c_void_p)]),

@@ -148,24 +148,41 @@ __global__ void k_split(int level_first, int j0, int level_count, int n, const i
  * subtree record -> two coordinate gathers), and the fixed cost of a tile (ticket, three barriers, look-back) is paid
  * once per 1 024 positions. With one position per thread (round 1 .. r2l) the kernel ran at 22 % of the DRAM rate, 34 % of
  * L2 and IPC 1.5 at 95 % occupancy: bound by those per-tile latencies, not by any unit. */
-constexpr int kLvThreads = 256, kLvItems = 4, kLvWarps = kLvThreads / 32;
-constexpr int kTile = kLvThreads * kLvItems; /* tile-local counts <= 1 024 fit the 11-bit fields below */
-constexpr int kLvParts = kLvItems * kLvWarps; /* warp totals of a tile in scan order: stripe-major */
-static_assert(kLvParts == 32, "one warp scans the warp totals");
+constexpr int kLvThreads = 256, kLvWarps = kLvThreads / 32;
+constexpr int kLvItems = 4;       /* lists of element ids only: 1 024 positions per tile */
+/* measured on B200 (tools/time_build.py, whole build): 20 M 15.7 vs 14.6 ms, 30 M 23.4 vs 22.2, 50 M 40.8 vs 41.0,
+ * 100 M 84.3 vs 100.5 with / without carried keys */
+constexpr int64_t kCarryMinPhotons = (int64_t)1 << 26;
+int64_t g_carry_min_photons = kCarryMinPhotons; /* pm_test_build_carry_from */
+constexpr int kLvItemsCarry = 2;  /* lists that carry their keys (below): 36 instead of 12 bytes per position in registers */
 constexpr uint64_t kStInvalid = 0ull, kStAgg = 1ull << 62, kStPrefix = 2ull << 62, kStMask = 3ull << 62;
 
 __device__ inline uint64_t tile_to_global(uint64_t x) { /* 4 x 11-bit tile-local fields -> L0 | P0<<30 | L1<<31 | P1<<61 */
   return (x & 0x7ffull) | (((x >> 11) & 0x7ffull) << 30) | (((x >> 22) & 0x7ffull) << 31) | (((x >> 33) & 0x7ffull) << 61);
 }
 
-__global__ void __launch_bounds__(kLvThreads, 4)
+/* CARRY: every entry of the list sorted along axis d carries, next to the element id, the element's ordered keys
+ * along the other two axes ((d+1)%3 in ka, (d+2)%3 in kb). The side of an element is then decided from what the pass
+ * streams anyway; without them it takes a 4-byte gather of the element's coordinate per list — free while the
+ * coordinate arrays sit in L2 (10 M photons: 120 MB), a 64-byte DRAM access each once they do not (100 M photons:
+ * 181 bytes of DRAM traffic per position and level, 3.5 ms per level; with the keys 80 bytes, all of it streamed). */
+struct CarriedKeys {
+  const uint32_t* ka_in[3]; const uint32_t* kb_in[3];
+  uint32_t* ka_out[3]; uint32_t* kb_out[3];
+};
+
+template <bool CARRY, int ITEMS>
+__global__ void __launch_bounds__(kLvThreads, CARRY ? 3 : 4)
 k_level(int n, int pos_lo, int pos_hi, int tile0, int level_first, const int* __restrict__ seg_of_pos, const SegRec* __restrict__ seg_rec,
         const int* __restrict__ in0, const int* __restrict__ in1, const int* __restrict__ in2,
         const float* __restrict__ c0, const float* __restrict__ c1, const float* __restrict__ c2,
         int* __restrict__ out0, int* __restrict__ out1, int* __restrict__ out2, int* __restrict__ seg_next,
-        unsigned long long* __restrict__ status, unsigned int* __restrict__ ticket) {
-  __shared__ uint64_t scanv[kTile];
-  __shared__ uint64_t warp_tot[kLvParts];
+        unsigned long long* __restrict__ status, unsigned int* __restrict__ ticket, const CarriedKeys ck) {
+  constexpr int kTileT = kLvThreads * ITEMS;   /* tile-local counts <= 1 024 fit the 11-bit fields */
+  constexpr int kParts = ITEMS * kLvWarps;     /* warp totals of a tile in scan order: stripe-major */
+  static_assert(kParts <= 32 && kTileT <= 1024, "one warp scans the warp totals; 11-bit fields");
+  __shared__ uint64_t scanv[kTileT];
+  __shared__ uint64_t warp_tot[32];
   __shared__ uint64_t carry_sh;
   __shared__ int tile_sh, last_head_sh, first_is_head_sh;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -174,21 +191,28 @@ k_level(int n, int pos_lo, int pos_hi, int tile0, int level_first, const int* __
   /* a sharded build passes only over [pos_lo, pos_hi) — the range of the rank's own subtree, which starts with a
    * range begin, so its first tile never looks back; positions outside are other ranks' and count as dead */
   const int tile = tile_sh;
-  const int tile_base = (tile0 + tile) * kTile;
+  const int tile_base = (tile0 + tile) * kTileT;
 
-  int s[kLvItems], e0[kLvItems], e1[kLvItems], e2[kLvItems];
+  int s[ITEMS], e0[ITEMS], e1[ITEMS], e2[ITEMS];
+  uint32_t ka[CARRY ? ITEMS : 1][3], kb[CARRY ? ITEMS : 1][3];
 #pragma unroll
-  for (int it = 0; it < kLvItems; it++) {
+  for (int it = 0; it < ITEMS; it++) {
     const int i = tile_base + it * kLvThreads + tid;
     s[it] = kDead; e0[it] = e1[it] = e2[it] = 0;
-    if (i >= pos_lo && i < pos_hi) { s[it] = seg_of_pos[i]; e0[it] = in0[i]; e1[it] = in1[i]; e2[it] = in2[i]; }
+    if (i >= pos_lo && i < pos_hi) {
+      s[it] = seg_of_pos[i]; e0[it] = in0[i]; e1[it] = in1[i]; e2[it] = in2[i];
+      if (CARRY) {
+#pragma unroll
+        for (int d = 0; d < 3; d++) { ka[it][d] = ck.ka_in[d][i]; kb[it][d] = ck.kb_in[d][i]; }
+      }
+    }
   }
   /* per position: side of the element in slot 0 (bits 0-1) and slot 1 (bits 2-3); 2 = it is the pivot */
-  uint32_t sides[kLvItems];
-  uint64_t f[kLvItems];
+  uint32_t sides[ITEMS];
+  uint64_t f[ITEMS];
   int my_last_head = -1;
 #pragma unroll
-  for (int it = 0; it < kLvItems; it++) {
+  for (int it = 0; it < ITEMS; it++) {
     const int i = tile_base + it * kLvThreads + tid;
     f[it] = 0ull; sides[it] = 0xau;
     bool head = true; /* a dead slot restarts the scan like a range begin */
@@ -196,12 +220,19 @@ k_level(int n, int pos_lo, int pos_hi, int tile0, int level_first, const int* __
       const int4 rec = *reinterpret_cast<const int4*>(seg_rec + (s[it] - level_first));
       const int pivot = rec.x & 0x3fffffff, dim = (int)((uint32_t)rec.x >> 30), begin = rec.y;
       const uint2 pk = make_uint2((uint32_t)rec.z, (uint32_t)rec.w);
-      const float* c = dim == 0 ? c0 : (dim == 1 ? c1 : c2);
       const uint32_t ea = (uint32_t)(dim == 0 ? e1[it] : (dim == 1 ? e2[it] : e0[it]));
       const uint32_t eb = (uint32_t)(dim == 0 ? e2[it] : (dim == 1 ? e0[it] : e1[it]));
-      const uint32_t ka = ordered_key(c[ea]), kb = ordered_key(c[eb]);
-      const uint32_t sd_a = ea == pk.y ? 2u : ((ka < pk.x || (ka == pk.x && ea < pk.y)) ? 0u : 1u);
-      const uint32_t sd_b = eb == pk.y ? 2u : ((kb < pk.x || (kb == pk.x && eb < pk.y)) ? 0u : 1u);
+      uint32_t key_a, key_b; /* the two elements' keys along the split axis */
+      if (CARRY) {
+        /* slot 0 is list (dim+1)%3, whose kb is axis dim; slot 1 is list (dim+2)%3, whose ka is axis dim */
+        key_a = dim == 0 ? kb[it][1] : (dim == 1 ? kb[it][2] : kb[it][0]);
+        key_b = dim == 0 ? ka[it][2] : (dim == 1 ? ka[it][0] : ka[it][1]);
+      } else {
+        const float* c = dim == 0 ? c0 : (dim == 1 ? c1 : c2);
+        key_a = ordered_key(c[ea]); key_b = ordered_key(c[eb]);
+      }
+      const uint32_t sd_a = ea == pk.y ? 2u : ((key_a < pk.x || (key_a == pk.x && ea < pk.y)) ? 0u : 1u);
+      const uint32_t sd_b = eb == pk.y ? 2u : ((key_b < pk.x || (key_b == pk.x && eb < pk.y)) ? 0u : 1u);
       seg_next[i] = i < pivot ? 2 * s[it] + 1 : (i > pivot ? 2 * s[it] + 2 : kDead);
       f[it] = (sd_a == 0u ? 1ull : (sd_a == 2u ? 1ull << 11 : 0ull)) + (sd_b == 0u ? 1ull << 22 : (sd_b == 2u ? 1ull << 33 : 0ull));
       sides[it] = sd_a | (sd_b << 2);
@@ -218,9 +249,9 @@ k_level(int n, int pos_lo, int pos_hi, int tile0, int level_first, const int* __
   }
 
   /* exclusive scan of f over the tile in position order: stripe by stripe, warp by warp */
-  uint64_t inc[kLvItems];
+  uint64_t inc[ITEMS];
 #pragma unroll
-  for (int it = 0; it < kLvItems; it++) {
+  for (int it = 0; it < ITEMS; it++) {
     uint64_t v = f[it];
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -232,23 +263,23 @@ k_level(int n, int pos_lo, int pos_hi, int tile0, int level_first, const int* __
   }
   __syncthreads();
   if (wid == 0) {
-    uint64_t w = warp_tot[lane];
+    uint64_t w = lane < kParts ? warp_tot[lane] : 0ull;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
+    for (int o = 1; o < kParts; o <<= 1) {
       const uint64_t v = __shfl_up_sync(0xffffffffu, w, o);
       if (lane >= o) w += v;
     }
-    warp_tot[lane] = w; /* inclusive over the 32 parts */
+    if (lane < kParts) warp_tot[lane] = w; /* inclusive over the parts */
   }
   __syncthreads();
-  uint64_t ex[kLvItems];
+  uint64_t ex[ITEMS];
 #pragma unroll
-  for (int it = 0; it < kLvItems; it++) {
+  for (int it = 0; it < ITEMS; it++) {
     const int part = it * kLvWarps + wid;
     ex[it] = inc[it] - f[it] + (part ? warp_tot[part - 1] : 0ull);
     scanv[it * kLvThreads + tid] = ex[it];
   }
-  const uint64_t total = warp_tot[kLvParts - 1];
+  const uint64_t total = warp_tot[kParts - 1];
   const int last_head = last_head_sh;
   const bool need_carry = !first_is_head_sh;
   __syncthreads();
@@ -288,7 +319,7 @@ k_level(int n, int pos_lo, int pos_hi, int tile0, int level_first, const int* __
   if (need_carry) __syncthreads();
 
 #pragma unroll
-  for (int it = 0; it < kLvItems; it++) {
+  for (int it = 0; it < ITEMS; it++) {
     if (s[it] == kDead) continue;
     const int i = tile_base + it * kLvThreads + tid;
     const int4 rec = *reinterpret_cast<const int4*>(seg_rec + (s[it] - level_first)); /* again: an L1 hit, four registers less */
@@ -307,10 +338,29 @@ k_level(int n, int pos_lo, int pos_hi, int tile0, int level_first, const int* __
     const int off = i - begin;
     const int dst_a = sd_a == 0u ? begin + (int)La : (sd_a == 1u ? pivot + 1 + (off - (int)La - (int)Pa) : pivot);
     const int dst_b = sd_b == 0u ? begin + (int)Lb : (sd_b == 1u ? pivot + 1 + (off - (int)Lb - (int)Pb) : pivot);
-    if (dim == 0) { out0[i] = e0[it]; out1[dst_a] = e1[it]; out2[dst_b] = e2[it]; }
-    else if (dim == 1) { out1[i] = e1[it]; out2[dst_a] = e2[it]; out0[dst_b] = e0[it]; }
-    else { out2[i] = e2[it]; out0[dst_a] = e0[it]; out1[dst_b] = e1[it]; }
+    /* list dim stays in place, list (dim+1)%3 goes to dst_a, list (dim+2)%3 to dst_b */
+    const int d0 = dim == 0 ? i : (dim == 1 ? dst_b : dst_a);
+    const int d1 = dim == 1 ? i : (dim == 2 ? dst_b : dst_a);
+    const int d2 = dim == 2 ? i : (dim == 0 ? dst_b : dst_a);
+    out0[d0] = e0[it]; out1[d1] = e1[it]; out2[d2] = e2[it];
+    if (CARRY) {
+      ck.ka_out[0][d0] = ka[it][0]; ck.kb_out[0][d0] = kb[it][0];
+      ck.ka_out[1][d1] = ka[it][1]; ck.kb_out[1][d1] = kb[it][1];
+      ck.ka_out[2][d2] = ka[it][2]; ck.kb_out[2][d2] = kb[it][2];
+    }
   }
+}
+
+/* the carried keys of the freshly sorted lists: one gather per list entry and key, once */
+__global__ void k_carry_init(int n, const int* __restrict__ ord0, const uint32_t* __restrict__ keys /* kx | ky | kz */,
+                             uint32_t* __restrict__ ka0, uint32_t* __restrict__ kb0) {
+  /* ord0 / ka0 / kb0 are the bases of 3 n entries: list d at d * n */
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= 3 * (int64_t)n) return;
+  const int d = (int)(t / n);
+  const int e = ord0[t];
+  ka0[t] = keys[(size_t)((d + 1) % 3) * n + e];
+  kb0[t] = keys[(size_t)((d + 2) % 3) * n + e];
 }
 
 /* ---- the last kLocalLevels levels: one CTA per subtree, everything in shared memory ----------
@@ -584,6 +634,17 @@ static int build_nodes(pm_ctx* ctx, const pm_photon44* src, int n, int rank, int
   /* per-level state */
   const int num_levels = 32 - __builtin_clz((unsigned)n);  /* floor(log2 n) + 1 */
   const int max_width = (n + 1) / 2 + 1;
+  /* lists that carry their keys from kCarryMinPhotons on (see k_level) */
+  const bool carry = n >= g_carry_min_photons;
+  const int kTile = kLvThreads * (carry ? kLvItemsCarry : kLvItems);
+  uint32_t *key_a[2] = {nullptr, nullptr}, *key_b[2] = {nullptr, nullptr};
+  if (carry) {
+    PM_CHECK(ctx->get_scratch(pm::S_BUILD17, (size_t)n * 6, &key_a[0]));
+    PM_CHECK(ctx->get_scratch(pm::S_BUILD18, (size_t)n * 6, &key_b[0]));
+    key_a[1] = key_a[0] + 3 * (size_t)n; key_b[1] = key_b[0] + 3 * (size_t)n;
+    k_carry_init<<<(unsigned)pm::div_up(3 * (int64_t)n, 256), 256, 0, st>>>(n, ord[0][0], keys_in, key_a[0], key_b[0]);
+    ctx->launches++;
+  }
   const unsigned ntiles = (unsigned)pm::div_up(n, kTile);
   const size_t status_words = (size_t)num_levels * ntiles + 64; /* per-level tile status words, then the tickets */
   float* box[2]; int* begin[2]; int *seg[2], *elem_of_node; uint8_t* dim_of_node; SegRec* seg_rec;
@@ -655,10 +716,22 @@ static int build_nodes(pm_ctx* ctx, const pm_photon44* src, int n, int rank, int
     const int lo = part ? pos_lo : 0, hi = part ? pos_hi : n;
     const int tile0 = lo / kTile;
     const unsigned tiles = (unsigned)(pm::div_up(hi, kTile) - tile0);
-    if (hi > lo)
-      k_level<<<tiles, kLvThreads, 0, st>>>(n, lo, hi, tile0, level_first, seg[L & 1], seg_rec, ord[cur][0], ord[cur][1], ord[cur][2], cx,
-                                      cy, cz, ord[cur ^ 1][0], ord[cur ^ 1][1], ord[cur ^ 1][2], seg[(L + 1) & 1],
-                                      status + (size_t)L * ntiles, tickets + L);
+    if (hi > lo) {
+      CarriedKeys ck{};
+      if (carry) {
+        for (int d = 0; d < 3; d++) {
+          ck.ka_in[d] = key_a[cur] + (size_t)d * n; ck.kb_in[d] = key_b[cur] + (size_t)d * n;
+          ck.ka_out[d] = key_a[cur ^ 1] + (size_t)d * n; ck.kb_out[d] = key_b[cur ^ 1] + (size_t)d * n;
+        }
+        k_level<true, kLvItemsCarry><<<tiles, kLvThreads, 0, st>>>(
+            n, lo, hi, tile0, level_first, seg[L & 1], seg_rec, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, ord[cur ^ 1][0],
+            ord[cur ^ 1][1], ord[cur ^ 1][2], seg[(L + 1) & 1], status + (size_t)L * ntiles, tickets + L, ck);
+      } else {
+        k_level<false, kLvItems><<<tiles, kLvThreads, 0, st>>>(
+            n, lo, hi, tile0, level_first, seg[L & 1], seg_rec, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, ord[cur ^ 1][0],
+            ord[cur ^ 1][1], ord[cur ^ 1][2], seg[(L + 1) & 1], status + (size_t)L * ntiles, tickets + L, ck);
+      }
+    }
     ctx->launches++;
     cur ^= 1;
   }
@@ -671,6 +744,8 @@ static int build_nodes(pm_ctx* ctx, const pm_photon44* src, int n, int rank, int
   *elem_out = elem_of_node; *dim_out = dim_of_node; *bounds_dev_out = bounds_dev;
   return PM_OK;
 }
+
+void pm_test_build_carry_from(int64_t n_min) { g_carry_min_photons = n_min > 0 ? n_min : kCarryMinPhotons; }
 
 int pm_map_build(pm_ctx* ctx, pm_photon44* photons, int64_t n64, float* bounds_host, pm_map** out) {
   PM_REQUIRE(ctx && out, "ctx/out is NULL");

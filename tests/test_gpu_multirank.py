@@ -33,8 +33,17 @@ def test_sharded_emission_merges_to_single_gpu_order(pkg, ctx, world, caustics):
     assert merged.tobytes() == full.tobytes()
 
 
+@pytest.fixture(params=[False, True], ids=["lists", "carried-keys"])
+def carried(request, pkg):
+    """both variants of the level pass: the default below 2^26 photons, and the large-map one forced on"""
+    if request.param:
+        pkg.lib().pm_test_build_carry_from(1)
+    yield request.param
+    pkg.lib().pm_test_build_carry_from(0)
+
+
 @pytest.mark.parametrize("n,world", [(300000, 2), (300000, 8), (1200001, 4), (5000, 4), (3, 2)])
-def test_sharded_build_equals_single_gpu_build(pkg, ctx, n, world):
+def test_sharded_build_equals_single_gpu_build(pkg, ctx, n, world, carried):
     """pm_map_build_shard for every emulated rank of `world` on ONE GPU, node tables summed as the all-reduce would,
     pm_map_build_finish: the tree array (split_dim included) and the bounds equal pm_map_build's byte for byte —
     unique coordinates and a tie-heavy lattice; trees too small to shard take the whole-build path."""
