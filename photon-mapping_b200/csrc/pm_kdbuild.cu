@@ -390,11 +390,18 @@ struct LocalSmem {
   uint8_t seg_dim[kLocalSegs];
 };
 
+__device__ __forceinline__ float key_to_float(uint32_t k) { /* inverse of ordered_key (-0 comes back as +0) */
+  return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k);
+}
+
+/* CARRY: the lists carry their keys (see k_level): the coordinates come out of the list entries — y and z from list 0's
+ * entry, x from list 1's — instead of three scattered 4-byte reads per element */
+template <bool CARRY>
 __global__ void __launch_bounds__(kLocalThreads)
 k_finish_subtrees(int level_first, int j0, int level_count, int n, const int* __restrict__ ord0, const int* __restrict__ ord1,
                   const int* __restrict__ ord2, const float* __restrict__ cx, const float* __restrict__ cy,
                   const float* __restrict__ cz, const float* __restrict__ box_cur, const int* __restrict__ begin_cur,
-                  int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node) {
+                  int* __restrict__ elem_of_node, uint8_t* __restrict__ dim_of_node, const CarriedKeys ck) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   LocalSmem& sm = *reinterpret_cast<LocalSmem*>(smem_raw);
   using Scan = cub::BlockScan<uint64_t, kLocalThreads>;
@@ -421,7 +428,8 @@ k_finish_subtrees(int level_first, int j0, int level_count, int n, const int* __
   for (int i = tid; i < m; i += kLocalThreads) {
     const int e = ord0[begin0 + i];
     sm.gid[i] = e;
-    sm.c[0][i] = cx[e]; sm.c[1][i] = cy[e]; sm.c[2][i] = cz[e];
+    if (CARRY) { sm.c[1][i] = key_to_float(ck.ka_in[0][begin0 + i]); sm.c[2][i] = key_to_float(ck.kb_in[0][begin0 + i]); }
+    else { sm.c[0][i] = cx[e]; sm.c[1][i] = cy[e]; sm.c[2][i] = cz[e]; }
     sm.lst[0][0][i] = (uint16_t)i;
     sm.segid[i] = 0;
     uint32_t h = ((uint32_t)e * 2654435761u) >> (32 - kHashBits);
@@ -436,6 +444,7 @@ k_finish_subtrees(int level_first, int j0, int level_count, int n, const int* __
       uint32_t h = ((uint32_t)e * 2654435761u) >> (32 - kHashBits);
       while (hkeys[h] != e) h = (h + 1) & (kHashSlots - 1);
       sm.lst[0][d][i] = hvals[h];
+      if (CARRY && d == 1) sm.c[0][hvals[h]] = key_to_float(ck.kb_in[1][begin0 + i]); /* list 1 carries (z, x) */
     }
   }
   __syncthreads();
@@ -698,11 +707,21 @@ static int build_nodes(pm_ctx* ctx, const pm_photon44* src, int n, int rank, int
       j1 = std::min(level_count, (rank + 1) << (L - S));
     }
     if (L == local_from) {
-      PM_CUDA(cudaFuncSetAttribute(k_finish_subtrees, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSmem)));
-      if (j1 > j0)
-        k_finish_subtrees<<<(unsigned)(j1 - j0), kLocalThreads, sizeof(LocalSmem), st>>>(
-            level_first, j0, j1, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
-            elem_of_node, dim_of_node);
+      CarriedKeys ck{};
+      if (carry)
+        for (int d = 0; d < 3; d++) { ck.ka_in[d] = key_a[cur] + (size_t)d * n; ck.kb_in[d] = key_b[cur] + (size_t)d * n; }
+      PM_CUDA(cudaFuncSetAttribute(k_finish_subtrees<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSmem)));
+      PM_CUDA(cudaFuncSetAttribute(k_finish_subtrees<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSmem)));
+      if (j1 > j0) {
+        if (carry)
+          k_finish_subtrees<true><<<(unsigned)(j1 - j0), kLocalThreads, sizeof(LocalSmem), st>>>(
+              level_first, j0, j1, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
+              elem_of_node, dim_of_node, ck);
+        else
+          k_finish_subtrees<false><<<(unsigned)(j1 - j0), kLocalThreads, sizeof(LocalSmem), st>>>(
+              level_first, j0, j1, n, ord[cur][0], ord[cur][1], ord[cur][2], cx, cy, cz, box[L & 1], begin[L & 1],
+              elem_of_node, dim_of_node, ck);
+      }
       ctx->launches++;
       break;
     }
