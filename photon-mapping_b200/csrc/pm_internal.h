@@ -61,7 +61,7 @@ enum ScratchSlot {
   S_STAGE_IN0 = 0, S_STAGE_IN1, S_STAGE_IN2, S_STAGE_OUT0, S_STAGE_OUT1, S_STAGE_OUT2,
   S_KEYS0, S_KEYS1, S_VALS0, S_VALS1, S_CUB, S_PERM, S_MISC0, S_MISC1, S_MISC2, S_MISC3,
   S_BUILD0, S_BUILD1, S_BUILD2, S_BUILD3, S_BUILD4, S_BUILD5, S_BUILD6, S_BUILD7, S_BUILD8,
-  S_BUILD9, S_BUILD10, S_BUILD11, S_BUILD12, S_BUILD13, S_BUILD14, S_BUILD15, S_BUILD16, S_BUILD17, S_BUILD18,
+  S_BUILD9, S_BUILD10, S_BUILD11, S_BUILD12, S_BUILD13, S_BUILD14, S_BUILD15, S_BUILD16, S_BUILD17, S_BUILD18, S_BUILD19,
   S_RENDER0, S_RENDER1, S_RENDER2, S_RENDER3, S_RENDER4, S_RENDER5, S_RENDER6, S_RENDER7,
   S_RENDER8, S_RENDER9, S_RENDER10, S_RENDER11,
   S_FAST0, S_FAST1, S_FAST2,

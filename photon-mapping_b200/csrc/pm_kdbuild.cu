@@ -47,14 +47,16 @@ __device__ inline uint32_t ordered_key(float f) {
 /* AoS -> keys for the three axis sorts, and iota values */
 __global__ void k_extract(const pm_photon44* __restrict__ ph, int n, float* __restrict__ cx, float* __restrict__ cy,
                           float* __restrict__ cz, uint32_t* __restrict__ kx, uint32_t* __restrict__ ky,
-                          uint32_t* __restrict__ kz, int* __restrict__ iota) {
+                          uint32_t* __restrict__ kz, int* __restrict__ iota, uint4* __restrict__ keys4 /* or NULL */) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float* p = reinterpret_cast<const float*>(ph) + (size_t)i * 11;
   const float x = p[0], y = p[1], z = p[2];
   cx[i] = x; cy[i] = y; cz[i] = z;
-  kx[i] = ordered_key(x); ky[i] = ordered_key(y); kz[i] = ordered_key(z);
+  const uint32_t a = ordered_key(x), b = ordered_key(y), c = ordered_key(z);
+  kx[i] = a; ky[i] = b; kz[i] = c;
   iota[i] = i;
+  if (keys4) keys4[i] = make_uint4(a, b, c, 0u); /* all three in one record: k_carry_init gathers it once per list entry */
 }
 
 /* bounds from the sorted lists: min = first element, max = last element of each axis list */
@@ -351,16 +353,16 @@ k_level(int n, int pos_lo, int pos_hi, int tile0, int level_first, const int* __
   }
 }
 
-/* the carried keys of the freshly sorted lists: one gather per list entry and key, once */
-__global__ void k_carry_init(int n, const int* __restrict__ ord0, const uint32_t* __restrict__ keys /* kx | ky | kz */,
+/* the carried keys of the freshly sorted lists: one 16-byte gather per list entry, once */
+__global__ void k_carry_init(int n, const int* __restrict__ ord0, const uint4* __restrict__ keys4,
                              uint32_t* __restrict__ ka0, uint32_t* __restrict__ kb0) {
   /* ord0 / ka0 / kb0 are the bases of 3 n entries: list d at d * n */
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= 3 * (int64_t)n) return;
   const int d = (int)(t / n);
-  const int e = ord0[t];
-  ka0[t] = keys[(size_t)((d + 1) % 3) * n + e];
-  kb0[t] = keys[(size_t)((d + 2) % 3) * n + e];
+  const uint4 k = __ldg(keys4 + ord0[t]);
+  ka0[t] = d == 0 ? k.y : (d == 1 ? k.z : k.x);
+  kb0[t] = d == 0 ? k.z : (d == 1 ? k.x : k.y);
 }
 
 /* ---- the last kLocalLevels levels: one CTA per subtree, everything in shared memory ----------
@@ -625,7 +627,11 @@ static int build_nodes(pm_ctx* ctx, const pm_photon44* src, int n, int rank, int
   for (int b = 0; b < 2; b++) { ord[b][1] = ord[b][0] + n; ord[b][2] = ord[b][0] + 2 * (size_t)n; }
 
   const unsigned nb256 = (unsigned)pm::div_up(n, 256);
-  k_extract<<<nb256, 256, 0, st>>>(src, n, cx, cy, cz, keys_in, keys_in + n, keys_in + 2 * (size_t)n, iota);
+  /* lists that carry their keys from kCarryMinPhotons on (see k_level) */
+  const bool carry = n >= g_carry_min_photons;
+  uint4* keys4 = nullptr;
+  if (carry) PM_CHECK(ctx->get_scratch(pm::S_BUILD19, (size_t)n, &keys4));
+  k_extract<<<nb256, 256, 0, st>>>(src, n, cx, cy, cz, keys_in, keys_in + n, keys_in + 2 * (size_t)n, iota, keys4);
   ctx->launches++;
 
   /* three stable LSD radix sorts: ties keep ascending element index */
@@ -643,15 +649,13 @@ static int build_nodes(pm_ctx* ctx, const pm_photon44* src, int n, int rank, int
   /* per-level state */
   const int num_levels = 32 - __builtin_clz((unsigned)n);  /* floor(log2 n) + 1 */
   const int max_width = (n + 1) / 2 + 1;
-  /* lists that carry their keys from kCarryMinPhotons on (see k_level) */
-  const bool carry = n >= g_carry_min_photons;
   const int kTile = kLvThreads * (carry ? kLvItemsCarry : kLvItems);
   uint32_t *key_a[2] = {nullptr, nullptr}, *key_b[2] = {nullptr, nullptr};
   if (carry) {
     PM_CHECK(ctx->get_scratch(pm::S_BUILD17, (size_t)n * 6, &key_a[0]));
     PM_CHECK(ctx->get_scratch(pm::S_BUILD18, (size_t)n * 6, &key_b[0]));
     key_a[1] = key_a[0] + 3 * (size_t)n; key_b[1] = key_b[0] + 3 * (size_t)n;
-    k_carry_init<<<(unsigned)pm::div_up(3 * (int64_t)n, 256), 256, 0, st>>>(n, ord[0][0], keys_in, key_a[0], key_b[0]);
+    k_carry_init<<<(unsigned)pm::div_up(3 * (int64_t)n, 256), 256, 0, st>>>(n, ord[0][0], keys4, key_a[0], key_b[0]);
     ctx->launches++;
   }
   const unsigned ntiles = (unsigned)pm::div_up(n, kTile);
