@@ -228,7 +228,7 @@ int  pm_map_build_shard(pm_ctx* ctx, const pm_photon44* photons_dev, int64_t n, 
 int  pm_map_build_finish(pm_ctx* ctx, pm_photon44* photons_dev, int64_t n, const int32_t* node_elem_dev,
                          const uint8_t* node_dim_dev, const float* bounds_host, pm_map** out);
 /* test hook: pm_map_build and its sharded variants let the per-axis index lists carry their sort keys from n_min photons
- * on (the variant for maps too large for L2, 2^26 by default; same tree either way). n_min <= 0 restores the default. */
+ * on (the variant for maps too large for L2, 2^24 by default; same tree either way). n_min <= 0 restores the default. */
 void pm_test_build_carry_from(int64_t n_min);
 /* Wrap an array that is ALREADY in tree order (e.g. built by the reference builder). */
 int  pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map** out);

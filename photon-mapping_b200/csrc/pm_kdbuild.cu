@@ -152,9 +152,9 @@ __global__ void k_split(int level_first, int j0, int level_count, int n, const i
  * L2 and IPC 1.5 at 95 % occupancy: bound by those per-tile latencies, not by any unit. */
 constexpr int kLvThreads = 256, kLvWarps = kLvThreads / 32;
 constexpr int kLvItems = 4;       /* lists of element ids only: 1 024 positions per tile */
-/* measured on B200 (tools/time_build.py, whole build): 20 M 15.7 vs 14.6 ms, 30 M 23.4 vs 22.2, 50 M 40.8 vs 41.0,
- * 100 M 84.3 vs 100.5 with / without carried keys */
-constexpr int64_t kCarryMinPhotons = (int64_t)1 << 26;
+/* measured on B200 (tools/time_build.py, whole build, with / without carried keys): 5 M 3.87 / 3.74 ms, 10 M 7.28 / 7.17,
+ * 20 M 14.41 / 14.59, 30 M 20.87 / 22.11, 50 M 35.93 / 40.93, 100 M 73.3 / 100.5 */
+constexpr int64_t kCarryMinPhotons = (int64_t)1 << 24;
 int64_t g_carry_min_photons = kCarryMinPhotons; /* pm_test_build_carry_from */
 constexpr int kLvItemsCarry = 2;  /* lists that carry their keys (below): 36 instead of 12 bytes per position in registers */
 constexpr uint64_t kStInvalid = 0ull, kStAgg = 1ull << 62, kStPrefix = 2ull << 62, kStMask = 3ull << 62;

@@ -35,7 +35,7 @@ def test_sharded_emission_merges_to_single_gpu_order(pkg, ctx, world, caustics):
 
 @pytest.fixture(params=[False, True], ids=["lists", "carried-keys"])
 def carried(request, pkg):
-    """both variants of the level pass: the default below 2^26 photons, and the large-map one forced on"""
+    """both variants of the level pass: the default below 2^24 photons, and the large-map one forced on"""
     if request.param:
         pkg.lib().pm_test_build_carry_from(1)
     yield request.param

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Times warm pm_map_build calls on the C2 cloud: min / median of N builds. Usage: python tools/time_build.py [n_photons] [reps]"""
+"""Times warm pm_map_build calls on the C2 cloud: min / median of N builds. Usage: python tools/time_build.py [n_photons] [reps] [carry_from]"""
 import os
 import sys
 import time
@@ -15,6 +15,8 @@ import bench  # noqa: E402
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 12
 pkg = graft.load_package()
+if len(sys.argv) > 3:  # force the carried-keys variant of the level pass from this many photons on
+    pkg.lib().pm_test_build_carry_from(int(sys.argv[3]))
 ctx = pkg.Context(0)
 cloud = torch.from_numpy(bench.make_cloud(n).view(np.uint8))
 d_tree = cloud.cuda()
