@@ -25,6 +25,9 @@ timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'k_
 timeout 300 python tools/prof_emit.py cornell 4000000 3 > gpurun_out/${tag}_plain_emit.log 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_walk -s 1 -c 1 -o gpurun_out/${tag}_walk \
   python tools/prof_emit.py cornell 4000000 3 > gpurun_out/${tag}_ncu_w.log 2>&1
+timeout 300 python tools/prof_emit.py big 16000000 2 > gpurun_out/${tag}_plain_emit_big.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_walk -s 1 -c 1 -o gpurun_out/${tag}_walk_big \
+  python tools/prof_emit.py big 16000000 2 > gpurun_out/${tag}_ncu_wb.log 2>&1
 timeout 300 python tools/prof_build.py 10000000 2 > gpurun_out/${tag}_plain_build.log 2>&1 && \
 timeout 1500 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__inst_executed.avg.per_cycle_active,l1tex__throughput.avg.pct_of_peak_sustained_elapsed,lts__throughput.avg.pct_of_peak_sustained_elapsed,gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed,sm__warps_active.avg.pct_of_peak_sustained_active,launch__registers_per_thread \
   --clock-control none -o gpurun_out/${tag}_build python tools/prof_build.py 10000000 1 > gpurun_out/${tag}_ncu_b.log 2>&1

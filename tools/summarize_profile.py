@@ -27,7 +27,8 @@ STEP_KERNELS = ("k_qbin_count", "k_qbin_scan", "k_qbin_scatter", "k_knn_fast", "
 
 
 def short_name(kname: str) -> str:
-    return kname.split("(")[0].replace("void ", "").strip().split("<")[0].split("::")[-1]
+    base = kname.split("(")[0].replace("void ", "").replace("<unnamed>::", "").strip()
+    return base.split("<")[0].split("::")[-1]
 
 
 if os.path.exists(launches):
