@@ -410,8 +410,10 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
     } else {
       /* gatherPhotons (ray-tracer/cuda/shading.h:93-121), summed across the warp. Division and square root are the
        * call-free fast paths of pm_knn.cuh; a query with an operand outside their range goes to the kd-tree kernel */
-      bool ok = pmk::sqrt_fast_ok(r2);
       const float rad = pmk::sqrt_rn_fast(r2);
+      /* rad is checked once; an accepted distance is 0 or lies in [2^-50.5, rad] as soon as its square passes the
+       * square root's own test (>= 2^-101), which is then all div_fast_ok(dist, rad) would ask */
+      bool ok = pmk::sqrt_fast_ok(r2) && pmk::div_fast_ok(rad, rad);
       float fr = 0.f, fg = 0.f, fb = 0.f;
 #pragma unroll
       for (int s = 0; s <= kSlots; s++) {
@@ -422,7 +424,7 @@ k_grid_query(const GridView g, const float4* __restrict__ color4, const pmk::Que
           const float4 c = __ldg(color4 + id);
           const float d2v = __int_as_float(hv);
           const float dist = pmk::sqrt_rn_fast(d2v);
-          ok = ok && pmk::sqrt_fast_ok(d2v) && pmk::div_fast_ok(dist, rad);
+          ok = ok && pmk::sqrt_fast_ok(d2v);
           const float w = __fsub_rn(1.f, __fmul_rn(pmk::div_rn_fast(dist, rad), 1.1f));
           const float sc = __fmul_rn(__fmul_rn(brdf, c.w), w);
           fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
@@ -736,8 +738,8 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
       /* gatherPhotons (ray-tracer/cuda/shading.h:93-121), summed across the warp; call-free division / square root
        * (pm_knn.cuh), exotic operands go to the general kernel */
       const float r2 = __uint_as_float(tau);
-      bool ok = pmk::sqrt_fast_ok(r2);
       const float rad = pmk::sqrt_rn_fast(r2);
+      bool ok = pmk::sqrt_fast_ok(r2) && pmk::div_fast_ok(rad, rad); /* see k_grid_query */
       float fr = 0.f, fg = 0.f, fb = 0.f;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
@@ -745,7 +747,7 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
           const float4 c = __ldg(color4 + kv[s].y);
           const float d2v = __uint_as_float(kv[s].x);
           const float dist = pmk::sqrt_rn_fast(d2v);
-          ok = ok && pmk::sqrt_fast_ok(d2v) && pmk::div_fast_ok(dist, rad);
+          ok = ok && pmk::sqrt_fast_ok(d2v);
           const float w = __fsub_rn(1.f, __fmul_rn(pmk::div_rn_fast(dist, rad), 1.1f));
           const float sc = __fmul_rn(__fmul_rn(brdf, c.w), w);
           fr = __fadd_rn(fr, __fmul_rn(sc, c.x));
