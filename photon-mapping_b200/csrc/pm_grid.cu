@@ -1386,49 +1386,12 @@ int cells_reorder(pm_ctx* ctx, pm_map* m) {
  * 0.806, 1.25 k + 10 0.797, 1.25 k + 20 0.803, 1.4 k + 10 0.822, 1.5 k + 16 0.827 — flat around the choice. */
 static float fast_expected_count(int k) { return 1.25f * (float)k + 10.f; }
 
-int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
-  const bool given = cell_size > 0.f; /* cells-only map: the caller names the cell, nothing is sampled (there is no tree) */
-  if (!given && m->n < kMinGridNodes) return PM_OK;
+/* dimensions for m->cell (grown until the offset table fits), then: node ids sorted by cell, the cell-ordered records,
+ * the offset table and — fast-path maps — its x-slowest copy. Leaves the map without a grid when the memory is not there. */
+static int grid_fill_arrays(pm_ctx* ctx, pm_map* m, bool given) {
   const int n = (int)m->n;
   cudaStream_t st = ctx->stream;
-  float cell = cell_size, rk = 2.f * cell_size;
-  bool uniform_like = false;
-  if (!given) {
-    /* 1. sample of exact k-th-neighbour distances (kd-tree kernel on kTuneSamples node positions) */
-    const int ns = kTuneSamples;
-    float *sq = nullptr, *sr2 = nullptr;
-    PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)ns * 3, &sq));
-    PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)ns, &sr2));
-    k_sample_queries<<<(unsigned)div_up(ns, 256), 256, 0, st>>>(m->nodes4, n, ns, sq);
-    ctx->launches++;
-    pmk::QueryIO io;
-    io.q = sq; io.nq = ns; io.k = kTuneK; io.cutoff2 = INFINITY; io.r2 = sr2;
-    PM_CHECK(kd_query(ctx, m, io, false, nullptr, nullptr));
-    std::vector<float> r2(ns);
-    PM_CUDA(cudaMemcpyAsync(r2.data(), sr2, sizeof(float) * ns, cudaMemcpyDeviceToHost, st));
-    PM_CUDA(cudaStreamSynchronize(st));
-    std::sort(r2.begin(), r2.end());
-    const float r50 = std::sqrt(r2[ns / 2]), r98 = std::sqrt(r2[(size_t)(ns * 0.98)]);
-    if (!(r98 > 0.f) || !std::isfinite(r98)) return PM_OK; /* degenerate cloud: kd-tree kernels only */
-    /* G >= 2 cells: two cells must cover the k-th-neighbour distance of nearly every query. Tight
-     * distributions (uniform clouds) take the 98th percentile plus a little; broad ones would pay
-     * for their tail in every dense neighbourhood, so they take the 90th and leave the rest to the
-     * kd-tree kernel. */
-    uniform_like = r98 < 1.25f * r50;
-    rk = uniform_like ? r98 * 1.03f : std::sqrt(r2[(size_t)(ns * 0.90)]);
-    cell = 0.5f * rk;
-    /* degenerate cloud (most sampled neighbourhoods are coincident photons): kd-tree kernels only */
-    if (!(cell > 0.f) || !std::isfinite(cell)) return PM_OK;
-    m->tuned_r50 = r50;
-    if (uniform_like) {
-      /* the fast path starts every query at the radius expected to hold 1.25 kTuneK + 10 photons and needs two
-       * cells (less the margins) to cover it: see fast_first_radius2 */
-      float maxabs0 = 0.f;
-      for (int d = 0; d < 6; d++) maxabs0 = std::max(maxabs0, std::fabs(m->bounds[d]));
-      const float r_first = r50 * std::cbrt(fast_expected_count(kTuneK) / ((float)kTuneK - 0.33f));
-      cell = (0.5f * r_first + 2.f * 16.f * FLT_EPSILON * maxabs0) / (1.f - 2.5e-3f);
-    }
-  }
+  float cell = m->cell;
   float maxabs = 0.f;
   for (int d = 0; d < 3; d++) {
     maxabs = std::max(maxabs, std::max(std::fabs(m->bounds[d]), std::fabs(m->bounds[3 + d])));
@@ -1447,13 +1410,11 @@ int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
     if (cells <= cell_cap && dim[0] < 32768 && dim[1] < 32768 && dim[2] < 32768) break;
     cell *= 1.26f;
   }
-  m->cell = cell; m->inv_cell = 1.f / cell; m->tuned_rk = rk;
-  m->fast_path = uniform_like; /* the descriptor pass models the cloud as locally uniform */
+  m->cell = cell; m->inv_cell = 1.f / cell;
   m->cell_margin = 1e-3f * cell + 16.f * FLT_EPSILON * maxabs;
   m->gdim[0] = dim[0]; m->gdim[1] = dim[1]; m->gdim[2] = dim[2];
   const int64_t n_cells = (int64_t)dim[0] * dim[1] * dim[2];
 
-  /* 2. sort node ids by cell, emit the cell-ordered records and the offset table */
   uint32_t *keys_in, *keys_out; int *vals_in, *vals_out;
   PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)n, &keys_in));
   PM_CHECK(ctx->get_scratch(pm::S_KEYS1, (size_t)n, &keys_out));
@@ -1464,6 +1425,7 @@ int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
     cudaGetLastError();
     pm::map_free(m->grid_pts);
     m->grid_pts = nullptr; m->cell_start = nullptr; /* no grid: the kd-tree kernels answer everything */
+    m->fast_path = false;
     if (given) { pm::set_error("pm_map_build_cells: out of device memory for the cell table"); return PM_ERR_NOMEM; }
     return PM_OK;
   }
@@ -1494,6 +1456,95 @@ int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
     }
   }
   return PM_OK;
+}
+
+__global__ void k_sample_to_sq(const float* __restrict__ q, int ns, float4* __restrict__ sq) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < ns) sq[i] = make_float4(q[3 * i], q[3 * i + 1], q[3 * i + 2], __int_as_float(i));
+}
+
+/* share of the sample the fast path may hand to the general kernel and still be the one to use */
+constexpr float kFastTrialMaxHandover = 0.10f;
+
+int grid_query(pm_ctx* ctx, const pm_map* map, const pmk::QueryIO& io, bool gather, int* fb_list, int* fb_count);
+
+int grid_build(pm_ctx* ctx, pm_map* m, float cell_size) {
+  const bool given = cell_size > 0.f; /* cells-only map: the caller names the cell, nothing is sampled (there is no tree) */
+  if (!given && m->n < kMinGridNodes) return PM_OK;
+  const int n = (int)m->n;
+  cudaStream_t st = ctx->stream;
+  if (given) {
+    m->cell = cell_size; m->tuned_rk = 2.f * cell_size; m->fast_path = false;
+    return grid_fill_arrays(ctx, m, true);
+  }
+  /* 1. sample of exact k-th-neighbour distances (kd-tree kernel on kTuneSamples node positions) */
+  const int ns = kTuneSamples;
+  float *sq = nullptr, *sr2 = nullptr;
+  PM_CHECK(ctx->get_scratch(pm::S_MISC0, (size_t)ns * 3, &sq));
+  PM_CHECK(ctx->get_scratch(pm::S_MISC3, (size_t)ns, &sr2));
+  k_sample_queries<<<(unsigned)div_up(ns, 256), 256, 0, st>>>(m->nodes4, n, ns, sq);
+  ctx->launches++;
+  {
+    pmk::QueryIO io;
+    io.q = sq; io.nq = ns; io.k = kTuneK; io.cutoff2 = INFINITY; io.r2 = sr2;
+    PM_CHECK(kd_query(ctx, m, io, false, nullptr, nullptr));
+  }
+  std::vector<float> r2(ns);
+  PM_CUDA(cudaMemcpyAsync(r2.data(), sr2, sizeof(float) * ns, cudaMemcpyDeviceToHost, st));
+  PM_CUDA(cudaStreamSynchronize(st));
+  std::sort(r2.begin(), r2.end());
+  const float r50 = std::sqrt(r2[ns / 2]), r90 = std::sqrt(r2[(size_t)(ns * 0.90)]), r98 = std::sqrt(r2[(size_t)(ns * 0.98)]);
+  if (!(r98 > 0.f) || !std::isfinite(r98)) return PM_OK; /* degenerate cloud: kd-tree kernels only */
+  m->tuned_r50 = r50;
+  float maxabs0 = 0.f;
+  for (int d = 0; d < 6; d++) maxabs0 = std::max(maxabs0, std::fabs(m->bounds[d]));
+  /* The fast path (k_knn_fast) starts every query at ONE radius — the one expected to hold 1.25 kTuneK + 10 photons at
+   * the median density — and needs two cells (less the margins) to cover it: see fast_first_radius2. Tight
+   * distributions of the k-th-neighbour distance (uniform clouds: r98 < 1.25 r50) take it unseen. Broader ones — photon
+   * maps proper: surfaces lit unevenly — take it if it proves itself: the sample is run through it, and it stays when it
+   * hands over no more than a tenth. (Forced on the surface clouds of the C1-like 1024x1024 frame and of the C4 room it
+   * answered everything itself and the gather kernels took 11.8 instead of 17.1 ms, the C4-like render 60.8 instead of
+   * 84.2 ms: a query off the median density costs a second attempt at a rescaled radius, which is still cheaper than
+   * the general kernel's density pass and histogram selection.) */
+  const bool uniform_like = r98 < 1.25f * r50;
+  const float r_first = r50 * std::cbrt(fast_expected_count(kTuneK) / ((float)kTuneK - 0.33f));
+  const float cell_fast = (0.5f * r_first + 2.f * 16.f * FLT_EPSILON * maxabs0) / (1.f - 2.5e-3f);
+  if (cell_fast > 0.f && std::isfinite(cell_fast)) {
+    m->cell = cell_fast; m->tuned_rk = r98 * 1.03f; m->fast_path = true;
+    PM_CHECK(grid_fill_arrays(ctx, m, false));
+    if (!m->grid_pts) return PM_OK;
+    if (m->fast_path && uniform_like) return PM_OK;
+    if (m->fast_path) {
+      float4* sq4 = nullptr; int32_t* ids = nullptr; int *fb_list = nullptr, *fb_count = nullptr;
+      PM_CHECK(ctx->get_scratch(pm::S_VALS1, (size_t)ns, &sq4));
+      PM_CHECK(ctx->get_scratch(pm::S_VALS0, (size_t)ns * kTuneK, &ids));
+      PM_CHECK(ctx->get_scratch(pm::S_MISC1, (size_t)ns, &fb_list));
+      PM_CHECK(ctx->get_scratch(pm::S_MISC2, (size_t)4, &fb_count));
+      PM_CUDA(cudaMemsetAsync(fb_count, 0, sizeof(int), st));
+      k_sample_to_sq<<<(unsigned)div_up(ns, 256), 256, 0, st>>>(sq, ns, sq4);
+      ctx->launches++;
+      pmk::QueryIO io;
+      io.q = sq; io.sq = sq4; io.nq = ns; io.k = kTuneK; io.cutoff2 = INFINITY; io.ids = ids;
+      PM_CHECK(grid_query(ctx, m, io, false, fb_list, fb_count));
+      int handed = ns;
+      if (ctx->ho_count_dev) PM_CUDA(cudaMemcpyAsync(&handed, ctx->ho_count_dev, sizeof(int), cudaMemcpyDeviceToHost, st));
+      PM_CUDA(cudaStreamSynchronize(st));
+      ctx->ho_count_dev = nullptr;
+      if ((float)handed <= kFastTrialMaxHandover * (float)ns) return PM_OK;
+    }
+    /* not this cloud: drop the grid and build the general kernel's */
+    pm::map_free(m->grid_pts); pm::map_free(m->cell_start); pm::map_free(m->cell_start_t);
+    m->grid_pts = nullptr; m->cell_start = nullptr; m->cell_start_t = nullptr;
+  }
+  /* G >= 2 cells: two cells must cover the k-th-neighbour distance of nearly every query; a broad distribution would
+   * pay for its tail in every dense neighbourhood, so it takes the 90th percentile and leaves the rest to the kd-tree
+   * kernel. */
+  m->fast_path = false;
+  m->tuned_rk = r90;
+  m->cell = 0.5f * r90;
+  /* degenerate cloud (most sampled neighbourhoods are coincident photons): kd-tree kernels only */
+  if (!(m->cell > 0.f) || !std::isfinite(m->cell)) return PM_OK;
+  return grid_fill_arrays(ctx, m, false);
 }
 
 /* first search radius² of the fast path for k neighbours: the radius expected to hold 1.25 k + 10 photons, from the

@@ -25,3 +25,4 @@ for it in range(reps):
     fb = scene.render(lights, gmap, cmap, cam, W, H, 1, 1)
     print(f"render {it}: {1e3 * (time.perf_counter() - t0):.2f} ms, global-map gather kernels {ctx.last_kernel_ms:.2f} ms, "
           f"photons {len(g44)} + {len(c44)}, kd fallbacks {ctx.last_fallback_count}, lit {float((fb[1:] != 0).mean()):.3f}", flush=True)
+print("hand-overs of the last gather call:", ctx.last_handover_count, "kd fallbacks:", ctx.last_fallback_count)
