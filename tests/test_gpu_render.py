@@ -44,6 +44,29 @@ def test_render_matches_oracle(pkg, ctx, orc, cornell, spp, depth):
     assert mx <= 1 and frac < 1e-3, (mx, frac)
 
 
+def test_render_matches_oracle_on_a_large_scene(pkg, ctx, orc):
+    """a 6 000-triangle soup (above 4 096: Morton-built hierarchy, final-gather rays traced by the vote-driven warp
+    traversal, k_fg<true>; the stored photons come from k_walk<true>): same image as the oracle's brute-force tracer"""
+    from helpers import LIGHT, soup_scene
+
+    sc = soup_scene(6000, 10, extent=6.0, size=1.8)
+    sc["lights"] = np.zeros(2, LIGHT)  # on the camera's side of the soup
+    sc["lights"][0] = ((3.0, 3.0, -6.0), (1, 1, 1), 40.0)
+    sc["lights"][1] = ((-3.0, 8.0, -4.0), (1.0, 0.9, 0.8), 30.0)
+    s = pkg.Scene(ctx, sc["verts"], sc["tris"], sc["tri_mesh"], sc["mats"])
+    g40, _, _, _ = s.emit_photons(sc["lights"], 20000, 8, False)
+    c40, _, _, _ = s.emit_photons(sc["lights"], 5000, 8, True)
+    g44, c44 = pkg.photons_to_maps(ctx, g40, c40)
+    gmap, cmap = pkg.PhotonMap.build(ctx, g44), pkg.PhotonMap.build(ctx, c44)
+    W, H = 64, 48
+    cam = pkg.make_camera([3.0, 3.0, -9.0], [3.0, 3.0, 3.0], [0.0, 1.0, 0.0], 0.9, W, H)
+    fb = s.render(sc["lights"], gmap, cmap, cam, W, H, 1, 2)
+    want, _ = oracle_render(orc, sc, g44, c44, cam, W, H, 1, 2)
+    mx, frac = compare(fb, want)
+    assert (want[1:] != 0xFFFFFFFF).mean() > 0.5 and len(np.unique(want)) > 200  # the camera sees the soup, lit unevenly
+    assert mx <= 1 and frac < 1e-3, (mx, frac)
+
+
 def test_render_without_maps_and_tiles(pkg, ctx, orc, cornell):
     sc, s, g44, c44, gmap, cmap = cornell
     W, H = 64, 48

@@ -128,9 +128,16 @@ def test_empty_scene(pkg, ctx):
 
 
 @pytest.mark.parametrize("caustics", [False, True])
-@pytest.mark.parametrize("scene_name", ["cornell_box", "sphere", "soup"])
+@pytest.mark.parametrize("scene_name", ["cornell_box", "sphere", "soup", "soup_6000"])
 def test_emit_matches_oracle_lcg(pkg, ctx, orc, scene_name, caustics):
-    sc = soup_scene(3000, 9, extent=6.0, size=2.5) if scene_name == "soup" else load_scene(scene_name)
+    """soup_6000 is above the 4 096 triangles from which the walk uses the vote-driven warp traversal (k_walk<true>) on
+    a Morton-built hierarchy; the others take the while-while loop on the host-built SAH hierarchy"""
+    if scene_name == "soup":
+        sc = soup_scene(3000, 9, extent=6.0, size=2.5)
+    elif scene_name == "soup_6000":
+        sc = soup_scene(6000, 10, extent=6.0, size=1.8)
+    else:
+        sc = load_scene(scene_name)
     casted, depth = (20000, 10) if scene_name != "sphere" else (3000, 6)
     s = make_scene(pkg, ctx, sc)
     got, cnt, npaths, nseg = s.emit_photons(sc["lights"], casted, depth, caustics)
