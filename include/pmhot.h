@@ -240,6 +240,9 @@ int  pm_map_from_tree(pm_ctx* ctx, const pm_photon44* photons, int64_t n, pm_map
 int  pm_map_build_cells(pm_ctx* ctx, const pm_photon44* photons, int64_t n, float cell_size, pm_map** out);
 void pm_map_destroy(pm_map* map);
 int64_t pm_map_size(const pm_map* map);
+/* test hook: which query kernels the map chose when it was built — 0: kd-tree kernels only (small or degenerate maps),
+ * 1: uniform-grid general kernel, 2: fast path (uniform-like clouds, and clouds whose tuning sample passed its trial) */
+int  pm_map_query_path(const pm_map* map);
 
 /* ---- stage 3 ------------------------------------------------------------------------- */
 /* kNN (≙ cukd::stackBased::knn<HeapCandidateList<k>> with cutoff radius):

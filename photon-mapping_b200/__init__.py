@@ -107,6 +107,7 @@ _SIGNATURES = {
     "pm_map_build_cells": (c_int, [c_void_p, c_void_p, c_int64, c_float, POINTER(c_void_p)]),
     "pm_map_destroy": (None, [c_void_p]),
     "pm_map_size": (c_int64, [c_void_p]),
+    "pm_map_query_path": (c_int, [c_void_p]),
     "pm_knn": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "pm_knn_static": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "pm_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_void_p]),

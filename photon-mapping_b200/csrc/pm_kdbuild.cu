@@ -954,5 +954,6 @@ void pm_map_destroy(pm_map* m) {
 }
 
 int64_t pm_map_size(const pm_map* m) { return m ? m->n : 0; }
+int pm_map_query_path(const pm_map* m) { return !m || !m->grid_pts ? 0 : (m->fast_path ? 2 : 1); }
 
 }  // extern "C"
