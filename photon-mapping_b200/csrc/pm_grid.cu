@@ -741,11 +741,26 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
       const float rad = pmk::sqrt_rn_fast(r2);
       bool ok = pmk::sqrt_fast_ok(r2) && pmk::div_fast_ok(rad, rad); /* see k_grid_query */
       float fr = 0.f, fg = 0.f, fb = 0.f;
+      /* the k accepted entries are compacted first (as for the id output above): the sum then runs over two full-width
+       * steps instead of four register slots of which 70 % hold an accepted entry (191 -> ~130 instructions per query) */
+      __syncwarp();
+      int base = 0;
 #pragma unroll
       for (int s = 0; s < kSlots; s++) {
-        if (kv[s].x <= tau) {
-          const float4 c = __ldg(color4 + kv[s].y);
-          const float d2v = __uint_as_float(kv[s].x);
+        if (s == kSlots - 1 && !four) break;
+        const bool a = kv[s].x <= tau;
+        const unsigned b = __ballot_sync(0xffffffffu, a);
+        if (a) ws.keys[base + __popc(b & lt)] = kv[s];
+        base += __popc(b);
+      }
+      __syncwarp();
+#pragma unroll
+      for (int u = 0; u < 2; u++) { /* k <= 64 */
+        const int p = lane + 32 * u;
+        if (p < k) {
+          const uint2 e = ws.keys[p];
+          const float4 c = __ldg(color4 + e.y);
+          const float d2v = __uint_as_float(e.x);
           const float dist = pmk::sqrt_rn_fast(d2v);
           ok = ok && pmk::sqrt_fast_ok(d2v);
           const float w = __fsub_rn(1.f, __fmul_rn(pmk::div_rn_fast(dist, rad), 1.1f));
