@@ -521,12 +521,27 @@ k_knn_fast(const GridView g, const float4* __restrict__ color4, const pmk::Query
   const float fk = (float)k;
   /* rows of the 5x5 block of the first attempt: lane -> (oy, oz) */
   const int oz5 = div_small(lane, 5) - 2, oy5 = lane - (oz5 + 2) * 5 - 2;
+  /* GATHER: the next query (position and factor, both in processing order) is loaded while this one is answered — the
+   * two dependent loads at the head of the loop were where a quarter of the kernel's stall samples sat */
+  float4 qnext = make_float4(0.f, 0.f, 0.f, 0.f);
+  float bnext = 0.f;
+  if (GATHER) {
+    const int t0 = blockIdx.x * kWarps + wid;
+    if (t0 < io.nq) { qnext = __ldg(fp.sq + t0); bnext = __ldg(io.sbrdf + t0); }
+  }
   for (int t = blockIdx.x * kWarps + wid; t < io.nq; t += gridDim.x * kWarps) {
-    const float4 qv = __ldg(fp.sq + t);
-    const int qi = __float_as_int(qv.w);
+    float4 qv;
     float brdf = 0.f;
     if (GATHER) {
-      brdf = __shfl_sync(0xffffffffu, __ldg(io.brdf + qi), 0); /* warp-uniform to the compiler */
+      qv = qnext; brdf = bnext;
+      const int tn = t + gridDim.x * kWarps;
+      if (tn < io.nq) { qnext = __ldg(fp.sq + tn); bnext = __ldg(io.sbrdf + tn); }
+    } else {
+      qv = __ldg(fp.sq + t);
+    }
+    const int qi = __float_as_int(qv.w);
+    if (GATHER) {
+      brdf = __shfl_sync(0xffffffffu, brdf, 0); /* warp-uniform to the compiler */
       if (!(brdf > 0.f)) {
         if (lane < 3) io.rgb[(size_t)qi * 3 + lane] = 0.f;
         continue;

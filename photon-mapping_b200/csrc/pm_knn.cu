@@ -148,7 +148,8 @@ k_qbin_scan(uint32_t* __restrict__ hist, int nbins, unsigned long long* __restri
 
 __global__ void __launch_bounds__(256)
 k_qbin_scatter(const float* __restrict__ q, const uint32_t* __restrict__ codes, int nq, int bits,
-               uint32_t* __restrict__ cursor, int* __restrict__ perm, float4* __restrict__ sq) {
+               uint32_t* __restrict__ cursor, int* __restrict__ perm, float4* __restrict__ sq,
+               const float* __restrict__ brdf, float* __restrict__ sbrdf) {
   uint32_t pos[kQItems];
   float qx[kQItems], qy[kQItems], qz[kQItems];
 #pragma unroll
@@ -174,6 +175,7 @@ k_qbin_scatter(const float* __restrict__ q, const uint32_t* __restrict__ codes, 
     if (i < nq) {
       if (perm) perm[pos[it]] = i;
       if (sq) sq[pos[it]] = make_float4(qx[it], qy[it], qz[it], __int_as_float(i));
+      if (sbrdf) sbrdf[pos[it]] = brdf[i];
     }
   }
 }
@@ -181,11 +183,12 @@ k_qbin_scatter(const float* __restrict__ q, const uint32_t* __restrict__ codes, 
 /* Morton-bin order of the queries inside the map's box -> permutation in scratch slot S_PERM and, with `sq_out`, the
  * queries themselves in that order as float4 (x, y, z, bits(index)) in S_VALS1 */
 int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float* brdf_dev, int nq, int** perm_out,
-                 float4** sq_out) {
-  uint32_t *codes, *hist; int* perm; float4* sq = nullptr;
+                 float4** sq_out, float** sbrdf_out = nullptr) {
+  uint32_t *codes, *hist; int* perm; float4* sq = nullptr; float* sbrdf = nullptr;
   PM_CHECK(ctx->get_scratch(pm::S_KEYS0, (size_t)nq, &codes));
   PM_CHECK(ctx->get_scratch(pm::S_PERM, (size_t)nq, &perm));
   if (sq_out) PM_CHECK(ctx->get_scratch(pm::S_VALS1, (size_t)nq, &sq));
+  if (sq_out && sbrdf_out && brdf_dev) PM_CHECK(ctx->get_scratch(pm::S_VALS0, (size_t)nq, &sbrdf));
   /* bins per axis: about four queries per bin, 2^4 .. 2^7 (a finer grid only costs the scan) */
   int bits = 4;
   while (bits < kQBitsMax && ((int64_t)1 << (3 * bits)) * 4 < nq) bits++;
@@ -207,11 +210,12 @@ int sort_queries(pm_ctx* ctx, const pm_map* map, const float* q_dev, const float
   k_qbin_count<<<grid, 256, 0, ctx->stream>>>(q_dev, brdf_dev, nq, box, bits, codes, hist);
   k_qbin_scan<<<tiles, 256, 0, ctx->stream>>>(hist, bins, status, tile_counter);
   /* the fast path reads the ordered queries themselves (sq) and nothing else reads the permutation then */
-  k_qbin_scatter<<<grid, 256, 0, ctx->stream>>>(q_dev, codes, nq, bits, hist, sq ? nullptr : perm, sq);
+  k_qbin_scatter<<<grid, 256, 0, ctx->stream>>>(q_dev, codes, nq, bits, hist, sq ? nullptr : perm, sq, brdf_dev, sbrdf);
   ctx->launches += 3;
   PM_CUDA(cudaGetLastError());
   *perm_out = perm;
   if (sq_out) *sq_out = sq;
+  if (sbrdf_out) *sbrdf_out = sbrdf;
   return PM_OK;
 }
 
@@ -349,9 +353,11 @@ int run_queries(pm_ctx* ctx, const pm_map* map, pmk::QueryIO io, bool gather, bo
   if (time_it) PM_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
   int* perm = nullptr;
   float4* sq = nullptr;
-  PM_CHECK(sort_queries(ctx, map, io.q, gather ? io.brdf : nullptr, io.nq, &perm, map->fast_path ? &sq : nullptr));
+  float* sbrdf = nullptr;
+  PM_CHECK(sort_queries(ctx, map, io.q, gather ? io.brdf : nullptr, io.nq, &perm, map->fast_path ? &sq : nullptr, &sbrdf));
   io.order = sq ? nullptr : perm; /* with sq the permutation is not written (sort_queries) */
   io.sq = sq;
+  io.sbrdf = sbrdf;
   ctx->fb_count_dev = nullptr;
   ctx->ho_count_dev = nullptr;
   if (map->grid_pts) {
